@@ -1,0 +1,245 @@
+"""ctypes binding of libedsbwt_cuda.so (include/edsbwt.h) -- the only Python in the product path.
+
+The directory name carries a hyphen (it mirrors the reference's name), so load it with
+``importlib.import_module("eds-bwt_b200")``.  Nothing here computes: every call goes through the C ABI
+into the CUDA library and raises if the library is missing or no GPU is present (no CPU fallback).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libedsbwt_cuda.so")
+
+LOCATE_SA, LOCATE_WALK = 0, 1
+LF_RANK, LF_MOVE = 0, 1
+
+OCC_DTYPE = np.dtype([("pat", "<u4"), ("str", "<u4"), ("seg", "<u4"), ("idx_in_seg", "<u4"), ("off", "<u4")])
+
+EXPORTS = [
+    "edsbwt_index_open", "edsbwt_index_open_ex", "edsbwt_index_info", "edsbwt_index_close", "edsbwt_search",
+    "edsbwt_search_device", "edsbwt_result_sizes", "edsbwt_result_device_ptrs", "edsbwt_result_fetch",
+    "edsbwt_result_free", "edsbwt_last_stats", "edsbwt_set_stats", "edsbwt_write_csv", "edsbwt_read_patterns",
+    "edsbwt_build_from_eds", "edsbwt_build_from_collection", "edsbwt_gather_bench", "edsbwt_free",
+    "edsbwt_strerror", "edsbwt_last_error", "edsbwt_version",
+]
+
+
+class Info(C.Structure):
+    _fields_ = [("n", C.c_uint32), ("n_text", C.c_uint32), ("n_seg", C.c_uint32), ("sigma", C.c_uint32),
+                ("alphabet", C.c_uint8 * 8), ("table_occ", C.c_uint32 * 25), ("seed_k", C.c_uint32),
+                ("locate_mode", C.c_uint32), ("device_bytes", C.c_uint64), ("seed_intervals", C.c_uint64)]
+
+
+class OpenOpts(C.Structure):
+    _fields_ = [("seed_k", C.c_int32), ("locate_mode", C.c_int32), ("verify", C.c_int32), ("build_move", C.c_int32),
+                ("reserved", C.c_int32 * 4)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("I", C.c_uint64), ("S", C.c_uint64), ("E", C.c_uint64), ("L", C.c_uint64), ("O", C.c_uint64),
+                ("steps", C.c_uint64), ("kernel_launches", C.c_uint64), ("lf_intervals", C.c_uint64),
+                ("lf_kernel_ms", C.c_double), ("locate_kernel_ms", C.c_double), ("total_ms", C.c_double),
+                ("frontier_peak", C.c_uint64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class EdsbwtError(RuntimeError):
+    def __init__(self, code, detail):
+        super().__init__("libedsbwt_cuda error %d: %s" % (code, detail))
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    """Load the CUDA library; fail loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("%s is missing: run `python eds-bwt_b200/build.py` (nvcc, sm_100a). "
+                              "There is no CPU fallback." % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        L.edsbwt_strerror.restype = C.c_char_p
+        L.edsbwt_last_error.restype = C.c_char_p
+        L.edsbwt_version.restype = C.c_char_p
+        L.edsbwt_free.argtypes = [C.c_void_p]
+        L.edsbwt_free.restype = None
+        L.edsbwt_index_close.argtypes = [C.c_void_p]
+        L.edsbwt_index_close.restype = None
+        L.edsbwt_result_free.argtypes = [C.c_void_p]
+        L.edsbwt_result_free.restype = None
+        L.edsbwt_index_open_ex.argtypes = [C.c_char_p, C.c_int, C.POINTER(OpenOpts), C.POINTER(C.c_void_p)]
+        L.edsbwt_index_info.argtypes = [C.c_void_p, C.POINTER(Info)]
+        L.edsbwt_search.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
+                                    C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+        L.edsbwt_search_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32,
+                                           C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.edsbwt_result_sizes.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
+        L.edsbwt_result_device_ptrs.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.edsbwt_result_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.edsbwt_last_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+        L.edsbwt_set_stats.argtypes = [C.c_void_p, C.c_int, C.c_uint32]
+        L.edsbwt_write_csv.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_int]
+        L.edsbwt_read_patterns.argtypes = [C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint32)]
+        L.edsbwt_build_from_eds.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+        L.edsbwt_build_from_collection.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_char_p, C.c_int]
+        L.edsbwt_gather_bench.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_double)]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise EdsbwtError(rc, lib().edsbwt_last_error().decode(errors="replace") or lib().edsbwt_strerror(rc).decode())
+
+
+def pack_patterns(patterns):
+    """list of bytes -> (uint8 array, uint64 offsets[npat+1])"""
+    off = np.zeros(len(patterns) + 1, dtype=np.uint64)
+    if len(patterns):
+        off[1:] = np.cumsum([len(p) for p in patterns], dtype=np.uint64)
+    data = np.frombuffer(b"".join(patterns), dtype=np.uint8).copy() if len(patterns) else np.zeros(0, np.uint8)
+    if data.size == 0:
+        data = np.zeros(1, np.uint8)
+    return data, off
+
+
+class Index:
+    """Device-resident EDS-BWT index (edsbwt_index_open_ex)."""
+
+    def __init__(self, base, device=0, seed_k=-1, locate_mode=LOCATE_SA, verify=True, build_move=False):
+        self._h = C.c_void_p()
+        o = OpenOpts(seed_k=seed_k, locate_mode=locate_mode, verify=int(verify), build_move=int(build_move))
+        _check(lib().edsbwt_index_open_ex(os.fsencode(base), device, C.byref(o), C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if self._h:
+            lib().edsbwt_index_close(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self):
+        i = Info()
+        _check(lib().edsbwt_index_info(self._h, C.byref(i)))
+        return i
+
+    def set_stats(self, collect=True, canonical_k=12):
+        _check(lib().edsbwt_set_stats(self._h, int(collect), canonical_k))
+
+    def last_stats(self):
+        s = Stats()
+        _check(lib().edsbwt_last_stats(self._h, C.byref(s)))
+        return s.as_dict()
+
+    def search(self, patterns, locate=True, lf_variant=LF_RANK):
+        """patterns: list of bytes, or (uint8 data, uint64 offsets).  -> (counts uint32[npat], occ structured array)"""
+        data, off = pack_patterns(patterns) if isinstance(patterns, (list, tuple)) and not (
+            len(patterns) == 2 and isinstance(patterns[0], np.ndarray)) else patterns
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.uint64)
+        npat = len(off) - 1
+        counts = np.zeros(max(npat, 1), dtype=np.uint32)
+        occ_p = C.c_void_p()
+        nocc = C.c_uint64(0)
+        _check(lib().edsbwt_search(self._h, data.ctypes.data, off.ctypes.data, npat, int(locate), lf_variant,
+                                   counts.ctypes.data, C.byref(occ_p), C.byref(nocc)))
+        occ = np.zeros(0, dtype=OCC_DTYPE)
+        if locate and nocc.value:
+            buf = (C.c_uint8 * (nocc.value * OCC_DTYPE.itemsize)).from_address(occ_p.value)
+            occ = np.frombuffer(buf, dtype=OCC_DTYPE).copy()
+            lib().edsbwt_free(occ_p)
+        return counts[:npat], occ
+
+    def search_device(self, d_bytes_ptr, d_off_ptr, npat, total_bytes, max_len, locate=True, lf_variant=LF_RANK):
+        """Device-pointer variant; returns a DeviceResult (results stay in HBM)."""
+        r = C.c_void_p()
+        _check(lib().edsbwt_search_device(self._h, C.c_void_p(d_bytes_ptr), C.c_void_p(d_off_ptr), npat, total_bytes,
+                                          max_len, int(locate), lf_variant, C.byref(r)))
+        return DeviceResult(r)
+
+
+class DeviceResult:
+    def __init__(self, h):
+        self._h = h
+        n, o = C.c_uint32(), C.c_uint64()
+        _check(lib().edsbwt_result_sizes(h, C.byref(n), C.byref(o)))
+        self.npat, self.nocc = n.value, o.value
+
+    def device_ptrs(self):
+        c, o = C.c_void_p(), C.c_void_p()
+        _check(lib().edsbwt_result_device_ptrs(self._h, C.byref(c), C.byref(o)))
+        return c.value, o.value
+
+    def fetch(self):
+        counts = np.zeros(max(self.npat, 1), dtype=np.uint32)
+        occ = np.zeros(max(self.nocc, 1), dtype=OCC_DTYPE)
+        _check(lib().edsbwt_result_fetch(self._h, counts.ctypes.data, occ.ctypes.data))
+        return counts[:self.npat], occ[:self.nocc]
+
+    def free(self):
+        if self._h:
+            lib().edsbwt_result_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def occ_rows(occ, pat_base=0):
+    """structured occurrence array -> sorted list of csv tuples (pat+1, str, seg, idx_in_seg, off)."""
+    return sorted(zip((occ["pat"] + pat_base + 1).tolist(), occ["str"].tolist(), occ["seg"].tolist(),
+                      occ["idx_in_seg"].tolist(), occ["off"].tolist()))
+
+
+def write_csv(path, occ, pat_base=0, move=False, append=False):
+    occ = np.ascontiguousarray(occ, dtype=OCC_DTYPE)
+    _check(lib().edsbwt_write_csv(os.fsencode(path), occ.ctypes.data if len(occ) else None, len(occ), pat_base, int(move), int(append)))
+
+
+def read_patterns(path):
+    b, o, n = C.c_void_p(), C.c_void_p(), C.c_uint32()
+    _check(lib().edsbwt_read_patterns(os.fsencode(path), C.byref(b), C.byref(o), C.byref(n)))
+    off = np.frombuffer((C.c_uint64 * (n.value + 1)).from_address(o.value), dtype=np.uint64).copy()
+    total = int(off[-1])
+    data = np.frombuffer((C.c_uint8 * max(total, 1)).from_address(b.value), dtype=np.uint8).copy()[:total]
+    lib().edsbwt_free(b)
+    lib().edsbwt_free(o)
+    return data, off
+
+
+def build_from_eds(eds_path, out_base, device=0):
+    _check(lib().edsbwt_build_from_eds(os.fsencode(eds_path), os.fsencode(out_base), device))
+
+
+def build_from_collection(text, str_off, seg_first, out_base, device=0):
+    text = np.ascontiguousarray(text, dtype=np.uint8)
+    str_off = np.ascontiguousarray(str_off, dtype=np.uint64)
+    seg_first = np.ascontiguousarray(seg_first, dtype=np.uint8)
+    _check(lib().edsbwt_build_from_collection(text.ctypes.data if text.size else None, str_off.ctypes.data, len(seg_first),
+                                              seg_first.ctypes.data, os.fsencode(out_base), device))
+
+
+def gather_bench(device=0, buffer_bytes=4 << 30, n_access=1 << 26, iters=5):
+    g = C.c_double()
+    _check(lib().edsbwt_gather_bench(device, buffer_bytes, n_access, iters, C.byref(g)))
+    return g.value

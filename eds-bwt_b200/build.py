@@ -1,0 +1,58 @@
+"""Builds eds-bwt_b200/libedsbwt_cuda.so and the two CLI executables with nvcc for sm_100a (in-tree)."""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libedsbwt_cuda.so")
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-Xptxas", "-v"]
+LIB_SRCS = ["engine.cu", "api.cu", "gather_bench.cu", "builder.cu", "host_io.cpp"]
+CLIS = {"EDSBWTsearch": "cli_edsbwtsearch.cpp", "MOVE_EDSBWTSearch": "cli_move_edsbwtsearch.cpp"}
+
+
+def _newer(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build(force=False, verbose=False):
+    os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    hdrs = [os.path.join(CSRC, "internal.cuh"), os.path.join(HERE, "..", "include", "edsbwt.h")]
+    objs = []
+    for src in LIB_SRCS:
+        sp = os.path.join(CSRC, src)
+        obj = os.path.join(HERE, "build", src + ".o")
+        objs.append(obj)
+        if force or _newer(obj, [sp] + hdrs):
+            cmd = [NVCC] + ARCH + COMMON + ["-x", "cu", "-c", sp, "-o", obj]
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            log = r.stdout + r.stderr
+            with open(obj + ".log", "w") as f:
+                f.write(log)
+            if r.returncode != 0:
+                sys.stderr.write(log)
+                raise RuntimeError("nvcc failed on " + src)
+            if verbose:
+                print(log)
+    if force or _newer(LIB, objs):
+        cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-lcudart"]
+        subprocess.run(cmd, check=True)
+    for exe, src in CLIS.items():
+        sp = os.path.join(CSRC, src)
+        if not os.path.exists(sp):
+            continue
+        out = os.path.join(HERE, exe)
+        if force or _newer(out, [sp, LIB] + hdrs):
+            cmd = ["g++", "-O2", "-std=c++17", "-Wall", "-o", out, sp, "-I", os.path.join(HERE, "..", "include"),
+                   "-L", HERE, "-ledsbwt_cuda", "-Wl,-rpath,$ORIGIN"]
+            subprocess.run(cmd, check=True)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

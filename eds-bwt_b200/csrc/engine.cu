@@ -1,0 +1,738 @@
+// Device-resident EDS-BWT index + level-synchronous batched search engine (sm_100a).
+//
+// Data-parallel restatement of the reference's per-pattern loop:
+//   frontier F   = all (pattern, [lo,hi]) row intervals of the whole batch, grouped by pattern, global 0-based rows
+//   one step     = lf_step_kernel  : LF_c of every interval + '#' count          (updateIntervals, EDSBWTsearch.cpp:956-1157)
+//                  enum_dollars     : strings whose start row lies in F           (dollars_in_interval, :1265-1281)
+//                  sort + dol_runs  : maximal runs of reachable segments          (link/preceding_dollars_finder, :1212-1307)
+//                  lf_step_kernel   : LF_c of the pile-0 ranges                   (updateIntervals on vectRangeDollarPile, :691)
+//                  compact/merge    : drop empty, merge adjacent                  (MergeAndRemove, :911-953)
+//                  combine          : F <- Dol' ++ F' per pattern                 (:696-700)
+// The first k steps of every pattern come from a seed table (frontiers of all 4^L suffixes, L <= k) that is
+// built with the very same step code run level-synchronously over all keys.
+#include <cub/cub.cuh>
+
+#include <algorithm>
+
+#include "internal.cuh"
+
+namespace edsbwt {
+
+// ===================================================================================================
+// small device helpers
+// ===================================================================================================
+__device__ __forceinline__ uint32_t upper_bound_u32(const uint32_t* __restrict__ a, uint32_t n, uint32_t v) {
+    uint32_t lo = 0, hi = n;                       // first index with a[idx] > v
+    while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if (__ldg(a + mid) <= v) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+__device__ __forceinline__ uint32_t lower_bound_u32(const uint32_t* __restrict__ a, uint32_t n, uint32_t v) {
+    uint32_t lo = 0, hi = n;                       // first index with a[idx] >= v
+    while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if (__ldg(a + mid) < v) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+__device__ __forceinline__ void warp_add(unsigned long long* dst, uint32_t v) {
+    // warp-aggregated statistics counter
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(dst, (unsigned long long)v);
+}
+
+static inline unsigned grid_for(size_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
+
+// ===================================================================================================
+// K1: Occ structure from the raw eBWT bytes  (replaces computeVectorOcc, EDSBWTsearch.cpp:1338-1442,
+//     and the rrr rank supports of recoverInfo, :1586-1604)
+// ===================================================================================================
+struct Lut { uint8_t code[256]; };     // 0..3 letter code, 4 = end-marker, 255 = not in the alphabet
+
+__global__ void occ_pack_kernel(const uint8_t* __restrict__ bytes, uint32_t n, Lut lut, uint4* __restrict__ occ,
+                                uint4* __restrict__ blkcnt, uint32_t ngroups, unsigned int* bad) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;          // one thread per 32-row group = one uint4 lane
+    uint32_t p0 = 0, p1 = 0, mk = 0, c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    if (g < ngroups) {
+        uint32_t base = g * 32u;
+        #pragma unroll 4
+        for (uint32_t b = 0; b < 32; ++b) {
+            uint32_t r = base + b;
+            if (r < n) {
+                uint8_t c = lut.code[bytes[r]];
+                if (c == 255) { atomicExch(bad, r + 1); c = 4; }
+                if (c == 4) mk |= 1u << b;
+                else { p0 |= (uint32_t)(c & 1) << b; p1 |= (uint32_t)((c >> 1) & 1) << b; c0 += c == 0; c1 += c == 1; c2 += c == 2; c3 += c == 3; }
+            }
+        }
+        occ[g] = make_uint4(0u, p0, p1, mk);
+    }
+    // sum the four groups of a block (consecutive lanes)
+    c0 += __shfl_xor_sync(0xffffffffu, c0, 1); c0 += __shfl_xor_sync(0xffffffffu, c0, 2);
+    c1 += __shfl_xor_sync(0xffffffffu, c1, 1); c1 += __shfl_xor_sync(0xffffffffu, c1, 2);
+    c2 += __shfl_xor_sync(0xffffffffu, c2, 1); c2 += __shfl_xor_sync(0xffffffffu, c2, 2);
+    c3 += __shfl_xor_sync(0xffffffffu, c3, 1); c3 += __shfl_xor_sync(0xffffffffu, c3, 2);
+    if (g < ngroups && (g & 3) == 0) blkcnt[g >> 2] = make_uint4(c0, c1, c2, c3);
+}
+struct AddU4 { __device__ __forceinline__ uint4 operator()(const uint4& a, const uint4& b) const { return make_uint4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); } };
+__global__ void occ_counts_kernel(uint4* __restrict__ occ, const uint4* __restrict__ prefix, uint32_t ngroups) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= ngroups) return;
+    uint4 p = prefix[g >> 2];
+    uint32_t j = g & 3;
+    occ[g].x = j == 0 ? p.x : j == 1 ? p.y : j == 2 ? p.z : p.w;
+}
+
+// ===================================================================================================
+// SA table: row -> (string, offset), by walking every string backwards from its end-marker row
+// (the inverse of the reference's locate rounds, findMultipleDollarsBackward :349-603)
+// ===================================================================================================
+__global__ void sa_walk_kernel(IndexView ix, uint32_t* __restrict__ sa_str, uint32_t* __restrict__ sa_dist, uint32_t* __restrict__ slen) {
+    uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= ix.n_text) return;
+    uint32_t row = w, d = 0;                     // pile-0 row w is the suffix "$_w"
+    for (;;) {
+        uint32_t s = occ_symbol(ix.occ, row);
+        if (s == 0) break;
+        row = ix.Cl[s - 1] + occ_rank1(ix.occ, row, (int)s - 1);
+        ++d;
+        sa_str[row] = w; sa_dist[row] = d;
+    }
+    slen[w] = d;
+}
+__global__ void sa_offset_kernel(uint32_t n_text, uint32_t n, const uint32_t* __restrict__ sa_str, uint32_t* __restrict__ sa_off, const uint32_t* __restrict__ slen) {
+    uint32_t row = n_text + blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n) return;
+    sa_off[row] = slen[sa_str[row]] - sa_off[row];
+}
+
+// ===================================================================================================
+// patterns
+// ===================================================================================================
+struct PatView {
+    const uint64_t* pack;    // [npat * words] 2-bit codes, char i of pattern q at bits 2*(i%32) of pack[q*words + i/32]
+    const uint32_t* len;     // 0 for patterns that cannot match (bad character / empty)
+    uint32_t words, npat, k; // k = seed depth used for this batch
+};
+__global__ void encode_patterns_kernel(const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ off, uint32_t npat, Lut lut,
+                                       uint32_t words, uint64_t* __restrict__ pack, uint32_t* __restrict__ len) {
+    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= npat) return;
+    uint64_t a = off[q], b = off[q + 1];
+    uint32_t m = (uint32_t)(b - a);
+    bool ok = m > 0;
+    uint64_t wv = 0;
+    for (uint32_t i = 0; i < m; ++i) {
+        uint8_t c = lut.code[bytes[a + i]];
+        if (c > 3) { ok = false; c = 0; }
+        wv |= (uint64_t)c << (2 * (i & 31));
+        if ((i & 31) == 31 || i + 1 == m) { pack[(size_t)q * words + (i >> 5)] = wv; wv = 0; }
+    }
+    len[q] = ok ? m : 0;
+}
+__device__ __forceinline__ uint32_t pat_char(const PatView& pv, uint32_t q, uint32_t idx) {
+    return (uint32_t)(__ldg(pv.pack + (size_t)q * pv.words + (idx >> 5)) >> (2 * (idx & 31))) & 3u;
+}
+
+// ===================================================================================================
+// seed table
+// ===================================================================================================
+struct SeedView { const uint32_t* off[17]; const uint32_t* lo[17]; const uint32_t* hi[17]; };
+
+// number of seed intervals of each pattern + where they start inside the level
+__global__ void seed_count_kernel(PatView pv, SeedView sv, uint32_t* __restrict__ cnt, uint32_t* __restrict__ src) {
+    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= pv.npat) return;
+    uint32_t m = pv.len[q];
+    if (m == 0) { cnt[q] = 0; src[q] = 0; return; }
+    uint32_t L = m < pv.k ? m : pv.k;
+    uint32_t key = 0;
+    for (uint32_t i = 0; i < L; ++i) key |= pat_char(pv, q, m - L + i) << (2 * i);
+    uint32_t a = __ldg(sv.off[L] + key), b = __ldg(sv.off[L] + key + 1);
+    cnt[q] = b - a; src[q] = a;
+}
+__global__ void seed_scatter_kernel(PatView pv, SeedView sv, const uint32_t* __restrict__ base, const uint32_t* __restrict__ src,
+                                    uint32_t total, uint32_t* __restrict__ fpat, uint32_t* __restrict__ flo, uint32_t* __restrict__ fhi) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= total) return;
+    uint32_t q = upper_bound_u32(base, pv.npat + 1, t) - 1;      // base = exclusive scan of cnt (npat+1 entries)
+    uint32_t m = pv.len[q];
+    uint32_t L = m < pv.k ? m : pv.k;
+    uint32_t j = src[q] + (t - base[q]);
+    fpat[t] = q; flo[t] = __ldg(sv.lo[L] + j); fhi[t] = __ldg(sv.hi[L] + j);
+}
+// level L -> the 4 children of every key, grouped by child key (4*key + c)
+__global__ void seed_expand_kernel(const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi,
+                                   const uint32_t* __restrict__ off, uint32_t nF, uint32_t* __restrict__ opat, uint32_t* __restrict__ olo, uint32_t* __restrict__ ohi) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nF) return;
+    uint32_t key = pat[i], a = off[key], cnt = off[key + 1] - a, r = i - a, l = lo[i], h = hi[i];
+    #pragma unroll
+    for (uint32_t c = 0; c < 4; ++c) { uint32_t d = 4 * a + c * cnt + r; opat[d] = 4 * key + c; olo[d] = l; ohi[d] = h; }
+}
+__global__ void level_keys_kernel(const uint32_t* __restrict__ off, uint32_t nkeys, uint32_t nF, uint32_t* __restrict__ keyof) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nF) return;
+    keyof[i] = upper_bound_u32(off, nkeys + 1, i) - 1;
+}
+__global__ void key_offsets_kernel(const uint32_t* __restrict__ pat, uint32_t nF, uint32_t nkeys, uint32_t* __restrict__ off) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k > nkeys) return;
+    off[k] = k == nkeys ? nF : lower_bound_u32(pat, nF, k);
+}
+
+// ===================================================================================================
+// the LF step (hot kernel)
+// ===================================================================================================
+// One 4-lane group per interval: each lane issues ONE 128-bit load per Occ block (64 B block = 4 coalesced
+// lanes), ranks come from popcounts + two xor-shuffles.  When both interval ends fall into the same block
+// (the common case after the seed phase) the block is fetched once.
+//   KEYMODE   : seed-table construction, "pattern" id is the child key, its character is key & 3
+//   otherwise : the character comes from the packed pattern; finished patterns pass through unchanged
+template <bool KEYMODE>
+__global__ void __launch_bounds__(256)
+lf_step_kernel(IndexView ix, PatView pv, uint32_t step, const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo,
+               const uint32_t* __restrict__ hi, uint32_t nF, uint32_t* __restrict__ olo, uint32_t* __restrict__ ohi,
+               uint32_t* __restrict__ dcnt, uint32_t* __restrict__ dstart, uint32_t* __restrict__ keep,
+               StatsDev* __restrict__ st, uint32_t kc, int is_dol) {
+    uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t i = gid >> 2; int lane4 = gid & 3;
+    bool act = i < nF;
+    uint32_t ii = act ? i : 0;
+    uint32_t q = __ldg(pat + ii), a = __ldg(lo + ii), b = __ldg(hi + ii) + 1;      // [a, b) half-open
+    int c = 0; bool pass = false; uint32_t L = 0, m = 0;
+    if (KEYMODE) c = q & 3;
+    else {
+        m = __ldg(pv.len + q);
+        L = (m < pv.k ? m : pv.k) + step;
+        if (L >= m) pass = true; else c = (int)pat_char(pv, q, m - L - 1);
+    }
+    bool doload = act && !pass;
+    uint32_t blk_a = a >> 7, blk_b = b >> 7;
+    uint4 va = make_uint4(0, 0, 0, 0), vb;
+    if (doload) va = occ_load(ix.occ, blk_a, lane4);
+    vb = va;
+    if (doload && blk_b != blk_a) vb = occ_load(ix.occ, blk_b, lane4);
+    uint32_t rca, rda, rcb, rdb;
+    rank4_from(va, a, c, lane4, rca, rda);
+    rank4_from(vb, b, c, lane4, rcb, rdb);
+    uint32_t nlo, nhi, nd = 0;
+    bool kept;
+    if (pass) { nlo = a; nhi = b - 1; kept = true; }
+    else { nlo = ix.Cl[c] + rca; nhi = ix.Cl[c] + rcb - 1; kept = rcb > rca; nd = rdb - rda; }
+    if (act && lane4 == 0) {
+        olo[i] = nlo; ohi[i] = nhi; keep[i] = kept ? 1u : 0u;
+        if (dcnt) { dcnt[i] = nd; dstart[i] = rda; }
+    }
+    if (st) {
+        bool mine = act && lane4 == 0 && !pass;
+        bool beyond = KEYMODE ? false : (L >= kc);
+        warp_add(&st->lf_intervals, mine ? 1u : 0u);
+        warp_add(&st->S, (mine && beyond) ? 1u : 0u);
+        warp_add(&st->E, (mine && beyond) ? nd : 0u);
+        if (!KEYMODE && !is_dol) {
+            uint32_t mk = m < kc ? m : kc;           // the canonical seed entry is the frontier at suffix length min(m, kc)
+            uint32_t Lv = (m < pv.k ? m : pv.k) + step;
+            warp_add(&st->I, (act && lane4 == 0 && m > 0 && Lv == mk) ? 1u : 0u);
+        }
+    }
+}
+// I-counter for the frontier left after the last step
+__global__ void count_I_kernel(PatView pv, uint32_t step, const uint32_t* __restrict__ pat, uint32_t nF, StatsDev* st, uint32_t kc) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool hit = false;
+    if (i < nF) { uint32_t m = pv.len[pat[i]]; hit = m > 0 && ((m < pv.k ? m : pv.k) + step == (m < kc ? m : kc)); }
+    warp_add(&st->I, hit ? 1u : 0u);
+}
+
+// ---- compaction + MergeAndRemove -----------------------------------------------------------------
+__global__ void compact_kernel(const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi,
+                               const uint32_t* __restrict__ keep, const uint32_t* __restrict__ pos, uint32_t n,
+                               uint32_t* __restrict__ opat, uint32_t* __restrict__ olo, uint32_t* __restrict__ ohi) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || !keep[i]) return;
+    uint32_t d = pos[i];
+    opat[d] = pat[i]; olo[d] = lo[i]; ohi[d] = hi[i];
+}
+// head[i] = 1 unless interval i continues interval i-1 (same pattern, still active, lo == prev.hi + 1)
+template <bool KEYMODE>
+__global__ void head_flags_kernel(PatView pv, uint32_t step, const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo,
+                                  const uint32_t* __restrict__ hi, const uint32_t* __restrict__ n_ptr, uint32_t nmax, uint32_t* __restrict__ head) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nmax) return;
+    uint32_t n = *n_ptr;
+    if (i >= n) { head[i] = 0; return; }
+    uint32_t h = 1;
+    if (i > 0 && pat[i - 1] == pat[i] && lo[i] == hi[i - 1] + 1) {
+        bool pass = false;
+        if (!KEYMODE) { uint32_t m = pv.len[pat[i]]; pass = (m < pv.k ? m : pv.k) + step >= m; }
+        if (!pass) h = 0;
+    }
+    head[i] = h;
+}
+__global__ void merge_kernel(const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi,
+                             const uint32_t* __restrict__ head, const uint32_t* __restrict__ pos, const uint32_t* __restrict__ n_ptr, uint32_t nmax,
+                             uint32_t* __restrict__ opat, uint32_t* __restrict__ olo, uint32_t* __restrict__ ohi) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t n = *n_ptr;
+    if (i >= nmax || i >= n) return;
+    uint32_t run = pos[i] + head[i] - 1;                 // pos = exclusive scan of head
+    if (head[i]) { opat[run] = pat[i]; olo[run] = lo[i]; }
+    if (i + 1 == n || head[i + 1]) ohi[run] = hi[i];
+}
+
+// ---- link -------------------------------------------------------------------------------------------
+__global__ void enum_dollars_kernel(IndexView ix, const uint32_t* __restrict__ pat, const uint32_t* __restrict__ dofs,
+                                    const uint32_t* __restrict__ dstart, uint32_t nF, uint32_t D, uint64_t* __restrict__ keys,
+                                    unsigned int* __restrict__ nvalid) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    bool valid = false;
+    if (t < D) {
+        uint32_t i = upper_bound_u32(dofs, nF + 1, t) - 1;
+        uint32_t w = __ldg(ix.eof_flat + dstart[i] + (t - dofs[i]));
+        uint64_t key = ~0ull;
+        if (w > ix.fsi) { key = ((uint64_t)pat[i] << 32) | (uint64_t)(__ldg(ix.str_seg + w) - 1); valid = true; }
+        keys[t] = key;
+    }
+    unsigned bal = __ballot_sync(0xffffffffu, valid);
+    if ((threadIdx.x & 31) == 0 && bal) atomicAdd(nvalid, (unsigned)__popc(bal));
+}
+// sorted (pattern, segment) keys -> heads of maximal runs of reachable segments (closure through segments
+// holding the empty string is the precomputed seg_low[])
+__global__ void dol_heads_kernel(IndexView ix, const uint64_t* __restrict__ keys, uint32_t Dv, uint32_t* __restrict__ head) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= Dv) return;
+    uint64_t k = keys[t];
+    uint32_t h = 1;
+    if (t > 0) {
+        uint64_t p = keys[t - 1];
+        if ((uint32_t)(p >> 32) == (uint32_t)(k >> 32) && __ldg(ix.seg_low + (uint32_t)k) <= (uint32_t)p + 1) h = 0;
+    }
+    head[t] = h;
+}
+__global__ void dol_build_kernel(IndexView ix, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ head, const uint32_t* __restrict__ pos,
+                                 uint32_t Dv, uint32_t* __restrict__ dpat, uint32_t* __restrict__ dlo, uint32_t* __restrict__ dhi) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= Dv) return;
+    uint64_t k = keys[t];
+    uint32_t s = (uint32_t)k, run = pos[t] + head[t] - 1;
+    if (head[t]) { dpat[run] = (uint32_t)(k >> 32); dlo[run] = __ldg(ix.seg_first + __ldg(ix.seg_low + s)); }
+    if (t + 1 == Dv || head[t + 1]) dhi[run] = __ldg(ix.seg_first + s + 1) - 1;
+}
+// F <- Dol' ++ F' per pattern (both inputs sorted by pattern)
+__global__ void combine_kernel(const uint32_t* __restrict__ fpat, const uint32_t* __restrict__ flo, const uint32_t* __restrict__ fhi, uint32_t nf,
+                               const uint32_t* __restrict__ dpat, const uint32_t* __restrict__ dlo, const uint32_t* __restrict__ dhi, uint32_t nd,
+                               uint32_t* __restrict__ opat, uint32_t* __restrict__ olo, uint32_t* __restrict__ ohi) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < nf) {
+        uint32_t q = fpat[t], d = t + upper_bound_u32(dpat, nd, q);
+        opat[d] = q; olo[d] = flo[t]; ohi[d] = fhi[t];
+    } else if (t < nf + nd) {
+        uint32_t j = t - nf, q = dpat[j], d = j + lower_bound_u32(fpat, nf, q);
+        opat[d] = q; olo[d] = dlo[j]; ohi[d] = dhi[j];
+    }
+}
+
+// ---- results ----------------------------------------------------------------------------------------
+__global__ void interval_len_kernel(const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi, uint32_t nF,
+                                    uint32_t* __restrict__ len, uint32_t* __restrict__ counts) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nF) return;
+    uint32_t l = hi[i] - lo[i] + 1;
+    len[i] = l;
+    atomicAdd(counts + pat[i], l);                       // "Found N", EDSBWTsearch.cpp:739-746
+}
+// one thread per occurrence row: (string, offset) by table lookup or by LF-walk, then segment / index in segment
+// (indices_of_dollars_in_interval, EDSBWTsearch.cpp:1310-1332)
+template <bool WALK>
+__global__ void locate_kernel(IndexView ix, const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo, const uint32_t* __restrict__ rofs,
+                              uint32_t nF, uint64_t nocc, edsbwt_occ* __restrict__ out, StatsDev* __restrict__ st) {
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t steps = 0;
+    if (t < nocc) {
+        uint32_t i = upper_bound_u32(rofs, nF + 1, (uint32_t)t) - 1;
+        uint32_t row = lo[i] + ((uint32_t)t - rofs[i]);
+        uint32_t w, r;
+        if (WALK) {
+            r = 0;
+            for (;;) {
+                uint32_t s = occ_symbol(ix.occ, row);
+                if (s == 0) break;
+                row = ix.Cl[s - 1] + occ_rank1(ix.occ, row, (int)s - 1);
+                ++r;
+            }
+            w = __ldg(ix.eof_flat + occ_rank_eof(ix.occ, row));
+        } else { w = __ldg(ix.sa_str + row); r = __ldg(ix.sa_off + row); }
+        uint32_t seg = __ldg(ix.str_seg + w);
+        edsbwt_occ o; o.pat = pat[i]; o.str = w; o.seg = seg; o.idx_in_seg = w - __ldg(ix.seg_first + seg); o.off = r;
+        out[t] = o;
+        steps = r + 1;
+    }
+    if (st) { warp_add(&st->L, steps); warp_add(&st->O, steps ? 1u : 0u); }
+}
+
+// ===================================================================================================
+// host side
+// ===================================================================================================
+struct Tri {
+    DevBuf<uint32_t> pat, lo, hi;
+    void ensure(size_t n) { pat.ensure(n); lo.ensure(n); hi.ensure(n); }
+    void swap(Tri& o) { std::swap(pat.p, o.pat.p); std::swap(lo.p, o.lo.p); std::swap(hi.p, o.hi.p);
+                        std::swap(pat.cap, o.pat.cap); std::swap(lo.cap, o.lo.cap); std::swap(hi.cap, o.hi.cap); }
+};
+
+struct Workspace {
+    Tri cur, raw, cmp, mrg, dol, dolraw, nxt;
+    DevBuf<uint32_t> keep, pos, dcnt, dstart, dofs, head, len, cnt, src, base, plen;
+    DevBuf<uint64_t> keys, keys2, ppack;
+    DevBuf<uint8_t> cubtmp;
+    DevBuf<unsigned int> scalars;        // [0] nvalid
+    StatsDev* d_stats = nullptr;
+    uint32_t* h_pin = nullptr;           // pinned read-back area
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr;
+    uint64_t launches = 0;
+    double lf_ms = 0;
+    ~Workspace() { if (d_stats) cudaFree(d_stats); if (h_pin) cudaFreeHost(h_pin); if (ev0) cudaEventDestroy(ev0); if (ev1) cudaEventDestroy(ev1);
+                   if (evk0) cudaEventDestroy(evk0); if (evk1) cudaEventDestroy(evk1); }
+};
+
+Index::~Index() {
+    for (SeedLevel* s : seed) delete s;
+    delete ws;
+    if (stream) cudaStreamDestroy(stream);
+}
+uint64_t Index::device_bytes() const {
+    uint64_t b = occ.bytes() + eof_flat.bytes() + str_seg.bytes() + seg_first.bytes() + seg_low.bytes() + sa_str.bytes() + sa_off.bytes();
+    for (SeedLevel* s : seed) if (s) b += s->off.bytes() + s->lo.bytes() + s->hi.bytes();
+    return b;
+}
+
+static void exclusive_sum(Workspace& ws, const uint32_t* in, uint32_t* out, size_t n, cudaStream_t s) {
+    size_t tmp = 0;
+    CUDA_OK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, in, out, (int)n, s));
+    ws.cubtmp.ensure(tmp);
+    CUDA_OK(cub::DeviceScan::ExclusiveSum(ws.cubtmp.p, tmp, in, out, (int)n, s));
+    ws.launches += 2;
+}
+static uint32_t read_u32(Workspace& ws, const uint32_t* d, cudaStream_t s) {
+    CUDA_OK(cudaMemcpyAsync(ws.h_pin, d, 4, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    return ws.h_pin[0];
+}
+static Lut make_lut(const HostIndex& h) {
+    Lut l; memset(l.code, 255, sizeof l.code);
+    l.code[h.alphabet[0]] = 4;
+    for (uint32_t a = 1; a < h.sigma; ++a) l.code[h.alphabet[a]] = (uint8_t)(a - 1);
+    return l;
+}
+
+// drop empty intervals and merge adjacent ones: raw(+keep) -> out ; returns the new count
+template <bool KEYMODE>
+static uint32_t compact_and_merge(Index& ix, Workspace& ws, PatView pv, uint32_t step, const uint32_t* pat, Tri& raw, uint32_t n, Tri& cmp, Tri& out) {
+    cudaStream_t s = ix.stream;
+    if (n == 0) return 0;
+    ws.pos.ensure(n + 1); ws.head.ensure(n + 1); cmp.ensure(n); out.ensure(n);
+    // keep[n] = 0 so that pos[n] = number kept
+    CUDA_OK(cudaMemsetAsync(ws.keep.p + n, 0, 4, s));
+    exclusive_sum(ws, ws.keep.p, ws.pos.p, n + 1, s);
+    compact_kernel<<<grid_for(n, 256), 256, 0, s>>>(pat, raw.lo.p, raw.hi.p, ws.keep.p, ws.pos.p, n, cmp.pat.p, cmp.lo.p, cmp.hi.p);
+    // head flags on the compacted list (count read on the device: no host round trip)
+    const uint32_t* d_nkeep = ws.pos.p + n;
+    uint32_t* d_nk_copy = ws.scalars.p + 1;        // pos is overwritten by the next scan: park the count
+    CUDA_OK(cudaMemcpyAsync(d_nk_copy, d_nkeep, 4, cudaMemcpyDeviceToDevice, s));
+    head_flags_kernel<KEYMODE><<<grid_for(n + 1, 256), 256, 0, s>>>(pv, step, cmp.pat.p, cmp.lo.p, cmp.hi.p, d_nk_copy, n + 1, ws.head.p);
+    exclusive_sum(ws, ws.head.p, ws.pos.p, n + 1, s);
+    merge_kernel<<<grid_for(n, 256), 256, 0, s>>>(cmp.pat.p, cmp.lo.p, cmp.hi.p, ws.head.p, ws.pos.p, d_nk_copy, n, out.pat.p, out.lo.p, out.hi.p);
+    ws.launches += 4;
+    return read_u32(ws, ws.pos.p + n, s);
+}
+
+// One level-synchronous backward step over the whole frontier ws.cur[0..nF) -> ws.cur ; returns new nF
+template <bool KEYMODE>
+static uint32_t engine_step(Index& ix, Workspace& ws, PatView pv, uint32_t step, uint32_t nF, StatsDev* st, uint32_t kc, bool time_lf) {
+    cudaStream_t s = ix.stream;
+    if (nF == 0) return 0;
+    ws.raw.ensure(nF); ws.keep.ensure(nF + 1); ws.dcnt.ensure(nF + 1); ws.dstart.ensure(nF); ws.dofs.ensure(nF + 2);
+    if (time_lf) CUDA_OK(cudaEventRecord(ws.evk0, s));
+    lf_step_kernel<KEYMODE><<<grid_for((size_t)nF * 4, 256), 256, 0, s>>>(ix.view, pv, step, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p, nF,
+        ws.raw.lo.p, ws.raw.hi.p, ws.dcnt.p, ws.dstart.p, ws.keep.p, st, kc, 0);
+    if (time_lf) { CUDA_OK(cudaEventRecord(ws.evk1, s)); }
+    ws.launches += 1;
+    // end-markers inside the frontier -> link
+    CUDA_OK(cudaMemsetAsync(ws.dcnt.p + nF, 0, 4, s));
+    exclusive_sum(ws, ws.dcnt.p, ws.dofs.p, nF + 1, s);
+    uint32_t D = read_u32(ws, ws.dofs.p + nF, s);
+    if (time_lf) { float ms = 0; CUDA_OK(cudaEventElapsedTime(&ms, ws.evk0, ws.evk1)); ws.lf_ms += ms; }
+    uint32_t nDol = 0;
+    if (D > 0) {
+        ws.keys.ensure(D); ws.keys2.ensure(D);
+        CUDA_OK(cudaMemsetAsync(ws.scalars.p, 0, 4, s));
+        enum_dollars_kernel<<<grid_for(D, 256), 256, 0, s>>>(ix.view, ws.cur.pat.p, ws.dofs.p, ws.dstart.p, nF, D, ws.keys.p, ws.scalars.p);
+        ws.launches += 1;
+        uint32_t Dv = read_u32(ws, ws.scalars.p, s);
+        if (Dv > 0) {
+            size_t tmp = 0;
+            int end_bit = 64;
+            CUDA_OK(cub::DeviceRadixSort::SortKeys(nullptr, tmp, ws.keys.p, ws.keys2.p, (int)D, 0, end_bit, s));
+            ws.cubtmp.ensure(tmp);
+            CUDA_OK(cub::DeviceRadixSort::SortKeys(ws.cubtmp.p, tmp, ws.keys.p, ws.keys2.p, (int)D, 0, end_bit, s));
+            ws.launches += 4;
+            ws.head.ensure(Dv + 1); ws.pos.ensure(Dv + 1); ws.dol.ensure(Dv);
+            dol_heads_kernel<<<grid_for(Dv, 256), 256, 0, s>>>(ix.view, ws.keys2.p, Dv, ws.head.p);
+            CUDA_OK(cudaMemsetAsync(ws.head.p + Dv, 0, 4, s));
+            exclusive_sum(ws, ws.head.p, ws.pos.p, Dv + 1, s);
+            dol_build_kernel<<<grid_for(Dv, 256), 256, 0, s>>>(ix.view, ws.keys2.p, ws.head.p, ws.pos.p, Dv, ws.dol.pat.p, ws.dol.lo.p, ws.dol.hi.p);
+            ws.launches += 2;
+            nDol = read_u32(ws, ws.pos.p + Dv, s);
+        }
+    }
+    // F' : drop empty, merge adjacent
+    uint32_t nF2 = compact_and_merge<KEYMODE>(ix, ws, pv, step, ws.cur.pat.p, ws.raw, nF, ws.cmp, ws.mrg);
+    if (nDol == 0) { ws.cur.swap(ws.mrg); return nF2; }
+    // Dol' : LF of the pile-0 ranges, then the same clean-up
+    ws.dolraw.ensure(nDol); ws.keep.ensure(nDol + 1);
+    if (time_lf) CUDA_OK(cudaEventRecord(ws.evk0, s));
+    lf_step_kernel<KEYMODE><<<grid_for((size_t)nDol * 4, 256), 256, 0, s>>>(ix.view, pv, step, ws.dol.pat.p, ws.dol.lo.p, ws.dol.hi.p, nDol,
+        ws.dolraw.lo.p, ws.dolraw.hi.p, ws.dcnt.p, ws.dstart.p, ws.keep.p, st, kc, 1);
+    if (time_lf) CUDA_OK(cudaEventRecord(ws.evk1, s));
+    ws.launches += 1;
+    Tri& dcmp = ws.cmp;         // cmp is free again (mrg holds F'')
+    uint32_t nDol2 = compact_and_merge<KEYMODE>(ix, ws, pv, step, ws.dol.pat.p, ws.dolraw, nDol, dcmp, ws.nxt);
+    if (time_lf) { float ms = 0; CUDA_OK(cudaEventElapsedTime(&ms, ws.evk0, ws.evk1)); ws.lf_ms += ms; }
+    // ws.nxt = Dol'' ; ws.mrg = F'' ; combine into cur
+    uint32_t total = nF2 + nDol2;
+    if (nDol2 == 0) { ws.cur.swap(ws.mrg); return nF2; }
+    ws.cur.ensure(total);
+    combine_kernel<<<grid_for(total, 256), 256, 0, s>>>(ws.mrg.pat.p, ws.mrg.lo.p, ws.mrg.hi.p, nF2, ws.nxt.pat.p, ws.nxt.lo.p, ws.nxt.hi.p, nDol2,
+                                                       ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p);
+    ws.launches += 1;
+    return total;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// index build on the device
+// ---------------------------------------------------------------------------------------------------
+static void build_seed_table(Index& ix, uint32_t k) {
+    Workspace& ws = *ix.ws;
+    cudaStream_t s = ix.stream;
+    ix.seed.assign(k + 1, nullptr);
+    // level 1: the piles
+    {
+        std::vector<uint32_t> off(5, 0), lo, hi;
+        for (uint32_t c = 0; c < 4; ++c) {
+            off[c] = (uint32_t)lo.size();
+            if (c < ix.view.nletters && ix.view.Cl[c + 1] > ix.view.Cl[c]) { lo.push_back(ix.view.Cl[c]); hi.push_back(ix.view.Cl[c + 1] - 1); }
+        }
+        off[4] = (uint32_t)lo.size();
+        SeedLevel* L1 = new SeedLevel; ix.seed[1] = L1;
+        L1->off.ensure(5); L1->lo.ensure(lo.size() + 1); L1->hi.ensure(lo.size() + 1); L1->n_iv = lo.size();
+        CUDA_OK(cudaMemcpyAsync(L1->off.p, off.data(), 20, cudaMemcpyHostToDevice, s));
+        if (!lo.empty()) { CUDA_OK(cudaMemcpyAsync(L1->lo.p, lo.data(), lo.size() * 4, cudaMemcpyHostToDevice, s));
+                           CUDA_OK(cudaMemcpyAsync(L1->hi.p, hi.data(), hi.size() * 4, cudaMemcpyHostToDevice, s)); }
+        CUDA_OK(cudaStreamSynchronize(s));
+        ix.seed_intervals = lo.size();
+    }
+    PatView pv{}; pv.k = 0;
+    for (uint32_t L = 1; L < k; ++L) {
+        SeedLevel* cur = ix.seed[L];
+        uint32_t nkeys = 1u << (2 * L), nF = (uint32_t)cur->n_iv;
+        size_t nE = (size_t)nF * 4;
+        if (nE > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "seed level %u too large", L + 1);
+        ws.cur.ensure(nE ? nE : 1); ws.nxt.ensure(nF ? nF : 1);
+        // pat array of the level = key of every interval (recovered from off)
+        uint32_t newF = 0;
+        if (nF) {
+            // key of interval i = upper_bound(off, i) - 1
+            ws.src.ensure(nF);
+            level_keys_kernel<<<grid_for(nF, 256), 256, 0, s>>>(cur->off.p, nkeys, nF, ws.src.p);
+            seed_expand_kernel<<<grid_for(nF, 256), 256, 0, s>>>(ws.src.p, cur->lo.p, cur->hi.p, cur->off.p, nF, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p);
+            ws.launches += 2;
+            newF = engine_step<true>(ix, ws, pv, 0, (uint32_t)nE, nullptr, 0, false);
+        }
+        SeedLevel* nx = new SeedLevel; ix.seed[L + 1] = nx;
+        uint32_t nk2 = nkeys * 4;
+        nx->off.ensure((size_t)nk2 + 1); nx->lo.ensure(newF + 1); nx->hi.ensure(newF + 1); nx->n_iv = newF;
+        if (newF) {
+            CUDA_OK(cudaMemcpyAsync(nx->lo.p, ws.cur.lo.p, (size_t)newF * 4, cudaMemcpyDeviceToDevice, s));
+            CUDA_OK(cudaMemcpyAsync(nx->hi.p, ws.cur.hi.p, (size_t)newF * 4, cudaMemcpyDeviceToDevice, s));
+        }
+        key_offsets_kernel<<<grid_for((size_t)nk2 + 1, 256), 256, 0, s>>>(ws.cur.pat.p, newF, nk2, nx->off.p);
+        CUDA_OK(cudaStreamSynchronize(s));
+        ix.seed_intervals += newF;
+    }
+    CUDA_OK(cudaGetLastError());
+}
+void build_device_index(Index& ix, const edsbwt_open_opts& o) {
+    HostIndex& h = ix.host;
+    CUDA_OK(cudaSetDevice(ix.device));
+    CUDA_OK(cudaStreamCreateWithFlags(&ix.stream, cudaStreamNonBlocking));
+    cudaStream_t s = ix.stream;
+    ix.ws = new Workspace;
+    Workspace& ws = *ix.ws;
+    CUDA_OK(cudaMalloc(&ws.d_stats, sizeof(StatsDev)));
+    CUDA_OK(cudaMallocHost(&ws.h_pin, 256));
+    CUDA_OK(cudaEventCreate(&ws.ev0)); CUDA_OK(cudaEventCreate(&ws.ev1)); CUDA_OK(cudaEventCreate(&ws.evk0)); CUDA_OK(cudaEventCreate(&ws.evk1));
+    ws.scalars.ensure(16);
+
+    IndexView& v = ix.view;
+    v.n = h.n; v.n_text = h.n_text; v.n_seg = h.n_seg; v.nletters = h.sigma - 1;
+    for (uint32_t c = 0; c < 5; ++c) v.Cl[c] = c < h.sigma - 1 ? h.pile_start[c + 1] : h.n;
+
+    // ---- K1: Occ blocks
+    uint32_t nblk = h.n / OCC_ROWS + 1, ngroups = nblk * 4;
+    ix.occ.ensure(ngroups);
+    {
+        DevBuf<uint8_t> d_bytes; d_bytes.ensure((size_t)h.n + 64);
+        DevBuf<uint4> blkcnt, prefix; blkcnt.ensure(nblk); prefix.ensure(nblk);
+        DevBuf<unsigned int> bad; bad.ensure(1);
+        CUDA_OK(cudaMemcpyAsync(d_bytes.p, h.ebwt.data(), h.n, cudaMemcpyHostToDevice, s));
+        CUDA_OK(cudaMemsetAsync(bad.p, 0, 4, s));
+        Lut lut = make_lut(h);
+        occ_pack_kernel<<<grid_for(ngroups, 256), 256, 0, s>>>(d_bytes.p, h.n, lut, ix.occ.p, blkcnt.p, ngroups, bad.p);
+        size_t tmp = 0;
+        CUDA_OK(cub::DeviceScan::ExclusiveScan(nullptr, tmp, blkcnt.p, prefix.p, AddU4(), make_uint4(0, 0, 0, 0), (int)nblk, s));
+        ws.cubtmp.ensure(tmp);
+        CUDA_OK(cub::DeviceScan::ExclusiveScan(ws.cubtmp.p, tmp, blkcnt.p, prefix.p, AddU4(), make_uint4(0, 0, 0, 0), (int)nblk, s));
+        occ_counts_kernel<<<grid_for(ngroups, 256), 256, 0, s>>>(ix.occ.p, prefix.p, ngroups);
+        unsigned int hbad = 0;
+        CUDA_OK(cudaMemcpyAsync(&hbad, bad.p, 4, cudaMemcpyDeviceToHost, s));
+        // totals of the last block must reproduce the pile sizes implied by tableOcc
+        uint4 last_prefix, last_cnt;
+        CUDA_OK(cudaMemcpyAsync(&last_prefix, prefix.p + (nblk - 1), 16, cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaMemcpyAsync(&last_cnt, blkcnt.p + (nblk - 1), 16, cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaStreamSynchronize(s));
+        if (hbad) EDS_FAIL(EDSBWT_E_FORMAT, "eBWT row %u holds a byte outside the alphabet of info.aux", hbad - 1);
+        uint32_t tot[4] = {last_prefix.x + last_cnt.x, last_prefix.y + last_cnt.y, last_prefix.z + last_cnt.z, last_prefix.w + last_cnt.w};
+        for (uint32_t c = 0; c + 1 < h.sigma; ++c) {
+            uint32_t expect = 0;
+            for (uint32_t p = 0; p < h.sigma; ++p) expect += h.table_occ[p * h.sigma + c + 1];
+            if (tot[c] != expect) EDS_FAIL(EDSBWT_E_FORMAT, "letter %c occurs %u times in the piles, tableOcc says %u", h.alphabet[c + 1], tot[c], expect);
+            // pile of letter c holds exactly the suffixes starting with c = number of occurrences of c
+            if (h.pile_start[c + 2] - h.pile_start[c + 1] != expect) EDS_FAIL(EDSBWT_E_FORMAT, "pile %u has %u rows but letter %c occurs %u times", c + 1, h.pile_start[c + 2] - h.pile_start[c + 1], h.alphabet[c + 1], expect);
+        }
+    }
+    v.occ = ix.occ.p;
+    // ---- end-marker array and segment structure (rank/select on .bitvector, closure through empty strings)
+    ix.eof_flat.ensure(h.n_text + 1); ix.str_seg.ensure(h.n_text + 1); ix.seg_first.ensure((size_t)h.n_seg + 3); ix.seg_low.ensure((size_t)h.n_seg + 2);
+    {
+        std::vector<uint32_t> str_seg(h.n_text), seg_first(h.n_seg + 2, 0), seg_low(h.n_seg + 1, 0);
+        std::vector<uint8_t> has_empty(h.n_seg + 1, 0);
+        uint32_t seg = 0;
+        for (uint32_t w = 0; w < h.n_text; ++w) {
+            if (h.seg_first_bit[w]) seg_first[++seg] = w;
+            str_seg[w] = seg;
+            if (h.ebwt[w] == h.alphabet[0]) has_empty[seg] = 1;        // pile-0 row w holds '#' <=> string w is empty
+        }
+        seg_first[h.n_seg + 1] = h.n_text;
+        for (uint32_t sg = 1; sg <= h.n_seg; ++sg) seg_low[sg] = (sg == 1 || !has_empty[sg]) ? sg : seg_low[sg - 1];
+        v.fsi = h.n_seg >= 2 ? seg_first[2] - 1 : h.n_text - 1;      // first_symbol_index (EDSBWTsearch.cpp:168)
+        CUDA_OK(cudaMemcpyAsync(ix.eof_flat.p, h.eof_flat.data(), (size_t)h.n_text * 4, cudaMemcpyHostToDevice, s));
+        CUDA_OK(cudaMemcpyAsync(ix.str_seg.p, str_seg.data(), (size_t)h.n_text * 4, cudaMemcpyHostToDevice, s));
+        CUDA_OK(cudaMemcpyAsync(ix.seg_first.p, seg_first.data(), seg_first.size() * 4, cudaMemcpyHostToDevice, s));
+        CUDA_OK(cudaMemcpyAsync(ix.seg_low.p, seg_low.data(), seg_low.size() * 4, cudaMemcpyHostToDevice, s));
+        CUDA_OK(cudaStreamSynchronize(s));
+    }
+    v.eof_flat = ix.eof_flat.p; v.str_seg = ix.str_seg.p; v.seg_first = ix.seg_first.p; v.seg_low = ix.seg_low.p;
+    // ---- SA table
+    ix.locate_mode = o.locate_mode == EDSBWT_LOCATE_WALK ? EDSBWT_LOCATE_WALK : EDSBWT_LOCATE_SA;
+    if (ix.locate_mode == EDSBWT_LOCATE_SA) {
+        ix.sa_str.ensure((size_t)h.n + 1); ix.sa_off.ensure((size_t)h.n + 1);
+        DevBuf<uint32_t> slen; slen.ensure(h.n_text + 1);
+        CUDA_OK(cudaMemsetAsync(ix.sa_str.p, 0xff, (size_t)h.n * 4, s));
+        sa_walk_kernel<<<grid_for(h.n_text, 128), 128, 0, s>>>(v, ix.sa_str.p, ix.sa_off.p, slen.p);
+        if (h.n > h.n_text) sa_offset_kernel<<<grid_for(h.n - h.n_text, 256), 256, 0, s>>>(h.n_text, h.n, ix.sa_str.p, ix.sa_off.p, slen.p);
+        CUDA_OK(cudaStreamSynchronize(s));
+        v.sa_str = ix.sa_str.p; v.sa_off = ix.sa_off.p;
+    }
+    // ---- seed table
+    int k = o.seed_k;
+    if (k < 0) { k = 1; while (k < 12 && (1ull << (2 * (k + 2))) <= (uint64_t)h.n) ++k; }
+    if (k < 1) k = 1;
+    if (k > 14) k = 14;
+    ix.seed_k = (uint32_t)k;
+    build_seed_table(ix, ix.seed_k);
+    CUDA_OK(cudaGetLastError());
+    h.ebwt.clear(); h.ebwt.shrink_to_fit();
+    h.seg_first_bit.clear(); h.seg_first_bit.shrink_to_fit();
+    h.eof_flat.clear(); h.eof_flat.shrink_to_fit();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// batched search
+// ---------------------------------------------------------------------------------------------------
+void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat, uint64_t total_bytes, uint32_t max_len,
+                bool locate, int lf_variant, SearchOut& out) {
+    if (lf_variant != EDSBWT_LF_RANK) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "move-table LF variant not built into this handle");
+    (void)total_bytes;
+    CUDA_OK(cudaSetDevice(ix.device));
+    std::lock_guard<std::mutex> lock(ix.mu);
+    Workspace& ws = *ix.ws;
+    cudaStream_t s = ix.stream;
+    ws.launches = 0; ws.lf_ms = 0;
+    const bool stats = ix.collect_counters != 0;
+    StatsDev* st = stats ? ws.d_stats : nullptr;
+    CUDA_OK(cudaMemsetAsync(ws.d_stats, 0, sizeof(StatsDev), s));
+    CUDA_OK(cudaEventRecord(ws.ev0, s));
+    out.npat = npat; out.nocc = 0;
+    out.counts.ensure(npat ? npat : 1);
+    CUDA_OK(cudaMemsetAsync(out.counts.p, 0, (size_t)(npat ? npat : 1) * 4, s));
+    uint32_t nF = 0, steps = 0; uint64_t peak = 0;
+    if (npat) {
+        // encode
+        uint32_t words = (max_len + 31) / 32; if (!words) words = 1;
+        ws.ppack.ensure((size_t)npat * words); ws.plen.ensure(npat);
+        Lut lut = make_lut(ix.host);
+        encode_patterns_kernel<<<grid_for(npat, 128), 128, 0, s>>>(d_bytes, d_off, npat, lut, words, ws.ppack.p, ws.plen.p);
+        PatView pv{ws.ppack.p, ws.plen.p, words, npat, ix.seed_k};
+        // seed lookup
+        SeedView sv{};
+        for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.lo[L] = ix.seed[L]->lo.p; sv.hi[L] = ix.seed[L]->hi.p; }
+        ws.cnt.ensure(npat + 1); ws.src.ensure(npat); ws.base.ensure(npat + 1);
+        seed_count_kernel<<<grid_for(npat, 256), 256, 0, s>>>(pv, sv, ws.cnt.p, ws.src.p);
+        CUDA_OK(cudaMemsetAsync(ws.cnt.p + npat, 0, 4, s));
+        exclusive_sum(ws, ws.cnt.p, ws.base.p, (size_t)npat + 1, s);
+        ws.launches += 2;
+        nF = read_u32(ws, ws.base.p + npat, s);
+        ws.cur.ensure(nF ? nF : 1);
+        if (nF) { seed_scatter_kernel<<<grid_for(nF, 256), 256, 0, s>>>(pv, sv, ws.base.p, ws.src.p, nF, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p); ws.launches += 1; }
+        peak = nF;
+        uint32_t total_steps = max_len > ix.seed_k ? max_len - ix.seed_k : 0;
+        for (uint32_t t = 0; t < total_steps && nF; ++t) {
+            nF = engine_step<false>(ix, ws, pv, t, nF, st, ix.canonical_k, true);
+            ++steps;
+            if (nF > peak) peak = nF;
+        }
+        if (stats && nF) { count_I_kernel<<<grid_for(nF, 256), 256, 0, s>>>(pv, steps, ws.cur.pat.p, nF, st, ix.canonical_k); ws.launches += 1; }
+        // counts (+ locate)
+        if (nF) {
+            ws.len.ensure(nF + 1); ws.dofs.ensure(nF + 2);
+            interval_len_kernel<<<grid_for(nF, 256), 256, 0, s>>>(ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p, nF, ws.len.p, out.counts.p);
+            ws.launches += 1;
+            if (locate) {
+                CUDA_OK(cudaMemsetAsync(ws.len.p + nF, 0, 4, s));
+                exclusive_sum(ws, ws.len.p, ws.dofs.p, (size_t)nF + 1, s);
+                uint32_t nocc = read_u32(ws, ws.dofs.p + nF, s);
+                out.nocc = nocc;
+                if (nocc) {
+                    out.occ.ensure(nocc);
+                    CUDA_OK(cudaEventRecord(ws.evk0, s));
+                    if (ix.locate_mode == EDSBWT_LOCATE_WALK)
+                        locate_kernel<true><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.cur.pat.p, ws.cur.lo.p, ws.dofs.p, nF, nocc, out.occ.p, st);
+                    else
+                        locate_kernel<false><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.cur.pat.p, ws.cur.lo.p, ws.dofs.p, nF, nocc, out.occ.p, st);
+                    CUDA_OK(cudaEventRecord(ws.evk1, s));
+                    ws.launches += 1;
+                }
+            }
+        }
+    }
+    CUDA_OK(cudaEventRecord(ws.ev1, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    CUDA_OK(cudaGetLastError());
+    StatsDev hs{};
+    CUDA_OK(cudaMemcpy(&hs, ws.d_stats, sizeof hs, cudaMemcpyDeviceToHost));
+    float ms = 0; CUDA_OK(cudaEventElapsedTime(&ms, ws.ev0, ws.ev1));
+    edsbwt_stats& ls = ix.last;
+    ls = edsbwt_stats{};
+    ls.I = hs.I; ls.S = hs.S; ls.E = hs.E; ls.L = hs.L; ls.O = hs.O; ls.lf_intervals = hs.lf_intervals;
+    ls.steps = steps; ls.kernel_launches = ws.launches; ls.lf_kernel_ms = ws.lf_ms; ls.total_ms = ms; ls.frontier_peak = peak;
+    if (locate && out.nocc) { float lm = 0; CUDA_OK(cudaEventElapsedTime(&lm, ws.evk0, ws.evk1)); ls.locate_kernel_ms = lm; }
+}
+
+}  // namespace edsbwt

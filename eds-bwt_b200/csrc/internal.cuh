@@ -1,0 +1,194 @@
+// Internal declarations of libedsbwt_cuda.so (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/edsbwt.h"
+
+namespace edsbwt {
+
+// ---------------------------------------------------------------------------------------------------
+// error plumbing
+// ---------------------------------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+struct Failure { int code; };
+#define EDS_FAIL(code, ...) do { ::edsbwt::set_error(__VA_ARGS__); throw ::edsbwt::Failure{code}; } while (0)
+#define CUDA_OK(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { \
+    ::edsbwt::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); \
+    throw ::edsbwt::Failure{EDSBWT_E_CUDA}; } } while (0)
+
+// ---------------------------------------------------------------------------------------------------
+// growable device buffer
+// ---------------------------------------------------------------------------------------------------
+template <class T>
+struct DevBuf {
+    T* p = nullptr; size_t cap = 0;
+    DevBuf() {}
+    DevBuf(const DevBuf&) = delete; DevBuf& operator=(const DevBuf&) = delete;
+    ~DevBuf() { release(); }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    // grow (contents NOT preserved unless keep = true)
+    void ensure(size_t n, cudaStream_t s = 0, bool keep = false, size_t keep_n = 0) {
+        if (n <= cap) return;
+        size_t ncap = n + n / 4 + 64;
+        T* q = nullptr;
+        CUDA_OK(cudaMalloc(&q, ncap * sizeof(T)));
+        if (keep && p && keep_n) { CUDA_OK(cudaMemcpyAsync(q, p, keep_n * sizeof(T), cudaMemcpyDeviceToDevice, s)); CUDA_OK(cudaStreamSynchronize(s)); }
+        if (p) cudaFree(p);
+        p = q; cap = ncap;
+    }
+    size_t bytes() const { return cap * sizeof(T); }
+};
+
+// ---------------------------------------------------------------------------------------------------
+// Occ layout (DESIGN.md "HBM layout"): one 64-byte block per 128 eBWT rows = 4 x uint4, lane j holds
+//   .x  number of occurrences of letter j (alphabet index j+1) in rows [0, 128*blk)
+//   .y  bit-plane 0 (low bit of the 2-bit letter code) of rows 128*blk + 32*j .. +31
+//   .z  bit-plane 1
+//   .w  end-marker mask of those 32 rows ('#' rows have planes 0)
+// so that a 4-lane group fetches one block with ONE coalesced 128-bit load per lane and the rank of any
+// letter and of '#' (rank_# = pos - sum of letter ranks) come out of the same 64 bytes.
+// ---------------------------------------------------------------------------------------------------
+constexpr uint32_t OCC_ROWS = 128;
+
+struct IndexView {
+    const uint4* occ;            // (n/128 + 1) blocks
+    uint32_t n, n_text, n_seg, fsi;      // fsi = first_symbol_index = last string of segment 1
+    uint32_t Cl[5];              // Cl[c] = global row of the first suffix starting with letter c; Cl[4] = n
+    uint32_t nletters;
+    const uint32_t* eof_flat;    // EOF_ID flattened in pile order == order of '#' rows in the eBWT
+    const uint32_t* str_seg;     // string -> 1-based segment        (rank on .bitvector)
+    const uint32_t* seg_first;   // [1..n_seg+1] first string of segment (select), [n_seg+1] = n_text
+    const uint32_t* seg_low;     // [1..n_seg] lowest segment reachable from s through segments holding ""
+    const uint32_t* sa_str;      // row -> string (rows >= n_text), may be null (WALK mode)
+    const uint32_t* sa_off;      // row -> offset in string
+};
+
+#ifdef __CUDACC__
+// rank of letter c and of '#' in rows [0,pos), computed by a 4-lane group (lanes hold lane4 = 0..3).
+// Every lane of the warp must call it (full-mask shuffles).
+__device__ __forceinline__ uint4 occ_load(const uint4* __restrict__ occ, uint32_t blk, int lane4) {
+    return __ldg(occ + (size_t)blk * 4 + lane4);
+}
+__device__ __forceinline__ void rank4_from(uint4 v, uint32_t pos, int c, int lane4, uint32_t& rc, uint32_t& rd) {
+    int below = (int)(pos & (OCC_ROWS - 1)) - 32 * lane4;
+    uint32_t lm = below <= 0 ? 0u : (below >= 32 ? 0xffffffffu : ((1u << below) - 1u));
+    uint32_t m = ((c & 1) ? v.y : ~v.y) & ((c & 2) ? v.z : ~v.z) & ~v.w & lm;
+    uint32_t pc = __popc(m) + (lane4 == c ? v.x : 0u);
+    uint32_t pd = __popc(v.w & lm) - v.x;                     // wraps; the 4-lane sum is exact mod 2^32
+    pc += __shfl_xor_sync(0xffffffffu, pc, 1); pc += __shfl_xor_sync(0xffffffffu, pc, 2);
+    pd += __shfl_xor_sync(0xffffffffu, pd, 1); pd += __shfl_xor_sync(0xffffffffu, pd, 2);
+    rc = pc;
+    rd = pd + (pos & ~(OCC_ROWS - 1));
+}
+// single-thread variants (index build, LF-walk locate)
+__device__ __forceinline__ uint32_t occ_symbol(const uint4* __restrict__ occ, uint32_t row) {   // 0 = '#', 1+c = letter c
+    uint4 v = __ldg(occ + (size_t)(row >> 7) * 4 + ((row >> 5) & 3));
+    uint32_t b = row & 31;
+    if ((v.w >> b) & 1) return 0;
+    return 1 + (((v.y >> b) & 1) | (((v.z >> b) & 1) << 1));
+}
+__device__ __forceinline__ uint32_t occ_rank1(const uint4* __restrict__ occ, uint32_t pos, int c) {
+    uint32_t blk = pos >> 7, off = pos & 127;
+    const uint4* b = occ + (size_t)blk * 4;
+    uint32_t r = __ldg(&b[c].x);
+    for (int j = 0; j < 4; ++j) {
+        int below = (int)off - 32 * j;
+        if (below <= 0) break;
+        uint4 v = __ldg(&b[j]);
+        uint32_t lm = below >= 32 ? 0xffffffffu : ((1u << below) - 1u);
+        r += __popc(((c & 1) ? v.y : ~v.y) & ((c & 2) ? v.z : ~v.z) & ~v.w & lm);
+    }
+    return r;
+}
+__device__ __forceinline__ uint32_t occ_rank_eof(const uint4* __restrict__ occ, uint32_t pos) {
+    uint32_t blk = pos >> 7, off = pos & 127;
+    const uint4* b = occ + (size_t)blk * 4;
+    uint32_t r = blk * OCC_ROWS;
+    for (int j = 0; j < 4; ++j) {
+        uint4 v = __ldg(&b[j]);
+        r -= v.x;
+        int below = (int)off - 32 * j;
+        if (below > 0) r += __popc(v.w & (below >= 32 ? 0xffffffffu : ((1u << below) - 1u)));
+    }
+    return r;
+}
+#endif
+
+// ---------------------------------------------------------------------------------------------------
+// host-side index image (everything read from the reference's files)
+// ---------------------------------------------------------------------------------------------------
+struct HostIndex {
+    uint32_t n = 0, n_text = 0, sigma = 0, n_seg = 0;
+    uint8_t alphabet[8] = {0};
+    std::vector<uint8_t> ebwt;            // piles concatenated (raw bytes)
+    uint32_t pile_start[9] = {0};         // global row of the start of pile p, [sigma] = n
+    std::vector<uint32_t> eof_flat;       // nText
+    uint32_t table_occ[64] = {0};         // sigma x sigma
+    std::vector<uint8_t> seg_first_bit;   // nText 0/1
+};
+void load_host_index(const std::string& base, bool verify, HostIndex& h);      // host_io.cpp
+
+// sdsl formats (host_io.cpp)
+std::vector<uint8_t> rrr_decode(const std::vector<uint8_t>& file);             // -> 0/1 per bit
+std::vector<uint8_t> rrr_encode(const uint8_t* bits01, size_t nbits);          // sdsl rrr_vector<63> bytes
+std::vector<uint8_t> bitvector_encode(const uint8_t* bits01, size_t nbits);
+std::vector<uint8_t> bitvector_decode(const std::vector<uint8_t>& file);
+std::vector<uint8_t> read_file(const std::string& path);
+void write_file(const std::string& path, const void* data, size_t len);
+// EDS text -> collection (eds_to_fasta.cpp:55-140)
+void parse_eds_text(const std::vector<uint8_t>& text, std::vector<uint8_t>& letters, std::vector<uint64_t>& str_off,
+                    std::vector<uint8_t>& seg_first);
+
+// ---------------------------------------------------------------------------------------------------
+// device index + search engine
+// ---------------------------------------------------------------------------------------------------
+struct SeedLevel { DevBuf<uint32_t> off, lo, hi; size_t n_iv = 0; };
+
+struct StatsDev { unsigned long long I, S, E, L, O, lf_intervals; };
+
+struct Workspace;   // engine.cu
+
+struct Index {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+    HostIndex host;       // ebwt bytes dropped after upload
+    DevBuf<uint4> occ;
+    DevBuf<uint32_t> eof_flat, str_seg, seg_first, seg_low, sa_str, sa_off;
+    IndexView view{};
+    uint32_t seed_k = 0;
+    int locate_mode = EDSBWT_LOCATE_SA;
+    std::vector<SeedLevel*> seed;       // seed[L] for L = 1..seed_k (index 0 unused)
+    uint64_t seed_intervals = 0;
+    Workspace* ws = nullptr;
+    edsbwt_stats last{};
+    int collect_counters = 0; uint32_t canonical_k = 12;
+    uint64_t device_bytes() const;
+    ~Index();
+};
+
+// engine.cu
+void build_device_index(Index& ix, const edsbwt_open_opts& o);
+struct SearchOut {
+    DevBuf<uint32_t> counts; DevBuf<edsbwt_occ> occ; uint32_t npat = 0; uint64_t nocc = 0;
+};
+void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat, uint64_t total_bytes,
+                uint32_t max_len, bool locate, int lf_variant, SearchOut& out);
+
+// builder.cu
+void build_index_files(const uint8_t* letters, const uint64_t* str_off, uint32_t nstr, const uint8_t* seg_first,
+                       const std::string& out_base, int device);
+// gather_bench.cu
+double gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, int iters);
+
+}  // namespace edsbwt
+
+struct edsbwt_index { edsbwt::Index ix; };
+struct edsbwt_result { edsbwt::SearchOut out; int device; };

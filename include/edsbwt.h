@@ -1,0 +1,141 @@
+/* edsbwt.h -- C ABI of libedsbwt_cuda.so: B200-native batched pattern search over the EDS-BWT index.
+ *
+ * The reference (riccardo-nozza/EDS-BWT) has no library API: its operator surface is two executables whose
+ * constructors run the whole job.  Each entry point below names the reference code
+ * it replaces, so that a maintainer can bind it from the reference's own main().
+ * Plain pointers and sizes only; no C++/torch types.  All functions return 0 on success or a negative
+ * EDSBWT_E_* code and never call exit() (the reference exits on every error: EDSBWTsearch.cpp:158-161,
+ * 1562-1565).  There is NO CPU fallback: without a CUDA device every compute entry point fails with
+ * EDSBWT_E_CUDA.
+ */
+#ifndef EDSBWT_H
+#define EDSBWT_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EDSBWT_OK            0
+#define EDSBWT_E_IO         -1   /* a file of the index / pattern set could not be opened or is truncated   */
+#define EDSBWT_E_FORMAT     -2   /* inconsistent index files (sizes, tableOcc, _bv_ vs _bwt_, .bitvector)    */
+#define EDSBWT_E_ALPHABET   -3   /* more than 4 letters besides the end-marker (2-bit Occ layout only)       */
+#define EDSBWT_E_CUDA       -4   /* no device / CUDA runtime error / out of device memory                    */
+#define EDSBWT_E_ARG        -5   /* bad argument                                                             */
+#define EDSBWT_E_UNSUPPORTED -6
+
+typedef struct edsbwt_index edsbwt_index;     /* opaque, immutable after open; one handle per GPU */
+typedef struct edsbwt_result edsbwt_result;   /* opaque, device-resident result of edsbwt_search_device */
+
+/* One occurrence = one row of the reference's <patterns>output.csv (EDSBWTsearch.cpp:1320-1327):
+ *   #Pat  $_i  D[i]  S_j  S_j[r]
+ * pat is the 0-based index of the pattern inside the call (the csv prints pat+1 = the 1-based line number). */
+typedef struct {
+    uint32_t pat;         /* pattern index within the batch                                   */
+    uint32_t str;         /* $_i : 0-based string index                                        */
+    uint32_t seg;         /* D[i]: 1-based degenerate segment                                  */
+    uint32_t idx_in_seg;  /* S_j : 0-based index of the string inside its segment              */
+    uint32_t off;         /* S_j[r]: 0-based offset of the occurrence inside the string        */
+} edsbwt_occ;
+
+typedef struct {
+    uint32_t n;                 /* eBWT length incl. end-markers (info.aux lengthTot_plus_eof) */
+    uint32_t n_text;            /* number of strings                                           */
+    uint32_t n_seg;             /* number of degenerate segments                               */
+    uint32_t sigma;             /* alphabet size incl. the end-marker                          */
+    uint8_t  alphabet[8];       /* alphaInverse[], alphabet[0] == '#'                          */
+    uint32_t table_occ[25];     /* tableOcc[sigma][sigma], row-major (recoverInfo dump)        */
+    uint32_t seed_k;            /* depth of the seed table actually built                      */
+    uint32_t locate_mode;       /* EDSBWT_LOCATE_*                                             */
+    uint64_t device_bytes;      /* HBM held by the handle                                      */
+    uint64_t seed_intervals;    /* total intervals stored in the seed table                    */
+} edsbwt_info;
+
+#define EDSBWT_LOCATE_SA    0   /* row -> (string, offset) table in HBM: one gather per occurrence           */
+#define EDSBWT_LOCATE_WALK  1   /* LF-walk each row to its string start (the reference's a9/a13 arithmetic)  */
+#define EDSBWT_LF_RANK      0   /* EDSBWTsearch:      LF by blocked rank                                      */
+#define EDSBWT_LF_MOVE      1   /* MOVE_EDSBWTSearch: LF by move table                                        */
+
+typedef struct {
+    int32_t  seed_k;            /* -1 = auto (min(12, floor(log4 n) - 1)), 0 = no seed table                  */
+    int32_t  locate_mode;       /* EDSBWT_LOCATE_SA / _WALK                                                   */
+    int32_t  verify;            /* 1 = cross-check _bv_<p>.aux (rrr) and tableOcc against the pile bytes      */
+    int32_t  build_move;        /* 1 = also build the move table (EDSBWT_LF_MOVE searches)                    */
+    int32_t  reserved[4];
+} edsbwt_open_opts;
+
+/* Canonical byte-model counters of DESIGN.md + engine statistics of the last search. */
+typedef struct {
+    uint64_t I, S, E, L, O;     /* seed intervals, interval-steps, end-markers enumerated, locate row-steps, occurrences */
+    uint64_t steps;             /* level-synchronous backward steps executed                                   */
+    uint64_t kernel_launches;   /* kernels of this library launched by the last search                         */
+    uint64_t lf_intervals;      /* intervals LF-mapped by the rank kernel (all steps, incl. those inside the seed range) */
+    double   lf_kernel_ms;      /* CUDA-event time summed over the launches of the LF rank kernel              */
+    double   locate_kernel_ms;  /* CUDA-event time of the locate kernel                                        */
+    double   total_ms;          /* CUDA-event time of the whole search on the library's stream                 */
+    uint64_t frontier_peak;     /* largest frontier (intervals) over all steps                                  */
+} edsbwt_stats;
+
+/* --- index load: replaces EDSBWT::recoverInfo (EDSBWTsearch.cpp:1557-1656), EDSBWT::computeVectorOcc
+ *     (:1338-1442) and the .bitvector rank/select set-up of the constructor (:150-168).
+ *     base is the reference's <indexBase>: reads base_info.aux, base_bwt_<p>.aux, base_bv_<p>.aux, base.bitvector. */
+int  edsbwt_index_open(const char* base, int device, edsbwt_index** out);
+int  edsbwt_index_open_ex(const char* base, int device, const edsbwt_open_opts* opts, edsbwt_index** out);
+int  edsbwt_index_info(const edsbwt_index* idx, edsbwt_info* info);
+void edsbwt_index_close(edsbwt_index* idx);
+
+/* --- search: replaces the per-pattern loop of the EDSBWT constructor (EDSBWTsearch.cpp:207-241) with one
+ *     batched call: EDSBWT::backwardSearch (:619-772), link (:1212-1307), updateIntervals (:956-1157) and,
+ *     when locate != 0, findMultipleDollarsBackward + indices_of_dollars_in_interval (:300-616, 1310-1332);
+ *     lf_variant = EDSBWT_LF_MOVE is MOVE_EDSBWT::backwardSearch (MOVE_EDSBWTSearch.cpp:228-374).
+ *     Pattern i is pat_bytes[pat_off[i] .. pat_off[i+1]) (pat_off has npat+1 entries); HOST pointers.
+ *     counts[i] = number of distinct starting positions ("Found N ...", :739-746).
+ *     locate != 0: *occ receives a malloc'ed array of *nocc tuples grouped by ascending pat (order inside a
+ *     pattern unspecified; the occurrence SET equals the reference's); release with edsbwt_free.
+ *     Patterns holding a byte outside the index alphabet (or the end-marker) yield 0 (reference: undefined
+ *     behaviour); empty patterns yield 0. */
+int  edsbwt_search(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat,
+                   int locate, int lf_variant, uint32_t* counts, edsbwt_occ** occ, uint64_t* nocc);
+
+/* Same search with the packed patterns already resident in HBM and the results left there (the `value`
+ * leg of bench.py).  d_* are DEVICE pointers on the handle's device.  total_bytes = pat_off[npat]. */
+int  edsbwt_search_device(edsbwt_index* idx, const uint8_t* d_pat_bytes, const uint64_t* d_pat_off, uint32_t npat,
+                          uint64_t total_bytes, uint32_t max_len, int locate, int lf_variant, edsbwt_result** res);
+int  edsbwt_result_sizes(const edsbwt_result* res, uint32_t* npat, uint64_t* nocc);
+int  edsbwt_result_device_ptrs(const edsbwt_result* res, const uint32_t** d_counts, const edsbwt_occ** d_occ);
+int  edsbwt_result_fetch(const edsbwt_result* res, uint32_t* counts, edsbwt_occ* occ); /* D2H into host buffers */
+void edsbwt_result_free(edsbwt_result* res);
+
+int  edsbwt_last_stats(const edsbwt_index* idx, edsbwt_stats* st);
+int  edsbwt_set_stats(edsbwt_index* idx, int collect_counters, uint32_t canonical_k);
+
+/* --- output: replaces the csv writing of EDSBWT's constructor (:179-193) and of
+ *     indices_of_dollars_in_interval (:1327).  Creates/truncates path, writes the header
+ *     "#Pat\t$_i\tD[i]\tS_j\tS_j[r]\n" (move != 0: the MOVE header ending "S_j[r] \n",
+ *     MOVE_EDSBWTSearch.cpp:55-59) and one row per tuple with pat + pat_base + 1. */
+int  edsbwt_write_csv(const char* path, const edsbwt_occ* occ, uint64_t nocc, uint32_t pat_base, int move, int append);
+
+/* --- pattern file: std::getline loop of the constructor (:200-241): one pattern per '\n'-separated line,
+ *     last line may lack '\n'.  *bytes / *off are malloc'ed (edsbwt_free). */
+int  edsbwt_read_patterns(const char* path, uint8_t** bytes, uint64_t** off, uint32_t* npat);
+
+/* --- index construction (replaces eds_to_fasta.cpp + gsufsort + da_to_everything.cpp):
+ *     GPU suffix sort of the string collection, writes the reference's files
+ *     out_base_info.aux, _bwt_<p>.aux, _bv_<p>.aux (sdsl rrr_vector<63>), .bitvector. */
+int  edsbwt_build_from_eds(const char* eds_path, const char* out_base, int device);
+/* text = S_0 S_1 ... (letters only, no separators), str_off[nstr+1], seg_first[nstr] = 1 for the first string
+ * of each segment.  HOST pointers. */
+int  edsbwt_build_from_collection(const uint8_t* text, const uint64_t* str_off, uint32_t nstr,
+                                  const uint8_t* seg_first, const char* out_base, int device);
+
+/* --- roofline denominator: 64-byte random gather over buffer_bytes of HBM (kernel K7). */
+int  edsbwt_gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, double* gb_per_s);
+
+void        edsbwt_free(void* p);
+const char* edsbwt_strerror(int code);
+const char* edsbwt_last_error(void);   /* thread-local detail of the last failure */
+const char* edsbwt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EDSBWT_H */

@@ -18,35 +18,7 @@ from oracle import eds_index as E, run as R   # noqa: E402
 OUT = os.path.dirname(os.path.abspath(__file__))
 
 
-def sample_patterns(rng, segs, n, lens, p_path=0.7):
-    """Patterns drawn from random EDS paths (hits) mixed with uniform random ones."""
-    strings = [s for seg in segs for s in seg]
-    seg_of = [i for i, seg in enumerate(segs) for _ in seg]
-    first = np.cumsum([0] + [len(s) for s in segs])
-    pats = []
-    for _ in range(n):
-        m = int(rng.choice(lens))
-        if rng.random() < p_path:
-            while True:
-                w = int(rng.integers(len(strings)))
-                if len(strings[w]):
-                    break
-            r = int(rng.integers(len(strings[w])))
-            out = bytearray(strings[w][r:])
-            s = seg_of[w] + 1
-            while len(out) < m and s < len(segs):
-                out += segs[s][int(rng.integers(len(segs[s])))]
-                s += 1
-            out = out[:m]
-            if len(out) < m:
-                out += bytes(rng.choice(list(b"ACGT"), size=m - len(out)).astype(np.uint8))
-            if rng.random() < 0.1:
-                k = int(rng.integers(m))
-                out[k] = int(rng.choice(list(b"ACGT")))
-            pats.append(bytes(out))
-        else:
-            pats.append(bytes(rng.choice(list(b"ACGT"), size=m).astype(np.uint8)))
-    return pats
+sample_patterns = E.sample_patterns
 
 
 def make(name, eds_text, patterns, note):

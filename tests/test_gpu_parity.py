@@ -1,0 +1,127 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via ctypes) against the oracle on the same inputs.
+Bit-exact bar: identical counts, identical occurrence sets, identical byte-model counters."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+
+from conftest import golden_names, load_golden
+from oracle import eds_index as E
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eb():
+    return importlib.import_module("eds-bwt_b200")
+
+
+def _index_files(tmp_path, segs, name="idx"):
+    ix = E.build_index(segs)
+    base = str(tmp_path / name)
+    E.write_index(ix, base)
+    return ix, base
+
+
+@pytest.mark.parametrize("name", golden_names())
+@pytest.mark.parametrize("seed_k,locate_mode", [(-1, 0), (1, 0), (3, 1), (6, 0)])
+def test_golden(eb, tmp_path, name, seed_k, locate_mode):
+    g = load_golden(name)
+    _, base = _index_files(tmp_path, E.parse_eds(g["eds"]))
+    with eb.Index(base, seed_k=seed_k, locate_mode=locate_mode) as idx:
+        counts, occ = idx.search(g["patterns"], locate=True)
+        assert counts.tolist() == g["counts"]
+        assert eb.occ_rows(occ) == sorted(g["rows_reference_order"])
+        assert np.all(np.diff(occ["pat"].astype(np.int64)) >= 0)          # grouped by ascending pattern
+        counts0, _ = idx.search(g["patterns"], locate=False)
+        assert counts0.tolist() == g["counts"]
+
+
+def _mixed_patterns(rng, segs, n, lens):
+    return E.sample_patterns(rng, segs, n, lens)
+
+
+@pytest.mark.parametrize("seed,kw,seed_k", [
+    (21, dict(n_seg=300, max_var=5, max_len=5, p_empty=0.3), 2),
+    (22, dict(n_seg=2000, max_var=4, max_len=6, p_empty=0.15, nondeg_len=(1, 40)), 4),
+    (23, dict(n_seg=1200, max_var=8, max_len=3, p_empty=0.45, nondeg_len=(1, 3)), 5),
+    (24, dict(n_seg=5000, max_var=3, max_len=8, p_empty=0.1, nondeg_len=(5, 120)), -1),
+])
+def test_random_vs_port(eb, oracle_built, tmp_path, seed, kw, seed_k):
+    rng = np.random.default_rng(seed)
+    segs = E.random_eds(rng, **kw)
+    _, base = _index_files(tmp_path, segs)
+    pats = _mixed_patterns(rng, segs, 600, [1, 2, 3, 5, 8, 13, 21, 32, 50, 64, 100])
+    pats += [b"", b"ACGNT", b"#A", b"A" * 300]
+    pf = str(tmp_path / "p.txt")
+    E.write_patterns(pf, [p if p else b"A" for p in pats])       # the file format cannot hold an empty line
+    with eb.Index(base, seed_k=seed_k, locate_mode=0) as idx:
+        k = idx.info().seed_k
+        idx.set_stats(True, canonical_k=k)
+        file_pats = [p if p else b"A" for p in pats]
+        c_port, rows_port, st_port = oracle_built.run_port(base, pf, locate=True, k=k)
+        counts, occ = idx.search(file_pats, locate=True)
+        st = idx.last_stats()
+        assert counts.tolist() == c_port
+        assert eb.occ_rows(occ) == sorted(rows_port)
+        for key in "ISELO":
+            assert st[key] == st_port[key], (key, st[key], st_port[key])
+        # the empty pattern itself (not representable in a file) -> 0
+        c2, o2 = idx.search([b"", b"ACG"], locate=True)
+        assert c2[0] == 0 and all(o2["pat"] == 1)
+    with eb.Index(base, seed_k=seed_k, locate_mode=1) as idx:          # LF-walk locate
+        counts, occ = idx.search(file_pats, locate=True)
+        assert counts.tolist() == c_port and eb.occ_rows(occ) == sorted(rows_port)
+
+
+def test_edge_cases(eb, tmp_path):
+    # single segment (the reference aborts here, App. C.3): plain matching
+    _, base = _index_files(tmp_path, [[b"ACGTACGT", b"CGT"]], "one")
+    with eb.Index(base) as idx:
+        c, o = idx.search([b"CGT", b"T", b"TA", b"GG"])
+        assert c.tolist() == [3, 3, 1, 0]
+        assert eb.occ_rows(o) == sorted([(1, 0, 1, 0, 1), (1, 0, 1, 0, 5), (1, 1, 1, 1, 0), (2, 0, 1, 0, 3), (2, 0, 1, 0, 7),
+                                         (2, 1, 1, 1, 2), (3, 0, 1, 0, 3)])
+        c, o = idx.search([], locate=True)
+        assert len(c) == 0 and len(o) == 0
+    # fewer than 4 letters
+    segs = [[b"AAC"], [b"A", b"", b"CA"], [b"CCA"]]
+    _, base = _index_files(tmp_path, segs, "two")
+    with eb.Index(base, seed_k=2) as idx:
+        pats = [b"A", b"AC", b"CAC", b"ACC", b"ACAC", b"AACCCA", b"G", b"T"]
+        c, o = idx.search(pats)
+        exp = []
+        for i, p in enumerate(pats):
+            bf = E.brute_force(segs, p) if all(ch in b"AC" for ch in p) else []
+            assert c[i] == len(bf)
+            exp += [(i + 1,) + t for t in bf]
+        assert eb.occ_rows(o) == sorted(exp)
+
+
+def test_bad_index_files(eb, tmp_path):
+    ix, base = _index_files(tmp_path, E.parse_eds(b"{TT,TA,C}{T}{TT,A,G}{TT,}{ATT}"))
+    with open(base + "_bwt_1.aux", "ab") as f:
+        f.write(b"A")
+    with pytest.raises(eb.EdsbwtError) as ei:
+        eb.Index(base)
+    assert ei.value.code == -2
+    with pytest.raises(eb.EdsbwtError) as ei:
+        eb.Index(str(tmp_path / "missing"))
+    assert ei.value.code == -1
+
+
+def test_csv_and_pattern_file(eb, tmp_path):
+    g = load_golden("readme_test")
+    _, base = _index_files(tmp_path, E.parse_eds(g["eds"]))
+    pf = str(tmp_path / "kmers.txt")
+    with open(pf, "wb") as f:
+        f.write(b"TATT\nACT\nTTAT")            # last line without '\n'
+    data, off = eb.read_patterns(pf)
+    assert len(off) == 4 and bytes(data[off[2]:off[3]]) == b"TTAT"
+    with eb.Index(base) as idx:
+        counts, occ = idx.search((data, off))
+    eb.write_csv(pf + "output.csv", occ)
+    header, rows = E.read_csv_rows(pf + "output.csv")
+    assert header == "#Pat\t$_i\tD[i]\tS_j\tS_j[r]\n"
+    assert sorted(rows) == sorted(g["rows_reference_order"])
