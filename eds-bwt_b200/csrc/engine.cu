@@ -486,7 +486,7 @@ static uint32_t engine_step(Index& ix, Workspace& ws, PatView pv, uint32_t step,
     uint32_t nF2 = compact_and_merge<KEYMODE>(ix, ws, pv, step, ws.cur.pat.p, ws.raw, nF, ws.cmp, ws.mrg);
     if (nDol == 0) { ws.cur.swap(ws.mrg); return nF2; }
     // Dol' : LF of the pile-0 ranges, then the same clean-up
-    ws.dolraw.ensure(nDol); ws.keep.ensure(nDol + 1);
+    ws.dolraw.ensure(nDol); ws.keep.ensure(nDol + 1); ws.dcnt.ensure(nDol + 1); ws.dstart.ensure(nDol + 1);
     if (time_lf) CUDA_OK(cudaEventRecord(ws.evk0, s));
     lf_step_kernel<KEYMODE><<<grid_for((size_t)nDol * 4, 256), 256, 0, s>>>(ix.view, pv, step, ws.dol.pat.p, ws.dol.lo.p, ws.dol.hi.p, nDol,
         ws.dolraw.lo.p, ws.dolraw.hi.p, ws.dcnt.p, ws.dstart.p, ws.keep.p, st, kc, 1);
