@@ -1,0 +1,384 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the EDS-BWT batched pattern search on B200 (BASELINE.json metric:
+"patterns/sec located (len 32)").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" = one pass of the hot path (seed lookup + backward search + locate) over one batch of synthetic
+patterns.  Workload at every N: cfg4 of SURVEY.md 8(d) -- the 250 Mbp synthetic chromosome-scale EDS
+(index replicated on every GPU) with 10 M length-32 patterns PER GPU (weak scaling, patterns sharded, no
+data-path collective).  value = patterns of all ranks / max-over-ranks device time.
+
+  value     patterns already packed in HBM, result tuples left in HBM (edsbwt_search_device)
+  e2e       the same batch through edsbwt_search with HOST buffers: H2D of the patterns and D2H of the
+            counts + occurrence tuples inside the timed region
+  roofline  dominant kernel against measured HBM bandwidth (see DESIGN.md "Measurement")
+  cpu_baseline   the reference's own CPU search (oracle/_ref, unmodified sources) on a bounded sample
+
+--impl reference times the reference's CPU implementation (all host cores) on the same index and prints
+the same JSON line shape.
+"""
+import argparse
+import ctypes
+import glob
+import importlib
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "patterns/sec located (len 32)"
+UNIT = "patterns/s"
+
+
+def log(*a):
+    print("[bench]", *a, file=sys.stderr, flush=True)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mbp", type=float, default=float(os.environ.get("EDSBWT_BENCH_MBP", "250")))
+    ap.add_argument("--npat", type=int, default=int(os.environ.get("EDSBWT_BENCH_NPAT", "10000000")))
+    ap.add_argument("--len", type=int, default=32, dest="plen")
+    ap.add_argument("--seed-k", type=int, default=-1)
+    ap.add_argument("--workdir", default=os.environ.get("EDSBWT_BENCH_DIR", ""))
+    ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU budget of the cpu_baseline sample")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--keep", action="store_true")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------------
+# clocks
+# ----------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi SM clocks and throttle reasons while the timed region runs."""
+
+    def __init__(self, device):
+        super().__init__(daemon=True)
+        self.device = device
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._halt = threading.Event()
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_throttle_reasons.hw_slowdown,clocks_throttle_reasons.hw_thermal_slowdown," \
+            "clocks_throttle_reasons.sw_thermal_slowdown,clocks_throttle_reasons.sw_power_cap"
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self._halt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip().split(",")
+                self.samples.append(float(out[0]))
+                self.max_mhz = float(out[1])
+                for nm, v in zip(names, out[2:]):
+                    if v.strip().lower() == "active":
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            self._halt.wait(0.05)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=6)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ----------------------------------------------------------------------------------------------------
+# workload
+# ----------------------------------------------------------------------------------------------------
+def workload_name(args):
+    return "cfg4: synthetic %g Mbp chromosome-scale EDS (1 variant site / 100 bp, 2-8 alleles), %d length-%d patterns per GPU, locate" % (
+        args.mbp, args.npat, args.plen)
+
+
+def build_index_files(eb, synth, args, base):
+    t0 = time.time()
+    col = synth.chromosome_eds(args.mbp, seed=4)
+    t1 = time.time()
+    eb.build_from_collection(col.letters, col.str_off, col.seg_first, base, device=0)
+    t2 = time.time()
+    log("EDS generated in %.1fs (n=%d rows, %d strings, %d segments); index files built on the GPU + written in %.1fs" % (
+        t1 - t0, col.n_rows, col.nstr, col.n_seg, t2 - t1))
+    return col
+
+
+def cpu_reference_run(base, pats, seconds, cores, note):
+    """Times the reference's own CPU search on `cores` independent processes (it is single-threaded:
+    mainEDS-BWT.cpp:66), each on its own shard of a bounded sample.  -> dict for cpu_baseline."""
+    from oracle import run as R
+    exe = R.ref_binary("rb1")
+    kind = "reference"
+    if exe is None:
+        if not os.path.exists(R.PORT):
+            R.build()
+        exe, kind = R.PORT, "port"
+    d = tempfile.mkdtemp(prefix="edsbwt_cpu_")
+    try:
+        def run_shards(per):
+            procs, files = [], []
+            for c in range(cores):
+                pf = os.path.join(d, "p%d.txt" % c)
+                with open(pf, "wb") as f:
+                    for r in pats[c * per:(c + 1) * per]:
+                        f.write(r.tobytes() + b"\n")
+                files.append(pf)
+            t0 = time.time()
+            for pf in files:
+                cmd = [exe, base, pf] if kind == "reference" else [exe, base, pf, "--locate", "1", "--csv", pf + "output.csv"]
+                procs.append(subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True))
+            took = []
+            for p in procs:
+                out = p.communicate()[0]
+                if kind == "reference":
+                    import re
+                    m = re.search(r"bs took:([0-9.eE+-]+)", out)
+                    took.append(float(m.group(1)) if m else float("nan"))
+                else:
+                    took.append(json.loads(out.strip().splitlines()[-1])["seconds"])
+            return time.time() - t0, max(took)
+        # calibrate with one pattern per core, then size the sample for ~`seconds` of search time
+        wall1, took1 = run_shards(1)
+        per = int(max(1, min(len(pats) // cores, seconds / max(took1, 1e-3))))
+        wall, took = run_shards(per)
+        val = per * cores / max(took, 1e-9)
+        return {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
+                "sample": "%d patterns (%d per process x %d processes) of the same batch, %s; max 'bs took' %.2fs (index load excluded, wall %.1fs)" % (
+                    per * cores, per, cores, note, took, wall),
+                "search_seconds": took}
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+
+
+# ----------------------------------------------------------------------------------------------------
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1 and args.gpus > 1 and args.impl == "ours":
+        # convenience: relaunch under torchrun
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    if args.impl == "reference" and rank != 0:
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    eb = importlib.import_module("eds-bwt_b200")
+    synth = importlib.import_module("eds-bwt_b200.synth")
+
+    workdir = args.workdir or os.path.join("/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir(), "edsbwt_bench_%d" % os.getuid())
+    base = os.path.join(workdir, "cfg4_%g" % args.mbp)
+    done_flag = base + ".done"
+
+    if args.impl == "reference":
+        return reference_arm(args, eb, synth, workdir, base, done_flag)
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    eb.lib()
+
+    # ---- index files: rank 0 generates + builds (GPU suffix sort), everybody opens
+    if rank == 0:
+        os.makedirs(workdir, exist_ok=True)
+        if not os.path.exists(done_flag):
+            build_index_files(eb, synth, args, base)
+            open(done_flag, "w").close()
+    if world > 1:
+        dist.barrier()
+    t0 = time.time()
+    idx = eb.Index(base, device=local_rank, seed_k=args.seed_k, verify=False)
+    info = idx.info()
+    log("rank %d: index open in %.1fs: n=%d nText=%d nSeg=%d seed_k=%d seed_intervals=%d device_bytes=%.2f GB" % (
+        rank, time.time() - t0, info.n, info.n_text, info.n_seg, info.seed_k, info.seed_intervals, info.device_bytes / 1e9))
+
+    # ---- patterns of this rank (every rank regenerates the collection; seeds differ per rank)
+    t0 = time.time()
+    col = synth.chromosome_eds(args.mbp, seed=4)
+    pats = synth.sample_patterns(col, args.npat, args.plen, seed=44 + rank)
+    del col
+    data, off = synth.pack_fixed(pats)
+    log("rank %d: %d patterns sampled in %.1fs" % (rank, args.npat, time.time() - t0))
+    h_data = torch.from_numpy(data).pin_memory()
+    h_off = torch.from_numpy(off.view(np.int64)).pin_memory()
+    d_data = h_data.cuda(non_blocking=False)
+    d_off = h_off.cuda(non_blocking=False)
+    total_bytes = int(data.size)
+    torch.cuda.synchronize()
+
+    def step_device():
+        r = idx.search_device(d_data.data_ptr(), d_off.data_ptr(), args.npat, total_bytes, args.plen, locate=True)
+        st = idx.last_stats()
+        nocc = r.nocc
+        r.free()
+        return st, nocc
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # counters pass (untimed): canonical byte model I,S,E,L,O + Occ blocks actually fetched
+    idx.set_stats(True, 12)
+    st_c, nocc = step_device()
+    idx.set_stats(False, 12)
+    for _ in range(max(args.warmup, 3) - 1):
+        step_device()
+
+    # ---- timed region: `value`
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    dev_ms, lf_ms, loc_ms, launches = 0.0, 0.0, 0.0, 0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        st, _ = step_device()
+        dev_ms += st["total_ms"]; lf_ms += st["lf_kernel_ms"]; loc_ms += st["locate_kernel_ms"]; launches += st["kernel_launches"]
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop()
+
+    # ---- e2e: host buffers through edsbwt_search
+    counts_h = np.zeros(args.npat, dtype=np.uint32)
+    e2e_ms, d2h = 0.0, 0
+    for it in range(1 + args.steps):
+        barrier()
+        t1 = time.perf_counter()
+        counts, occ = idx.search((data, off), locate=True)
+        dt = (time.perf_counter() - t1) * 1e3
+        if it > 0:
+            e2e_ms += dt
+            d2h = counts.nbytes + occ.nbytes
+    h2d = data.nbytes + off.nbytes
+    del counts_h
+
+    def allmax(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    dev_ms_max = allmax(dev_ms)
+    wall_ms_max = allmax(wall_ms)
+    e2e_ms_max = allmax(e2e_ms)
+    total_pat = args.npat * world * args.steps
+    value = total_pat / (dev_ms_max * 1e-3)
+    e2e_val = total_pat / (e2e_ms_max * 1e-3)
+
+    out = None
+    if rank == 0:
+        peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6553.6))
+        peak_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6553.6 GB/s (B200_PROFILING.md)"
+        # dominant kernel: the LF rank kernel.  Algorithmic bytes = 64 B per distinct Occ block an interval end needs
+        # + the 12 B interval record read + 8 B written; canonical SURVEY model printed next to it.
+        occ_blocks = st_c.get("occ_blocks", 0) or 2 * st_c["lf_intervals"]
+        alg_bytes = 64.0 * occ_blocks + 20.0 * st_c["lf_intervals"]
+        lf_ms_step = lf_ms / args.steps
+        achieved = alg_bytes / (lf_ms_step * 1e-3) / 1e9 if lf_ms_step > 0 else 0.0
+        canon = 8.0 * (args.npat + st_c["I"]) + 128.0 * st_c["S"] + 16.0 * st_c["E"] + 64.0 * st_c["L"] + 28.0 * st_c["O"]
+        try:
+            g_big = eb.gather_bench(local_rank, 4 << 30, 1 << 26, 3)
+            g_idx = eb.gather_bench(local_rank, max(64 << 20, int(info.n // 128 + 1) * 64), 1 << 26, 3)
+        except Exception as e:      # noqa
+            log("gather bench failed:", e)
+            g_big = g_idx = None
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u32", "data": "synthetic",
+            "config": {"workload": workload_name(args), "index_rows": info.n, "strings": info.n_text, "segments": info.n_seg,
+                       "patterns_per_gpu": args.npat, "pattern_len": args.plen, "seed_k": info.seed_k, "locate": "sa-table",
+                       "parallelism": "patterns sharded x%d, index replicated" % world,
+                       "l2": "inputs larger than L2 (patterns %.0f MB + index %.2f GB per step; no flush needed)" % (data.nbytes / 1e6, info.device_bytes / 1e9)},
+            "wall_ms_per_step": wall_ms_max / args.steps,
+            "occurrences_per_step": int(nocc),
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "ms_per_step": e2e_ms_max / args.steps},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "lf_step_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak if peak else None, "traffic": None, "peak_source": peak_src,
+                         "alg_bytes_per_step": alg_bytes, "kernel_ms_per_step": lf_ms_step,
+                         "kernel_share_of_step": lf_ms_step / (dev_ms / args.steps) if dev_ms else None,
+                         "gather64_gbs_4GiB": g_big, "gather64_gbs_index_sized": g_idx,
+                         "frac_of_gather64": (achieved / g_big) if g_big else None,
+                         "canonical_model": {"I": st_c["I"], "S": st_c["S"], "E": st_c["E"], "L": st_c["L"], "O": st_c["O"],
+                                             "bytes_per_step": canon, "bytes_per_pattern": canon / args.npat,
+                                             "GBps_over_whole_step": canon / (dev_ms / args.steps * 1e-3) / 1e9}},
+        }
+    idx.close()
+    if rank == 0 and world == 1 and not args.no_cpu:
+        try:
+            out["cpu_baseline"] = cpu_reference_run(base, pats, args.cpu_seconds, os.cpu_count() or 1, "locate (RECOVERBW=1)")
+        except Exception as e:
+            out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": "failed: %r" % (e,)}
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+        if not args.keep and not os.environ.get("EDSBWT_BENCH_KEEP"):
+            pass        # index files stay in the work dir for the reference arm that the driver runs next
+    return 0
+
+
+def reference_arm(args, eb, synth, workdir, base, done_flag):
+    """--impl reference: the reference's CPU search, all host cores, same index / pattern recipe."""
+    os.makedirs(workdir, exist_ok=True)
+    if not os.path.exists(done_flag):
+        import torch
+        if not torch.cuda.is_available():
+            print(json.dumps({"impl": "reference", "unavailable": "index files for cfg4 are built by the GPU suffix sorter; no CUDA device here"}))
+            return 0
+        build_index_files(eb, synth, args, base)
+        open(done_flag, "w").close()
+    col = synth.chromosome_eds(args.mbp, seed=4)
+    pats = synth.sample_patterns(col, min(args.npat, 200000), args.plen, seed=44)
+    del col
+    cores = os.cpu_count() or 1
+    vals, secs = [], []
+    base_info = None
+    for it in range(args.warmup + args.steps):
+        r = cpu_reference_run(base, pats[it * 4096:], args.cpu_seconds, cores, "locate (RECOVERBW=1), step %d" % it)
+        if it >= args.warmup:
+            vals.append(r["value"]); secs.append(r["search_seconds"]); base_info = r
+    v = float(np.mean(vals))
+    out = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": float(np.mean(secs)) * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
+           "data": "synthetic", "config": {"workload": workload_name(args)},
+           "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": base_info["kind"], "sample": base_info["sample"]},
+           "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

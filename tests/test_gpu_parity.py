@@ -125,3 +125,65 @@ def test_csv_and_pattern_file(eb, tmp_path):
     header, rows = E.read_csv_rows(pf + "output.csv")
     assert header == "#Pat\t$_i\tD[i]\tS_j\tS_j[r]\n"
     assert sorted(rows) == sorted(g["rows_reference_order"])
+
+
+# ---- GPU index builder (edsbwt_build_from_collection / _from_eds): byte-identical files -------------------------
+def _files(base):
+    out = {}
+    for suf in ["_info.aux", ".bitvector"] + ["_bwt_%d.aux" % p for p in range(8)] + ["_bv_%d.aux" % p for p in range(8)]:
+        if os.path.exists(base + suf):
+            with open(base + suf, "rb") as f:
+                out[suf] = f.read()
+    return out
+
+
+def _builder_cases():
+    rng = np.random.default_rng(77)
+    cases = [E.parse_eds(load_golden(n)["eds"]) for n in golden_names()]
+    cases.append(E.random_eds(rng, n_seg=3000, max_var=6, max_len=7, p_empty=0.2, nondeg_len=(1, 60)))
+    # long repeats: many doubling rounds, duplicate strings, strings that are prefixes/suffixes of each other
+    cases.append([[b"A" * 300], [b"A" * 299, b"A" * 300, b"", b"A"], [b"ACAC" * 80, b"CACA" * 80, b"ACAC" * 80], [b"A" * 150 + b"C"]])
+    cases.append([[b"ACGT" * 50, b"ACGT" * 50], [b"T"], [b"ACGT" * 49 + b"ACG", b""], [b"GT" * 100]])
+    cases.append([[b"AC"], [b"C", b"A"]])                                  # two letters only
+    cases.append([[b"A"], [b"AA", b""], [b"AAA"]])                         # one letter
+    return cases
+
+
+@pytest.mark.parametrize("case", range(len(_builder_cases())))
+def test_builder_files_identical_to_oracle_writer(eb, tmp_path, case):
+    segs = _builder_cases()[case]
+    ix, base = _index_files(tmp_path, segs, "ora")
+    synth = importlib.import_module("eds-bwt_b200.synth")
+    col = synth.from_segments(segs)
+    gbase = str(tmp_path / "gpu")
+    eb.build_from_collection(col.letters, col.str_off, col.seg_first, gbase)
+    a, b = _files(base), _files(gbase)
+    assert sorted(a) == sorted(b)
+    for k in a:
+        assert a[k] == b[k], k
+    # the .eds text route
+    eds = str(tmp_path / "x.eds")
+    with open(eds, "wb") as f:
+        f.write(E.format_eds([[s if s else b"E" for s in seg] if len(seg) == 1 else seg for seg in segs]))
+    ebase = str(tmp_path / "eds")
+    eb.build_from_eds(eds, ebase)
+    assert _files(ebase) == a
+
+
+def test_synthetic_generators_search_parity(eb, oracle_built, tmp_path):
+    """cfg3-shaped and cfg4-shaped workloads at reduced scale: GPU builder -> GPU search vs the oracle."""
+    synth = importlib.import_module("eds-bwt_b200.synth")
+    for col, npat in [(synth.sarscov2_like_eds(600, seed=3), 3000), (synth.chromosome_eds(0.2, seed=4), 3000)]:
+        base = str(tmp_path / col.name.replace(".", "_"))
+        eb.build_from_collection(col.letters, col.str_off, col.seg_first, base)
+        pats = synth.sample_patterns(col, npat, 32, seed=33)
+        pf = base + ".pat"
+        with open(pf, "wb") as f:
+            for r in pats:
+                f.write(r.tobytes() + b"\n")
+        c_port, rows_port, _ = oracle_built.run_port(base, pf, locate=True)
+        with eb.Index(base) as idx:
+            counts, occ = idx.search(synth.pack_fixed(pats), locate=True)
+        assert counts.tolist() == c_port
+        assert eb.occ_rows(occ) == sorted(rows_port)
+        assert sum(c_port) > 0.5 * npat
