@@ -252,9 +252,11 @@ def main():
     sampler.start()
     dev_ms, lf_ms, loc_ms, launches = 0.0, 0.0, 0.0, 0
     t0 = time.perf_counter()
+    torch.cuda.nvtx.range_push("timed")
     for _ in range(args.steps):
         st, _ = step_device()
         dev_ms += st["total_ms"]; lf_ms += st["lf_kernel_ms"]; loc_ms += st["locate_kernel_ms"]; launches += st["kernel_launches"]
+    torch.cuda.nvtx.range_pop()
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop()
