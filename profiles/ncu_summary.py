@@ -1,0 +1,63 @@
+#!/usr/bin/env python
+"""Turns ncu outputs brought back in gpurun_out/ into the small text summaries committed under profiles/.
+
+  python profiles/ncu_summary.py launches <launches.csv>            per-kernel totals / shares of a launch list
+  python profiles/ncu_summary.py raw <file.ncu-rep> [kernel-regex]   key counters of a --set full capture
+"""
+import collections
+import csv
+import re
+import subprocess
+import sys
+
+KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_sector_hit_rate.pct", "l1tex__t_sector_hit_rate.pct",
+        "lts__t_bytes.sum", "sm__warps_active.avg.pct_of_peak_sustained_active", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "launch__registers_per_thread", "launch__grid_size", "launch__block_size", "launch__occupancy_limit_registers",
+        "launch__occupancy_limit_shared_mem", "sm__maximum_warps_per_active_cycle_pct",
+        "smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct", "smsp__warp_issue_stalled_short_scoreboard_per_warp_active.pct",
+        "smsp__warp_issue_stalled_lg_throttle_per_warp_active.pct", "smsp__warp_issue_stalled_barrier_per_warp_active.pct",
+        "smsp__warp_issue_stalled_wait_per_warp_active.pct", "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum",
+        "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum", "smsp__inst_executed.sum", "dram__sectors_read.sum",
+        "lts__t_sectors_srcunit_tex_op_read.sum"]
+
+
+def launches(path):
+    with open(path) as f:
+        lines = [l for l in f if not l.startswith("==")]
+    agg = collections.defaultdict(lambda: [0, 0.0])
+    for row in csv.DictReader(lines):
+        if row.get("Metric Name") != "gpu__time_duration.sum":
+            continue
+        v = float(row["Metric Value"].replace(",", ""))
+        v *= {"ns": 1.0, "us": 1e3, "ms": 1e6, "s": 1e9}.get(row["Metric Unit"], 1.0)
+        name = re.sub(r"\(.*", "", row["Kernel Name"])[:70]
+        agg[name][0] += 1
+        agg[name][1] += v
+    tot = sum(v[1] for v in agg.values())
+    print("# %s : %d launches, %.3f ms summed device time (cold-cache, serialised: compare shares)" % (
+        path, sum(v[0] for v in agg.values()), tot / 1e6))
+    for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        print("%-72s %6d launches %10.3f ms %6.2f%%" % (k, v[0], v[1] / 1e6, 100 * v[1] / tot))
+
+
+def raw(path, pat=None):
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    r = list(csv.reader(out.splitlines()))
+    h, units = r[0], r[1]
+    for row in r[2:]:
+        name = row[h.index("Kernel Name")]
+        if pat and not re.search(pat, name):
+            continue
+        print("## " + name[:100])
+        for k in KEYS:
+            if k in h:
+                i = h.index(k)
+                print("  %-72s %s %s" % (k, row[i], units[i]))
+
+
+if __name__ == "__main__":
+    if sys.argv[1] == "launches":
+        launches(sys.argv[2])
+    else:
+        raw(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else None)
