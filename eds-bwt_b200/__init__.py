@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(HERE, "libedsbwt_cuda.so")
 
 LOCATE_SA, LOCATE_WALK = 0, 1
 LF_RANK, LF_MOVE = 0, 1
+ENGINE_FUSED, ENGINE_LEVELSYNC = 0, 1
 
 OCC_DTYPE = np.dtype([("pat", "<u4"), ("str", "<u4"), ("seg", "<u4"), ("idx_in_seg", "<u4"), ("off", "<u4")])
 
@@ -34,14 +35,15 @@ class Info(C.Structure):
 
 class OpenOpts(C.Structure):
     _fields_ = [("seed_k", C.c_int32), ("locate_mode", C.c_int32), ("verify", C.c_int32), ("build_move", C.c_int32),
-                ("reserved", C.c_int32 * 4)]
+                ("engine", C.c_int32), ("fused_cap", C.c_int32), ("reserved", C.c_int32 * 2)]
 
 
 class Stats(C.Structure):
     _fields_ = [("I", C.c_uint64), ("S", C.c_uint64), ("E", C.c_uint64), ("L", C.c_uint64), ("O", C.c_uint64),
                 ("steps", C.c_uint64), ("kernel_launches", C.c_uint64), ("lf_intervals", C.c_uint64),
                 ("lf_kernel_ms", C.c_double), ("locate_kernel_ms", C.c_double), ("total_ms", C.c_double),
-                ("frontier_peak", C.c_uint64)]
+                ("frontier_peak", C.c_uint64), ("occ_blocks", C.c_uint64), ("overflow_patterns", C.c_uint64),
+                ("search_kernel_ms", C.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -112,9 +114,11 @@ def pack_patterns(patterns):
 class Index:
     """Device-resident EDS-BWT index (edsbwt_index_open_ex)."""
 
-    def __init__(self, base, device=0, seed_k=-1, locate_mode=LOCATE_SA, verify=True, build_move=False):
+    def __init__(self, base, device=0, seed_k=-1, locate_mode=LOCATE_SA, verify=True, build_move=False,
+                 engine=ENGINE_FUSED, fused_cap=0):
         self._h = C.c_void_p()
-        o = OpenOpts(seed_k=seed_k, locate_mode=locate_mode, verify=int(verify), build_move=int(build_move))
+        o = OpenOpts(seed_k=seed_k, locate_mode=locate_mode, verify=int(verify), build_move=int(build_move),
+                     engine=engine, fused_cap=fused_cap)
         _check(lib().edsbwt_index_open_ex(os.fsencode(base), device, C.byref(o), C.byref(self._h)))
         self.device = device
 

@@ -83,23 +83,44 @@ __global__ void occ_counts_kernel(uint4* __restrict__ occ, const uint4* __restri
 // SA table: row -> (string, offset), by walking every string backwards from its end-marker row
 // (the inverse of the reference's locate rounds, findMultipleDollarsBackward :349-603)
 // ===================================================================================================
-__global__ void sa_walk_kernel(IndexView ix, uint32_t* __restrict__ sa_str, uint32_t* __restrict__ sa_dist, uint32_t* __restrict__ slen) {
+__global__ void sa_walk_kernel(IndexView ix, uint2* __restrict__ sa, uint32_t* __restrict__ slen) {
     uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= ix.n_text) return;
     uint32_t row = w, d = 0;                     // pile-0 row w is the suffix "$_w"
+    sa[w] = make_uint2(w, 0);                    // end-marker rows: (string, distance 0); never read by locate
     for (;;) {
         uint32_t s = occ_symbol(ix.occ, row);
         if (s == 0) break;
         row = ix.Cl[s - 1] + occ_rank1(ix.occ, row, (int)s - 1);
         ++d;
-        sa_str[row] = w; sa_dist[row] = d;
+        sa[row] = make_uint2(w, d);              // d = distance to the end of the string
     }
     slen[w] = d;
 }
-__global__ void sa_offset_kernel(uint32_t n_text, uint32_t n, const uint32_t* __restrict__ sa_str, uint32_t* __restrict__ sa_off, const uint32_t* __restrict__ slen) {
+__global__ void sa_offset_kernel(uint32_t n_text, uint32_t n, uint2* __restrict__ sa, const uint32_t* __restrict__ slen) {
     uint32_t row = n_text + blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n) return;
-    sa_off[row] = slen[sa_str[row]] - sa_off[row];
+    uint2 v = sa[row];
+    sa[row] = make_uint2(v.x, slen[v.x] - v.y);
+}
+// link_rec[r] for the r-th end-marker row of the eBWT (EOF_ID order): everything link() derives from it
+// (preceding_dollars_finder :1287-1307 + the empty-string closure :1255); str_info[w] = (segment, index in segment)
+__global__ void link_rec_kernel(IndexView ix, uint2* __restrict__ link_rec, uint2* __restrict__ str_info) {
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= ix.n_text) return;
+    uint32_t w = ix.eof_flat[r];
+    uint2 rec = make_uint2(1u, 0u);              // x > y: no predecessor
+    if (w > ix.fsi) {
+        uint32_t sg = ix.str_seg[w] - 1;         // previous segment
+        rec = make_uint2(ix.seg_first[ix.seg_low[sg]], ix.seg_first[sg + 1] - 1);
+    }
+    link_rec[r] = rec;
+    uint32_t sg = ix.str_seg[r];                 // r doubles as a string index for str_info
+    str_info[r] = make_uint2(sg, r - ix.seg_first[sg]);
+}
+__global__ void zip_kernel(const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi, uint32_t n, uint2* __restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = make_uint2(lo[i], hi[i]);
 }
 
 // ===================================================================================================
@@ -110,11 +131,12 @@ struct PatView {
     const uint32_t* len;     // 0 for patterns that cannot match (bad character / empty)
     uint32_t words, npat, k; // k = seed depth used for this batch
 };
-__global__ void encode_patterns_kernel(const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ off, uint32_t npat, Lut lut,
-                                       uint32_t words, uint64_t* __restrict__ pack, uint32_t* __restrict__ len) {
+__global__ void encode_patterns_kernel(const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ off, const uint32_t* __restrict__ ids,
+                                       uint32_t npat, Lut lut, uint32_t words, uint64_t* __restrict__ pack, uint32_t* __restrict__ len) {
     uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= npat) return;
-    uint64_t a = off[q], b = off[q + 1];
+    uint32_t g = ids ? ids[q] : q;               // local pattern q of this pass = pattern g of the batch
+    uint64_t a = off[g], b = off[g + 1];
     uint32_t m = (uint32_t)(b - a);
     bool ok = m > 0;
     uint64_t wv = 0;
@@ -133,7 +155,6 @@ __device__ __forceinline__ uint32_t pat_char(const PatView& pv, uint32_t q, uint
 // ===================================================================================================
 // seed table
 // ===================================================================================================
-struct SeedView { const uint32_t* off[17]; const uint32_t* lo[17]; const uint32_t* hi[17]; };
 
 // number of seed intervals of each pattern + where they start inside the level
 __global__ void seed_count_kernel(PatView pv, SeedView sv, uint32_t* __restrict__ cnt, uint32_t* __restrict__ src) {
@@ -155,14 +176,15 @@ __global__ void seed_scatter_kernel(PatView pv, SeedView sv, const uint32_t* __r
     uint32_t m = pv.len[q];
     uint32_t L = m < pv.k ? m : pv.k;
     uint32_t j = src[q] + (t - base[q]);
-    fpat[t] = q; flo[t] = __ldg(sv.lo[L] + j); fhi[t] = __ldg(sv.hi[L] + j);
+    uint2 v = __ldg(sv.iv[L] + j);
+    fpat[t] = q; flo[t] = v.x; fhi[t] = v.y;
 }
 // level L -> the 4 children of every key, grouped by child key (4*key + c)
-__global__ void seed_expand_kernel(const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi,
+__global__ void seed_expand_kernel(const uint32_t* __restrict__ pat, const uint2* __restrict__ iv,
                                    const uint32_t* __restrict__ off, uint32_t nF, uint32_t* __restrict__ opat, uint32_t* __restrict__ olo, uint32_t* __restrict__ ohi) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nF) return;
-    uint32_t key = pat[i], a = off[key], cnt = off[key + 1] - a, r = i - a, l = lo[i], h = hi[i];
+    uint32_t key = pat[i], a = off[key], cnt = off[key + 1] - a, r = i - a, l = iv[i].x, h = iv[i].y;
     #pragma unroll
     for (uint32_t c = 0; c < 4; ++c) { uint32_t d = 4 * a + c * cnt + r; opat[d] = 4 * key + c; olo[d] = l; ohi[d] = h; }
 }
@@ -330,39 +352,54 @@ __global__ void combine_kernel(const uint32_t* __restrict__ fpat, const uint32_t
 }
 
 // ---- results ----------------------------------------------------------------------------------------
-__global__ void interval_len_kernel(const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi, uint32_t nF,
-                                    uint32_t* __restrict__ len, uint32_t* __restrict__ counts) {
+// level-synchronous frontier (grouped by LOCAL pattern index) -> staging slots + per-pattern list / count of the batch
+__global__ void ls_finalize_kernel(const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo, const uint32_t* __restrict__ hi, uint32_t nF,
+                                   const uint32_t* __restrict__ ids, uint32_t sbase, uint2* __restrict__ staging, uint2* __restrict__ plist,
+                                   uint32_t* __restrict__ counts) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nF) return;
-    uint32_t l = hi[i] - lo[i] + 1;
-    len[i] = l;
-    atomicAdd(counts + pat[i], l);                       // "Found N", EDSBWTsearch.cpp:739-746
+    uint32_t q = pat[i], l = lo[i], h = hi[i];
+    staging[sbase + i] = make_uint2(l, h);
+    uint32_t g = ids ? ids[q] : q;
+    atomicAdd(counts + g, h - l + 1);                    // "Found N", EDSBWTsearch.cpp:739-746
+    if (i == 0 || pat[i - 1] != q) {                     // head of the pattern's run: list start + length
+        uint32_t e = upper_bound_u32(pat, nF, q);
+        plist[g] = make_uint2(sbase + i, e - i);
+    }
 }
 // one thread per occurrence row: (string, offset) by table lookup or by LF-walk, then segment / index in segment
-// (indices_of_dollars_in_interval, EDSBWTsearch.cpp:1310-1332)
+// (indices_of_dollars_in_interval, EDSBWTsearch.cpp:1310-1332).  Output grouped by ascending pattern.
 template <bool WALK>
-__global__ void locate_kernel(IndexView ix, const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo, const uint32_t* __restrict__ rofs,
-                              uint32_t nF, uint64_t nocc, edsbwt_occ* __restrict__ out, StatsDev* __restrict__ st) {
+__global__ void locate_kernel(IndexView ix, const uint2* __restrict__ plist, const uint32_t* __restrict__ occ_ofs, const uint2* __restrict__ staging,
+                              uint32_t npat, uint64_t nocc, edsbwt_occ* __restrict__ out, StatsDev* __restrict__ st) {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t steps = 0;
     if (t < nocc) {
-        uint32_t i = upper_bound_u32(rofs, nF + 1, (uint32_t)t) - 1;
-        uint32_t row = lo[i] + ((uint32_t)t - rofs[i]);
-        uint32_t w, r;
+        uint32_t q = upper_bound_u32(occ_ofs, npat + 1, (uint32_t)t) - 1;
+        uint32_t r = (uint32_t)t - __ldg(occ_ofs + q);
+        uint2 pl = __ldg(plist + q);
+        uint32_t row = 0;
+        for (uint32_t j = 0; j < pl.y; ++j) {
+            uint2 iv = __ldg(staging + pl.x + j);
+            uint32_t len = iv.y - iv.x + 1;
+            if (r < len) { row = iv.x + r; break; }
+            r -= len;
+        }
+        uint32_t w, off;
         if (WALK) {
-            r = 0;
+            off = 0;
             for (;;) {
-                uint32_t s = occ_symbol(ix.occ, row);
-                if (s == 0) break;
-                row = ix.Cl[s - 1] + occ_rank1(ix.occ, row, (int)s - 1);
-                ++r;
+                uint32_t sy = occ_symbol(ix.occ, row);
+                if (sy == 0) break;
+                row = ix.Cl[sy - 1] + occ_rank1(ix.occ, row, (int)sy - 1);
+                ++off;
             }
             w = __ldg(ix.eof_flat + occ_rank_eof(ix.occ, row));
-        } else { w = __ldg(ix.sa_str + row); r = __ldg(ix.sa_off + row); }
-        uint32_t seg = __ldg(ix.str_seg + w);
-        edsbwt_occ o; o.pat = pat[i]; o.str = w; o.seg = seg; o.idx_in_seg = w - __ldg(ix.seg_first + seg); o.off = r;
+        } else { uint2 v = __ldg(ix.sa + row); w = v.x; off = v.y; }
+        uint2 si = __ldg(ix.str_info + w);
+        edsbwt_occ o; o.pat = q; o.str = w; o.seg = si.x; o.idx_in_seg = si.y; o.off = off;
         out[t] = o;
-        steps = r + 1;
+        steps = off + 1;
     }
     if (st) { warp_add(&st->L, steps); warp_add(&st->O, steps ? 1u : 0u); }
 }
@@ -383,13 +420,16 @@ struct Workspace {
     DevBuf<uint64_t> keys, keys2, ppack;
     DevBuf<uint8_t> cubtmp;
     DevBuf<unsigned int> scalars;        // [0] nvalid
+    DevBuf<uint2> plist, staging;        // per-pattern final lists (fused + level-synchronous results)
+    DevBuf<uint32_t> fcursor, ovf_ids, occ_ofs;
     StatsDev* d_stats = nullptr;
     uint32_t* h_pin = nullptr;           // pinned read-back area
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr, evf0 = nullptr, evf1 = nullptr, evl0 = nullptr, evl1 = nullptr;
     uint64_t launches = 0;
     double lf_ms = 0;
     ~Workspace() { if (d_stats) cudaFree(d_stats); if (h_pin) cudaFreeHost(h_pin); if (ev0) cudaEventDestroy(ev0); if (ev1) cudaEventDestroy(ev1);
-                   if (evk0) cudaEventDestroy(evk0); if (evk1) cudaEventDestroy(evk1); }
+                   if (evk0) cudaEventDestroy(evk0); if (evk1) cudaEventDestroy(evk1); if (evf0) cudaEventDestroy(evf0); if (evf1) cudaEventDestroy(evf1);
+                   if (evl0) cudaEventDestroy(evl0); if (evl1) cudaEventDestroy(evl1); }
 };
 
 Index::~Index() {
@@ -398,8 +438,8 @@ Index::~Index() {
     if (stream) cudaStreamDestroy(stream);
 }
 uint64_t Index::device_bytes() const {
-    uint64_t b = occ.bytes() + eof_flat.bytes() + str_seg.bytes() + seg_first.bytes() + seg_low.bytes() + sa_str.bytes() + sa_off.bytes();
-    for (SeedLevel* s : seed) if (s) b += s->off.bytes() + s->lo.bytes() + s->hi.bytes();
+    uint64_t b = occ.bytes() + eof_flat.bytes() + str_seg.bytes() + seg_first.bytes() + seg_low.bytes() + sa.bytes() + link_rec.bytes() + str_info.bytes();
+    for (SeedLevel* s : seed) if (s) b += s->off.bytes() + s->iv.bytes();
     return b;
 }
 
@@ -521,10 +561,11 @@ static void build_seed_table(Index& ix, uint32_t k) {
         }
         off[4] = (uint32_t)lo.size();
         SeedLevel* L1 = new SeedLevel; ix.seed[1] = L1;
-        L1->off.ensure(5); L1->lo.ensure(lo.size() + 1); L1->hi.ensure(lo.size() + 1); L1->n_iv = lo.size();
+        std::vector<uint2> iv(lo.size());
+        for (size_t i = 0; i < lo.size(); ++i) iv[i] = make_uint2(lo[i], hi[i]);
+        L1->off.ensure(5); L1->iv.ensure(lo.size() + 1); L1->n_iv = lo.size();
         CUDA_OK(cudaMemcpyAsync(L1->off.p, off.data(), 20, cudaMemcpyHostToDevice, s));
-        if (!lo.empty()) { CUDA_OK(cudaMemcpyAsync(L1->lo.p, lo.data(), lo.size() * 4, cudaMemcpyHostToDevice, s));
-                           CUDA_OK(cudaMemcpyAsync(L1->hi.p, hi.data(), hi.size() * 4, cudaMemcpyHostToDevice, s)); }
+        if (!iv.empty()) CUDA_OK(cudaMemcpyAsync(L1->iv.p, iv.data(), iv.size() * 8, cudaMemcpyHostToDevice, s));
         CUDA_OK(cudaStreamSynchronize(s));
         ix.seed_intervals = lo.size();
     }
@@ -541,17 +582,14 @@ static void build_seed_table(Index& ix, uint32_t k) {
             // key of interval i = upper_bound(off, i) - 1
             ws.src.ensure(nF);
             level_keys_kernel<<<grid_for(nF, 256), 256, 0, s>>>(cur->off.p, nkeys, nF, ws.src.p);
-            seed_expand_kernel<<<grid_for(nF, 256), 256, 0, s>>>(ws.src.p, cur->lo.p, cur->hi.p, cur->off.p, nF, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p);
+            seed_expand_kernel<<<grid_for(nF, 256), 256, 0, s>>>(ws.src.p, cur->iv.p, cur->off.p, nF, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p);
             ws.launches += 2;
             newF = engine_step<true>(ix, ws, pv, 0, (uint32_t)nE, nullptr, 0, false);
         }
         SeedLevel* nx = new SeedLevel; ix.seed[L + 1] = nx;
         uint32_t nk2 = nkeys * 4;
-        nx->off.ensure((size_t)nk2 + 1); nx->lo.ensure(newF + 1); nx->hi.ensure(newF + 1); nx->n_iv = newF;
-        if (newF) {
-            CUDA_OK(cudaMemcpyAsync(nx->lo.p, ws.cur.lo.p, (size_t)newF * 4, cudaMemcpyDeviceToDevice, s));
-            CUDA_OK(cudaMemcpyAsync(nx->hi.p, ws.cur.hi.p, (size_t)newF * 4, cudaMemcpyDeviceToDevice, s));
-        }
+        nx->off.ensure((size_t)nk2 + 1); nx->iv.ensure(newF + 1); nx->n_iv = newF;
+        if (newF) zip_kernel<<<grid_for(newF, 256), 256, 0, s>>>(ws.cur.lo.p, ws.cur.hi.p, newF, nx->iv.p);
         key_offsets_kernel<<<grid_for((size_t)nk2 + 1, 256), 256, 0, s>>>(ws.cur.pat.p, newF, nk2, nx->off.p);
         CUDA_OK(cudaStreamSynchronize(s));
         ix.seed_intervals += newF;
@@ -568,6 +606,12 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     CUDA_OK(cudaMalloc(&ws.d_stats, sizeof(StatsDev)));
     CUDA_OK(cudaMallocHost(&ws.h_pin, 256));
     CUDA_OK(cudaEventCreate(&ws.ev0)); CUDA_OK(cudaEventCreate(&ws.ev1)); CUDA_OK(cudaEventCreate(&ws.evk0)); CUDA_OK(cudaEventCreate(&ws.evk1));
+    CUDA_OK(cudaEventCreate(&ws.evf0)); CUDA_OK(cudaEventCreate(&ws.evf1)); CUDA_OK(cudaEventCreate(&ws.evl0)); CUDA_OK(cudaEventCreate(&ws.evl1));
+    ix.engine = o.engine == EDSBWT_ENGINE_LEVELSYNC ? EDSBWT_ENGINE_LEVELSYNC : EDSBWT_ENGINE_FUSED;
+    ix.fused_cap = o.fused_cap > 0 ? (uint32_t)o.fused_cap : 24u;
+    if (ix.fused_cap < 4) ix.fused_cap = 4;
+    if (ix.fused_cap > 192) ix.fused_cap = 192;             // 192 slots x 128 threads x 8 B = 192 KB of shared memory per CTA
+    { Lut l = make_lut(h); ix.lut.ensure(256); CUDA_OK(cudaMemcpyAsync(ix.lut.p, l.code, 256, cudaMemcpyHostToDevice, s)); CUDA_OK(cudaStreamSynchronize(s)); }
     ws.scalars.ensure(16);
 
     IndexView& v = ix.view;
@@ -629,17 +673,22 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
         CUDA_OK(cudaStreamSynchronize(s));
     }
     v.eof_flat = ix.eof_flat.p; v.str_seg = ix.str_seg.p; v.seg_first = ix.seg_first.p; v.seg_low = ix.seg_low.p;
+    // ---- link records + string info (one gather each in the hot kernels)
+    ix.link_rec.ensure((size_t)h.n_text + 1); ix.str_info.ensure((size_t)h.n_text + 1);
+    link_rec_kernel<<<grid_for(h.n_text, 256), 256, 0, s>>>(v, ix.link_rec.p, ix.str_info.p);
+    v.link_rec = ix.link_rec.p; v.str_info = ix.str_info.p;
     // ---- SA table
     ix.locate_mode = o.locate_mode == EDSBWT_LOCATE_WALK ? EDSBWT_LOCATE_WALK : EDSBWT_LOCATE_SA;
     if (ix.locate_mode == EDSBWT_LOCATE_SA) {
-        ix.sa_str.ensure((size_t)h.n + 1); ix.sa_off.ensure((size_t)h.n + 1);
+        ix.sa.ensure((size_t)h.n + 1);
         DevBuf<uint32_t> slen; slen.ensure(h.n_text + 1);
-        CUDA_OK(cudaMemsetAsync(ix.sa_str.p, 0xff, (size_t)h.n * 4, s));
-        sa_walk_kernel<<<grid_for(h.n_text, 128), 128, 0, s>>>(v, ix.sa_str.p, ix.sa_off.p, slen.p);
-        if (h.n > h.n_text) sa_offset_kernel<<<grid_for(h.n - h.n_text, 256), 256, 0, s>>>(h.n_text, h.n, ix.sa_str.p, ix.sa_off.p, slen.p);
+        CUDA_OK(cudaMemsetAsync(ix.sa.p, 0xff, (size_t)h.n * 8, s));
+        sa_walk_kernel<<<grid_for(h.n_text, 128), 128, 0, s>>>(v, ix.sa.p, slen.p);
+        if (h.n > h.n_text) sa_offset_kernel<<<grid_for(h.n - h.n_text, 256), 256, 0, s>>>(h.n_text, h.n, ix.sa.p, slen.p);
         CUDA_OK(cudaStreamSynchronize(s));
-        v.sa_str = ix.sa_str.p; v.sa_off = ix.sa_off.p;
+        v.sa = ix.sa.p;
     }
+    CUDA_OK(cudaStreamSynchronize(s));
     // ---- seed table
     int k = o.seed_k;
     if (k < 0) { k = 1; while (k < 12 && (1ull << (2 * (k + 2))) <= (uint64_t)h.n) ++k; }
@@ -656,6 +705,38 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
 // ---------------------------------------------------------------------------------------------------
 // batched search
 // ---------------------------------------------------------------------------------------------------
+// Level-synchronous search of a subset (ids == nullptr: the whole batch).  Leaves the final frontier, grouped by LOCAL
+// pattern index, in ws.cur and returns its length.
+static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, const uint32_t* ids, uint32_t nsub, uint32_t max_len,
+                                 StatsDev* st, uint32_t& steps, uint64_t& peak) {
+    Workspace& ws = *ix.ws;
+    cudaStream_t s = ix.stream;
+    uint32_t words = (max_len + 31) / 32; if (!words) words = 1;
+    ws.ppack.ensure((size_t)nsub * words); ws.plen.ensure(nsub);
+    Lut lut = make_lut(ix.host);
+    encode_patterns_kernel<<<grid_for(nsub, 128), 128, 0, s>>>(d_bytes, d_off, ids, nsub, lut, words, ws.ppack.p, ws.plen.p);
+    PatView pv{ws.ppack.p, ws.plen.p, words, nsub, ix.seed_k};
+    SeedView sv{};
+    for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; }
+    ws.cnt.ensure(nsub + 1); ws.src.ensure(nsub); ws.base.ensure(nsub + 1);
+    seed_count_kernel<<<grid_for(nsub, 256), 256, 0, s>>>(pv, sv, ws.cnt.p, ws.src.p);
+    CUDA_OK(cudaMemsetAsync(ws.cnt.p + nsub, 0, 4, s));
+    exclusive_sum(ws, ws.cnt.p, ws.base.p, (size_t)nsub + 1, s);
+    ws.launches += 2;
+    uint32_t nF = read_u32(ws, ws.base.p + nsub, s);
+    ws.cur.ensure(nF ? nF : 1);
+    if (nF) { seed_scatter_kernel<<<grid_for(nF, 256), 256, 0, s>>>(pv, sv, ws.base.p, ws.src.p, nF, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p); ws.launches += 1; }
+    if (nF > peak) peak = nF;
+    uint32_t total_steps = max_len > ix.seed_k ? max_len - ix.seed_k : 0;
+    for (uint32_t t = 0; t < total_steps && nF; ++t) {
+        nF = engine_step<false>(ix, ws, pv, t, nF, st, ix.canonical_k, true);
+        ++steps;
+        if (nF > peak) peak = nF;
+    }
+    if (st && nF) { count_I_kernel<<<grid_for(nF, 256), 256, 0, s>>>(pv, steps, ws.cur.pat.p, nF, st, ix.canonical_k); ws.launches += 1; }
+    return nF;
+}
+
 void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat, uint64_t total_bytes, uint32_t max_len,
                 bool locate, int lf_variant, SearchOut& out) {
     if (lf_variant != EDSBWT_LF_RANK) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "move-table LF variant not built into this handle");
@@ -671,54 +752,71 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     CUDA_OK(cudaEventRecord(ws.ev0, s));
     out.npat = npat; out.nocc = 0;
     out.counts.ensure(npat ? npat : 1);
-    CUDA_OK(cudaMemsetAsync(out.counts.p, 0, (size_t)(npat ? npat : 1) * 4, s));
-    uint32_t nF = 0, steps = 0; uint64_t peak = 0;
+    uint32_t steps = 0, novf = 0; uint64_t peak = 0;
+    bool fused_ran = false, locate_ran = false;
     if (npat) {
-        // encode
-        uint32_t words = (max_len + 31) / 32; if (!words) words = 1;
-        ws.ppack.ensure((size_t)npat * words); ws.plen.ensure(npat);
-        Lut lut = make_lut(ix.host);
-        encode_patterns_kernel<<<grid_for(npat, 128), 128, 0, s>>>(d_bytes, d_off, npat, lut, words, ws.ppack.p, ws.plen.p);
-        PatView pv{ws.ppack.p, ws.plen.p, words, npat, ix.seed_k};
-        // seed lookup
-        SeedView sv{};
-        for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.lo[L] = ix.seed[L]->lo.p; sv.hi[L] = ix.seed[L]->hi.p; }
-        ws.cnt.ensure(npat + 1); ws.src.ensure(npat); ws.base.ensure(npat + 1);
-        seed_count_kernel<<<grid_for(npat, 256), 256, 0, s>>>(pv, sv, ws.cnt.p, ws.src.p);
-        CUDA_OK(cudaMemsetAsync(ws.cnt.p + npat, 0, 4, s));
-        exclusive_sum(ws, ws.cnt.p, ws.base.p, (size_t)npat + 1, s);
-        ws.launches += 2;
-        nF = read_u32(ws, ws.base.p + npat, s);
-        ws.cur.ensure(nF ? nF : 1);
-        if (nF) { seed_scatter_kernel<<<grid_for(nF, 256), 256, 0, s>>>(pv, sv, ws.base.p, ws.src.p, nF, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p); ws.launches += 1; }
-        peak = nF;
-        uint32_t total_steps = max_len > ix.seed_k ? max_len - ix.seed_k : 0;
-        for (uint32_t t = 0; t < total_steps && nF; ++t) {
-            nF = engine_step<false>(ix, ws, pv, t, nF, st, ix.canonical_k, true);
-            ++steps;
-            if (nF > peak) peak = nF;
+        ws.plist.ensure(npat); ws.fcursor.ensure(4);
+        CUDA_OK(cudaMemsetAsync(ws.fcursor.p, 0, 16, s));
+        uint32_t nstage = 0;
+        const uint32_t* ids = nullptr;
+        if (ix.engine == EDSBWT_ENGINE_FUSED) {
+            // ---- the hot kernel: one thread per pattern
+            size_t want = (size_t)npat * 2 + (1u << 16);
+            if (want > 0xfffffff0ull) want = 0xfffffff0ull;
+            ws.staging.ensure(want); ws.ovf_ids.ensure(npat);
+            SeedView sv{};
+            for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; }
+            FusedOut fo{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.ovf_ids.p};
+            CUDA_OK(cudaEventRecord(ws.evf0, s));
+            launch_fused_search(ix.view, sv, ix.seed_k, d_bytes, d_off, npat, ix.lut.p, ix.fused_cap, fo, st, ix.canonical_k, s);
+            CUDA_OK(cudaEventRecord(ws.evf1, s));
+            ws.launches += 1; fused_ran = true;
+            CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 8, cudaMemcpyDeviceToHost, s));
+            CUDA_OK(cudaStreamSynchronize(s));
+            nstage = ws.h_pin[0]; novf = ws.h_pin[1];
+            ids = ws.ovf_ids.p;
+        } else {
+            CUDA_OK(cudaMemsetAsync(out.counts.p, 0, (size_t)npat * 4, s));
+            CUDA_OK(cudaMemsetAsync(ws.plist.p, 0, (size_t)npat * 8, s));
+            novf = npat;
         }
-        if (stats && nF) { count_I_kernel<<<grid_for(nF, 256), 256, 0, s>>>(pv, steps, ws.cur.pat.p, nF, st, ix.canonical_k); ws.launches += 1; }
-        // counts (+ locate)
-        if (nF) {
-            ws.len.ensure(nF + 1); ws.dofs.ensure(nF + 2);
-            interval_len_kernel<<<grid_for(nF, 256), 256, 0, s>>>(ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p, nF, ws.len.p, out.counts.p);
-            ws.launches += 1;
-            if (locate) {
-                CUDA_OK(cudaMemsetAsync(ws.len.p + nF, 0, 4, s));
-                exclusive_sum(ws, ws.len.p, ws.dofs.p, (size_t)nF + 1, s);
-                uint32_t nocc = read_u32(ws, ws.dofs.p + nF, s);
-                out.nocc = nocc;
-                if (nocc) {
-                    out.occ.ensure(nocc);
-                    CUDA_OK(cudaEventRecord(ws.evk0, s));
-                    if (ix.locate_mode == EDSBWT_LOCATE_WALK)
-                        locate_kernel<true><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.cur.pat.p, ws.cur.lo.p, ws.dofs.p, nF, nocc, out.occ.p, st);
-                    else
-                        locate_kernel<false><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.cur.pat.p, ws.cur.lo.p, ws.dofs.p, nF, nocc, out.occ.p, st);
-                    CUDA_OK(cudaEventRecord(ws.evk1, s));
-                    ws.launches += 1;
-                }
+        if (novf) {
+            // ---- level-synchronous engine: the whole batch (ENGINE_LEVELSYNC) or the patterns whose frontier outgrew the fused kernel
+            uint32_t nF = levelsync_search(ix, d_bytes, d_off, ids, novf, max_len, st, steps, peak);
+            if (nF) {
+                if ((uint64_t)nstage + nF > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 result intervals in one batch; split the batch");
+                ws.staging.ensure((size_t)nstage + nF, s, true, nstage);
+                ls_finalize_kernel<<<grid_for(nF, 256), 256, 0, s>>>(ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p, nF, ids, nstage, ws.staging.p, ws.plist.p, out.counts.p);
+                ws.launches += 1;
+            }
+        }
+        if (locate) {
+            ws.occ_ofs.ensure((size_t)npat + 2);
+            // exclusive scan of the counts (npat + 1 entries: the last one is the total)
+            size_t tmp = 0;
+            CUDA_OK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, out.counts.p, ws.occ_ofs.p, (int)npat, s));
+            ws.cubtmp.ensure(tmp);
+            CUDA_OK(cub::DeviceScan::ExclusiveSum(ws.cubtmp.p, tmp, out.counts.p, ws.occ_ofs.p, (int)npat, s));
+            ws.launches += 2;
+            // total = ofs[npat-1] + counts[npat-1]
+            CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.occ_ofs.p + (npat - 1), 4, cudaMemcpyDeviceToHost, s));
+            CUDA_OK(cudaMemcpyAsync(ws.h_pin + 1, out.counts.p + (npat - 1), 4, cudaMemcpyDeviceToHost, s));
+            CUDA_OK(cudaStreamSynchronize(s));
+            uint64_t nocc = (uint64_t)ws.h_pin[0] + ws.h_pin[1];
+            if (nocc > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 occurrences in one batch; split the batch");
+            CUDA_OK(cudaMemcpyAsync(ws.occ_ofs.p + npat, ws.h_pin, 0, cudaMemcpyHostToDevice, s));
+            uint32_t tot32 = (uint32_t)nocc;
+            CUDA_OK(cudaMemcpyAsync(ws.occ_ofs.p + npat, &tot32, 4, cudaMemcpyHostToDevice, s));
+            out.nocc = nocc;
+            if (nocc) {
+                out.occ.ensure(nocc);
+                CUDA_OK(cudaEventRecord(ws.evl0, s));
+                if (ix.locate_mode == EDSBWT_LOCATE_WALK)
+                    locate_kernel<true><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, out.occ.p, st);
+                else
+                    locate_kernel<false><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, out.occ.p, st);
+                CUDA_OK(cudaEventRecord(ws.evl1, s));
+                ws.launches += 1; locate_ran = true;
             }
         }
     }
@@ -730,9 +828,11 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     float ms = 0; CUDA_OK(cudaEventElapsedTime(&ms, ws.ev0, ws.ev1));
     edsbwt_stats& ls = ix.last;
     ls = edsbwt_stats{};
-    ls.I = hs.I; ls.S = hs.S; ls.E = hs.E; ls.L = hs.L; ls.O = hs.O; ls.lf_intervals = hs.lf_intervals;
+    ls.I = hs.I; ls.S = hs.S; ls.E = hs.E; ls.L = hs.L; ls.O = hs.O; ls.lf_intervals = hs.lf_intervals; ls.occ_blocks = hs.occ_blocks;
     ls.steps = steps; ls.kernel_launches = ws.launches; ls.lf_kernel_ms = ws.lf_ms; ls.total_ms = ms; ls.frontier_peak = peak;
-    if (locate && out.nocc) { float lm = 0; CUDA_OK(cudaEventElapsedTime(&lm, ws.evk0, ws.evk1)); ls.locate_kernel_ms = lm; }
+    ls.overflow_patterns = ix.engine == EDSBWT_ENGINE_FUSED ? novf : 0;
+    if (fused_ran) { float fm = 0; CUDA_OK(cudaEventElapsedTime(&fm, ws.evf0, ws.evf1)); ls.search_kernel_ms = fm; }
+    if (locate_ran) { float lm = 0; CUDA_OK(cudaEventElapsedTime(&lm, ws.evl0, ws.evl1)); ls.locate_kernel_ms = lm; }
 }
 
 }  // namespace edsbwt

@@ -1,0 +1,219 @@
+// The hot kernel: one thread per pattern runs the WHOLE backward search after the seed lookup.
+//
+//   reference per-pattern loop     EDSBWT::backwardSearch   EDSBWTsearch.cpp:619-772
+//   LF of every frontier interval  updateIntervals / updateSingleInterval / rankManySymbols / MergeAndRemove   :841-1209
+//   segment jump                   link / dollars_in_interval / preceding_dollars_finder   :1212-1307
+//
+// Per thread: the frontier (sorted lists Dol' ++ F' of SURVEY App. B.2) lives in shared memory, `cap` (lo,hi) slots per
+// thread, column-major so that lanes touching the same slot index do not conflict.  Each interval-step is ONE 64-byte Occ
+// block fetched with two 256-bit loads (two when the interval spans blocks): letter rank, '#' rank and '#' count all come
+// out of those 64 bytes.  A '#' inside the frontier costs one 8-byte gather of link_rec[] (the pile-0 range of the
+// preceding segment(s), closure through empty strings included, precomputed at load); the ranges are kept as a sorted,
+// merged set at the top of the thread's slot column and LF-mapped in a second pass, exactly like the reference's
+// vectRangeDollarPile.  Patterns whose lists do not fit are handed to the level-synchronous engine (engine.cu), which has
+// no capacity limit -- still on the GPU.
+#include "internal.cuh"
+
+namespace edsbwt {
+
+namespace {
+
+struct Blk { uint32_t w[16]; };      // w[4j] = count of letter j before the block, w[4j+1] plane0, w[4j+2] plane1, w[4j+3] '#' mask of rows 32j..32j+31
+
+__device__ __forceinline__ void ld256(const void* p, uint32_t* r) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "l"(p));
+}
+__device__ __forceinline__ void load_blk(const uint4* __restrict__ occ, uint32_t blk, Blk& b) {
+    const uint4* p = occ + (size_t)blk * 4;
+    ld256(p, b.w); ld256(p + 2, b.w + 8);
+}
+// rank of letter c (x0/x1 = plane inversion masks of c) and number of '#' in rows [0,off) of the block, off in [0,128)
+__device__ __forceinline__ void rank_in_blk(const Blk& b, uint32_t off, int c, uint32_t x0, uint32_t x1, uint32_t& rc, uint32_t& nmk) {
+    uint32_t r = c == 0 ? b.w[0] : c == 1 ? b.w[4] : c == 2 ? b.w[8] : b.w[12];
+    uint32_t k = 0;
+    #pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        int below = (int)off - 32 * j;
+        uint32_t lm = below <= 0 ? 0u : (below >= 32 ? 0xffffffffu : ((1u << below) - 1u));
+        uint32_t mk = b.w[4 * j + 3] & lm;
+        r += __popc((b.w[4 * j + 1] ^ x0) & (b.w[4 * j + 2] ^ x1) & ~b.w[4 * j + 3] & lm);
+        k += __popc(mk);
+    }
+    rc = r; nmk = k;
+}
+__device__ __forceinline__ uint32_t letters_before(const Blk& b) { return b.w[0] + b.w[4] + b.w[8] + b.w[12]; }
+
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+}  // namespace
+
+template <bool STATS>
+__global__ void __launch_bounds__(FUSED_THREADS)
+fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ poff,
+                    uint32_t npat, const uint8_t* __restrict__ lut, uint32_t cap, FusedOut out, StatsDev* __restrict__ st, uint32_t kc) {
+    extern __shared__ uint2 s_list[];                 // [cap][FUSED_THREADS]
+    __shared__ uint8_t s_lut[256];
+    for (int i = threadIdx.x; i < 256; i += FUSED_THREADS) s_lut[i] = lut[i];
+    __syncthreads();
+#define LIST(j) s_list[(j) * FUSED_THREADS + threadIdx.x]
+#define DOL(i) s_list[(cap - 1 - (i)) * FUSED_THREADS + threadIdx.x]
+
+    const uint32_t q = blockIdx.x * FUSED_THREADS + threadIdx.x;
+    const bool live = q < npat;
+    uint32_t nF = 0, m = 0, L0 = 0;
+    uint64_t base = 0;
+    bool ovf = false;
+    unsigned long long sI = 0, sS = 0, sE = 0, sLF = 0, sBlk = 0;
+    if (live) {
+        base = poff[q];
+        uint64_t len64 = poff[q + 1] - base;
+        m = len64 > 0xffffffffull ? 0u : (uint32_t)len64;
+        L0 = m < k ? m : k;
+        bool ok = m > 0;
+        uint32_t key = 0;
+        for (uint32_t i = 0; i < m; ++i) {
+            uint32_t c = s_lut[__ldg(bytes + base + i)];
+            if (c > 3) { ok = false; c = 0; }
+            if (i >= m - L0) key |= c << (2 * (i - (m - L0)));
+        }
+        if (ok) {
+            uint32_t a = __ldg(sv.off[L0] + key), n0 = __ldg(sv.off[L0] + key + 1) - a;
+            if (n0 > cap) ovf = true;
+            else { for (uint32_t j = 0; j < n0; ++j) LIST(j) = __ldg(sv.iv[L0] + a + j); nF = n0; }
+        } else m = 0;
+    }
+    const uint32_t steps = m - L0;
+    const uint32_t mk = m < kc ? m : kc;
+    uint32_t s = 0;
+    for (; s < steps && nF && !ovf; ++s) {
+        const int c = (int)s_lut[__ldg(bytes + base + (m - L0 - s - 1))];
+        const uint32_t x0 = (c & 1) ? 0u : 0xffffffffu, x1 = (c & 2) ? 0u : 0xffffffffu;
+        const uint32_t Cc = ix.Cl[c];
+        const bool beyond = STATS && (L0 + s >= kc);
+        if (STATS && L0 + s == mk) sI += nF;
+        uint32_t nout = 0, ndol = 0;
+        // ---- pass 1: F' = LF_c(F) in place, and the set of pile-0 ranges reached through the '#' rows of F
+        for (uint32_t j = 0; j < nF && !ovf; ++j) {
+            const uint2 iv = LIST(j);
+            const uint32_t a = iv.x, b = iv.y + 1;
+            const uint32_t blkA = a >> 7, blkB = b >> 7;
+            Blk B;
+            load_blk(ix.occ, blkA, B);
+            uint32_t rca, ka, rcb, kb;
+            rank_in_blk(B, a & 127u, c, x0, x1, rca, ka);
+            const uint32_t rda = blkA * OCC_ROWS - letters_before(B) + ka;
+            if (blkB != blkA) load_blk(ix.occ, blkB, B);
+            rank_in_blk(B, b & 127u, c, x0, x1, rcb, kb);
+            const uint32_t rdb = blkB * OCC_ROWS - letters_before(B) + kb;
+            if (STATS) { sLF += 1; sBlk += blkB != blkA ? 2 : 1; if (beyond) { sS += 1; sE += rdb - rda; } }
+            if (rcb > rca) {
+                const uint32_t nlo = Cc + rca, nhi = Cc + rcb - 1;
+                if (nout && LIST(nout - 1).y + 1 == nlo) LIST(nout - 1).y = nhi;
+                else { LIST(nout) = make_uint2(nlo, nhi); ++nout; }
+            }
+            for (uint32_t e = rda; e < rdb; ++e) {
+                const uint2 rec = __ldg(ix.link_rec + e);
+                if (rec.x > rec.y) continue;                              // string of the first segment: no predecessor
+                uint32_t l = rec.x, h = rec.y, i = 0;
+                while (i < ndol && DOL(i).y + 1 < l) ++i;
+                if (i < ndol && DOL(i).x <= h + 1) {                      // overlaps / touches D[i]: merge, then absorb followers
+                    const uint2 d = DOL(i);
+                    l = l < d.x ? l : d.x; h = h > d.y ? h : d.y;
+                    uint32_t t = i + 1;
+                    while (t < ndol && DOL(t).x <= h + 1) { const uint32_t y = DOL(t).y; h = h > y ? h : y; ++t; }
+                    DOL(i) = make_uint2(l, h);
+                    if (t > i + 1) { for (uint32_t u = t; u < ndol; ++u) DOL(i + 1 + (u - t)) = DOL(u); ndol -= t - (i + 1); }
+                } else {                                                  // insert before i
+                    if (nF + ndol + 1 >= cap) { ovf = true; break; }
+                    for (uint32_t u = ndol; u > i; --u) DOL(u) = DOL(u - 1);
+                    DOL(i) = make_uint2(l, h);
+                    ++ndol;
+                }
+            }
+        }
+        if (ovf) break;
+        // ---- pass 2: Dol' = LF_c(Dol), pile-0 rows (in place in the top region), then F <- Dol' ++ F'
+        if (ndol) {
+            uint32_t ndp = 0;
+            for (uint32_t i = 0; i < ndol; ++i) {
+                const uint2 iv = DOL(i);
+                const uint32_t a = iv.x, b = iv.y + 1;
+                const uint32_t blkA = a >> 7, blkB = b >> 7;
+                Blk B;
+                load_blk(ix.occ, blkA, B);
+                uint32_t rca, ka, rcb, kb;
+                rank_in_blk(B, a & 127u, c, x0, x1, rca, ka);
+                const uint32_t rda = blkA * OCC_ROWS - letters_before(B) + ka;
+                if (blkB != blkA) load_blk(ix.occ, blkB, B);
+                rank_in_blk(B, b & 127u, c, x0, x1, rcb, kb);
+                if (STATS) { sLF += 1; sBlk += blkB != blkA ? 2 : 1; if (beyond) { sS += 1; sE += (blkB * OCC_ROWS - letters_before(B) + kb) - rda; } }
+                if (rcb > rca) {
+                    const uint32_t nlo = Cc + rca, nhi = Cc + rcb - 1;
+                    if (ndp && DOL(ndp - 1).y + 1 == nlo) DOL(ndp - 1).y = nhi;
+                    else { DOL(ndp) = make_uint2(nlo, nhi); ++ndp; }
+                }
+            }
+            if (ndp) {
+                if (nout + 2 * ndp > cap) { ovf = true; break; }
+                for (uint32_t j = nout; j > 0; --j) LIST(j - 1 + ndp) = LIST(j - 1);
+                for (uint32_t i = 0; i < ndp; ++i) LIST(i) = DOL(i);
+                nout += ndp;
+            }
+        }
+        nF = nout;
+    }
+    if (STATS && !ovf && live && m && L0 + s == mk) sI += nF;            // frontier left at suffix length min(m, kc)
+    // ---- results: per-pattern count + the final interval list, staged contiguously per warp
+    uint32_t cnt = 0;
+    if (ovf) nF = 0;
+    for (uint32_t j = 0; j < nF; ++j) { const uint2 iv = LIST(j); cnt += iv.y - iv.x + 1; }
+    const int lane = threadIdx.x & 31;
+    uint32_t pre = nF;                                                  // inclusive warp scan
+    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += t; }
+    const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
+    uint32_t wbase = 0;
+    if (lane == 31 && total) wbase = atomicAdd(out.cursor, total);
+    wbase = __shfl_sync(0xffffffffu, wbase, 31);
+    const bool nospace = total && (uint64_t)wbase + total > out.staging_cap;
+    if (nospace && nF) { ovf = true; nF = 0; cnt = 0; }
+    if (live) {
+        const uint32_t my = wbase + pre - nF;
+        for (uint32_t j = 0; j < nF; ++j) out.staging[my + j] = LIST(j);
+        out.plist[q] = make_uint2(my, nF);
+        out.counts[q] = cnt;
+        if (ovf) out.ovf_ids[atomicAdd(out.cursor + 1, 1u)] = q;
+    }
+    if (STATS) {
+        if (ovf) sI = sS = sE = sLF = sBlk = 0;          // the level-synchronous engine redoes (and recounts) this pattern
+        const unsigned long long v[5] = {sI, sS, sE, sLF, sBlk};
+        unsigned long long* dst[5] = {&st->I, &st->S, &st->E, &st->lf_intervals, &st->occ_blocks};
+        #pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            uint32_t x = warp_sum((uint32_t)v[i]);
+            if (lane == 0 && x) atomicAdd(dst[i], (unsigned long long)x);
+        }
+    }
+#undef LIST
+#undef DOL
+}
+
+void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat,
+                         const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s) {
+    if (npat == 0) return;
+    const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
+    static bool attr_set[2] = {false, false};
+    if (st) {
+        if (!attr_set[1]) { CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr_set[1] = true; }
+        fused_search_kernel<true><<<(npat + FUSED_THREADS - 1) / FUSED_THREADS, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, npat, d_lut, cap, out, st, kc);
+    } else {
+        if (!attr_set[0]) { CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr_set[0] = true; }
+        fused_search_kernel<false><<<(npat + FUSED_THREADS - 1) / FUSED_THREADS, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, npat, d_lut, cap, out, st, kc);
+    }
+    CUDA_OK(cudaGetLastError());
+}
+
+}  // namespace edsbwt

@@ -66,8 +66,11 @@ struct IndexView {
     const uint32_t* str_seg;     // string -> 1-based segment        (rank on .bitvector)
     const uint32_t* seg_first;   // [1..n_seg+1] first string of segment (select), [n_seg+1] = n_text
     const uint32_t* seg_low;     // [1..n_seg] lowest segment reachable from s through segments holding ""
-    const uint32_t* sa_str;      // row -> string (rows >= n_text), may be null (WALK mode)
-    const uint32_t* sa_off;      // row -> offset in string
+    const uint2*    sa;          // row -> (string, offset in string); null in WALK mode
+    const uint2*    link_rec;    // per end-marker rank r (order of '#' rows in the eBWT): pile-0 row range [x,y] of all
+                                 // strings of the segments reachable from string eof_flat[r] (x > y: none) -- the whole
+                                 // preceding_dollars_finder + empty-string closure of link() in one 8-byte gather
+    const uint2*    str_info;    // string -> (1-based segment, index inside the segment)
 };
 
 #ifdef __CUDACC__
@@ -149,9 +152,10 @@ void parse_eds_text(const std::vector<uint8_t>& text, std::vector<uint8_t>& lett
 // ---------------------------------------------------------------------------------------------------
 // device index + search engine
 // ---------------------------------------------------------------------------------------------------
-struct SeedLevel { DevBuf<uint32_t> off, lo, hi; size_t n_iv = 0; };
+struct SeedLevel { DevBuf<uint32_t> off; DevBuf<uint2> iv; size_t n_iv = 0; };     // iv[off[key] .. off[key+1]) = frontier (lo,hi) of key
+struct SeedView { const uint32_t* off[17]; const uint2* iv[17]; };
 
-struct StatsDev { unsigned long long I, S, E, L, O, lf_intervals; };
+struct StatsDev { unsigned long long I, S, E, L, O, lf_intervals, occ_blocks, overflow; };
 
 struct Workspace;   // engine.cu
 
@@ -161,7 +165,9 @@ struct Index {
     std::mutex mu;
     HostIndex host;       // ebwt bytes dropped after upload
     DevBuf<uint4> occ;
-    DevBuf<uint32_t> eof_flat, str_seg, seg_first, seg_low, sa_str, sa_off;
+    DevBuf<uint32_t> eof_flat, str_seg, seg_first, seg_low;
+    DevBuf<uint2> sa, link_rec, str_info;
+    DevBuf<uint8_t> lut;             // 256-byte byte -> code table on the device (0..3 letters, 4 end-marker, 255 other)
     IndexView view{};
     uint32_t seed_k = 0;
     int locate_mode = EDSBWT_LOCATE_SA;
@@ -170,6 +176,7 @@ struct Index {
     Workspace* ws = nullptr;
     edsbwt_stats last{};
     int collect_counters = 0; uint32_t canonical_k = 12;
+    int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 24;
     uint64_t device_bytes() const;
     ~Index();
 };
@@ -181,6 +188,19 @@ struct SearchOut {
 };
 void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat, uint64_t total_bytes,
                 uint32_t max_len, bool locate, int lf_variant, SearchOut& out);
+
+// fused.cu -- one thread per pattern, whole backward search in one launch
+constexpr int FUSED_THREADS = 128;
+struct FusedOut {
+    uint2*    plist;        // [npat] (first slot in staging, number of final intervals)
+    uint32_t* counts;       // [npat] number of occurrences ("Found N")
+    uint2*    staging;      // final (lo,hi) row intervals, contiguous per pattern
+    uint32_t  staging_cap;
+    uint32_t* cursor;       // [0] slots used in staging, [1] number of patterns handed to the level-synchronous engine
+    uint32_t* ovf_ids;      // [npat] those patterns
+};
+void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat,
+                         const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s);
 
 // builder.cu
 void build_index_files(const uint8_t* letters, const uint64_t* str_off, uint32_t nstr, const uint8_t* seg_first,

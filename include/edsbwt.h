@@ -52,6 +52,8 @@ typedef struct {
 
 #define EDSBWT_LOCATE_SA    0   /* row -> (string, offset) table in HBM: one gather per occurrence           */
 #define EDSBWT_LOCATE_WALK  1   /* LF-walk each row to its string start (the reference's a9/a13 arithmetic)  */
+#define EDSBWT_ENGINE_FUSED     0   /* one thread per pattern, one launch; oversized frontiers fall through to: */
+#define EDSBWT_ENGINE_LEVELSYNC 1   /* level-synchronous interval-parallel engine (also builds the seed table)   */
 #define EDSBWT_LF_RANK      0   /* EDSBWTsearch:      LF by blocked rank                                      */
 #define EDSBWT_LF_MOVE      1   /* MOVE_EDSBWTSearch: LF by move table                                        */
 
@@ -60,7 +62,9 @@ typedef struct {
     int32_t  locate_mode;       /* EDSBWT_LOCATE_SA / _WALK                                                   */
     int32_t  verify;            /* 1 = cross-check _bv_<p>.aux (rrr) and tableOcc against the pile bytes      */
     int32_t  build_move;        /* 1 = also build the move table (EDSBWT_LF_MOVE searches)                    */
-    int32_t  reserved[4];
+    int32_t  engine;            /* EDSBWT_ENGINE_FUSED (default) / _LEVELSYNC                                 */
+    int32_t  fused_cap;         /* frontier slots per pattern of the fused kernel (0 = default 24)            */
+    int32_t  reserved[2];
 } edsbwt_open_opts;
 
 /* Canonical byte-model counters of DESIGN.md + engine statistics of the last search. */
@@ -72,7 +76,10 @@ typedef struct {
     double   lf_kernel_ms;      /* CUDA-event time summed over the launches of the LF rank kernel              */
     double   locate_kernel_ms;  /* CUDA-event time of the locate kernel                                        */
     double   total_ms;          /* CUDA-event time of the whole search on the library's stream                 */
-    uint64_t frontier_peak;     /* largest frontier (intervals) over all steps                                  */
+    uint64_t frontier_peak;     /* largest frontier (intervals) over all steps of the level-synchronous engine  */
+    uint64_t occ_blocks;        /* 64-byte Occ blocks fetched by the search kernels (collect_counters only)     */
+    uint64_t overflow_patterns; /* patterns the fused kernel handed to the level-synchronous engine            */
+    double   search_kernel_ms;  /* CUDA-event time of the fused search kernel                                   */
 } edsbwt_stats;
 
 /* --- index load: replaces EDSBWT::recoverInfo (EDSBWTsearch.cpp:1557-1656), EDSBWT::computeVectorOcc

@@ -25,11 +25,11 @@ def _index_files(tmp_path, segs, name="idx"):
 
 
 @pytest.mark.parametrize("name", golden_names())
-@pytest.mark.parametrize("seed_k,locate_mode", [(-1, 0), (1, 0), (3, 1), (6, 0)])
-def test_golden(eb, tmp_path, name, seed_k, locate_mode):
+@pytest.mark.parametrize("seed_k,locate_mode,engine,cap", [(-1, 0, 0, 0), (1, 0, 0, 0), (3, 1, 0, 4), (6, 0, 1, 0), (2, 0, 0, 5)])
+def test_golden(eb, tmp_path, name, seed_k, locate_mode, engine, cap):
     g = load_golden(name)
     _, base = _index_files(tmp_path, E.parse_eds(g["eds"]))
-    with eb.Index(base, seed_k=seed_k, locate_mode=locate_mode) as idx:
+    with eb.Index(base, seed_k=seed_k, locate_mode=locate_mode, engine=engine, fused_cap=cap) as idx:
         counts, occ = idx.search(g["patterns"], locate=True)
         assert counts.tolist() == g["counts"]
         assert eb.occ_rows(occ) == sorted(g["rows_reference_order"])
@@ -56,20 +56,31 @@ def test_random_vs_port(eb, oracle_built, tmp_path, seed, kw, seed_k):
     pats += [b"", b"ACGNT", b"#A", b"A" * 300]
     pf = str(tmp_path / "p.txt")
     E.write_patterns(pf, [p if p else b"A" for p in pats])       # the file format cannot hold an empty line
-    with eb.Index(base, seed_k=seed_k, locate_mode=0) as idx:
-        k = idx.info().seed_k
-        idx.set_stats(True, canonical_k=k)
-        file_pats = [p if p else b"A" for p in pats]
-        c_port, rows_port, st_port = oracle_built.run_port(base, pf, locate=True, k=k)
-        counts, occ = idx.search(file_pats, locate=True)
-        st = idx.last_stats()
-        assert counts.tolist() == c_port
-        assert eb.occ_rows(occ) == sorted(rows_port)
-        for key in "ISELO":
-            assert st[key] == st_port[key], (key, st[key], st_port[key])
-        # the empty pattern itself (not representable in a file) -> 0
-        c2, o2 = idx.search([b"", b"ACG"], locate=True)
-        assert c2[0] == 0 and all(o2["pat"] == 1)
+    file_pats = [p if p else b"A" for p in pats]
+    c_port = rows_port = None
+    # the fused kernel (default), the fused kernel with a tiny frontier capacity (most patterns fall through to the
+    # level-synchronous engine), and the level-synchronous engine alone: same counts, rows and byte-model counters
+    for engine, cap in [(eb.ENGINE_FUSED, 0), (eb.ENGINE_FUSED, 4), (eb.ENGINE_LEVELSYNC, 0)]:
+        with eb.Index(base, seed_k=seed_k, locate_mode=0, engine=engine, fused_cap=cap) as idx:
+            k = idx.info().seed_k
+            idx.set_stats(True, canonical_k=k)
+            if c_port is None:
+                c_port, rows_port, st_port = oracle_built.run_port(base, pf, locate=True, k=k)
+            counts, occ = idx.search(file_pats, locate=True)
+            st = idx.last_stats()
+            assert counts.tolist() == c_port
+            assert eb.occ_rows(occ) == sorted(rows_port)
+            assert np.all(np.diff(occ["pat"].astype(np.int64)) >= 0)
+            for key in "ISELO":
+                assert st[key] == st_port[key], (engine, cap, key, st[key], st_port[key])
+            if engine == eb.ENGINE_FUSED and cap == 4:
+                assert st["overflow_patterns"] > 0
+            idx.set_stats(False)
+            counts, occ = idx.search(file_pats, locate=True)
+            assert counts.tolist() == c_port and eb.occ_rows(occ) == sorted(rows_port)
+            # the empty pattern itself (not representable in a file) -> 0
+            c2, o2 = idx.search([b"", b"ACG"], locate=True)
+            assert c2[0] == 0 and all(o2["pat"] == 1)
     with eb.Index(base, seed_k=seed_k, locate_mode=1) as idx:          # LF-walk locate
         counts, occ = idx.search(file_pats, locate=True)
         assert counts.tolist() == c_port and eb.occ_rows(occ) == sorted(rows_port)
