@@ -255,7 +255,7 @@ def main():
     torch.cuda.nvtx.range_push("timed")
     for _ in range(args.steps):
         st, _ = step_device()
-        dev_ms += st["total_ms"]; lf_ms += st["lf_kernel_ms"]; loc_ms += st["locate_kernel_ms"]; launches += st["kernel_launches"]
+        dev_ms += st["total_ms"]; lf_ms += st["search_kernel_ms"]; loc_ms += st["locate_kernel_ms"]; launches += st["kernel_launches"]
     torch.cuda.nvtx.range_pop()
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
@@ -301,8 +301,8 @@ def main():
         peak_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6553.6 GB/s (B200_PROFILING.md)"
         # dominant kernel: the LF rank kernel.  Algorithmic bytes = 64 B per distinct Occ block an interval end needs
         # + the 12 B interval record read + 8 B written; canonical SURVEY model printed next to it.
-        occ_blocks = st_c.get("occ_blocks", 0) or 2 * st_c["lf_intervals"]
-        alg_bytes = 64.0 * occ_blocks + 20.0 * st_c["lf_intervals"]
+        occ_blocks = st_c["occ_blocks"]
+        alg_bytes = 64.0 * occ_blocks + 8.0 * st_c["E"] + (args.plen + 16.0) * args.npat + 8.0 * st_c["I"]
         lf_ms_step = lf_ms / args.steps
         achieved = alg_bytes / (lf_ms_step * 1e-3) / 1e9 if lf_ms_step > 0 else 0.0
         canon = 8.0 * (args.npat + st_c["I"]) + 128.0 * st_c["S"] + 16.0 * st_c["E"] + 64.0 * st_c["L"] + 28.0 * st_c["O"]
@@ -326,12 +326,14 @@ def main():
                     "ms_per_step": e2e_ms_max / args.steps},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "lf_step_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "fused_search_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak if peak else None, "traffic": None, "peak_source": peak_src,
                          "alg_bytes_per_step": alg_bytes, "kernel_ms_per_step": lf_ms_step,
                          "kernel_share_of_step": lf_ms_step / (dev_ms / args.steps) if dev_ms else None,
                          "gather64_gbs_4GiB": g_big, "gather64_gbs_index_sized": g_idx,
                          "frac_of_gather64": (achieved / g_big) if g_big else None,
+                         "locate_kernel_ms_per_step": loc_ms / args.steps, "overflow_patterns": st_c["overflow_patterns"], "occ_blocks": occ_blocks,
+                         "lf_intervals": st_c["lf_intervals"],
                          "canonical_model": {"I": st_c["I"], "S": st_c["S"], "E": st_c["E"], "L": st_c["L"], "O": st_c["O"],
                                              "bytes_per_step": canon, "bytes_per_pattern": canon / args.npat,
                                              "GBps_over_whole_step": canon / (dev_ms / args.steps * 1e-3) / 1e9}},
