@@ -142,25 +142,26 @@ def cpu_reference_run(base, pats, seconds, cores, note):
             for pf in files:
                 cmd = [exe, base, pf] if kind == "reference" else [exe, base, pf, "--locate", "1", "--csv", pf + "output.csv"]
                 procs.append(subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True))
-            took = []
+            took, found = [], []
             for p in procs:
                 out = p.communicate()[0]
                 if kind == "reference":
                     import re
                     m = re.search(r"bs took:([0-9.eE+-]+)", out)
                     took.append(float(m.group(1)) if m else float("nan"))
+                    found += [int(x) for x in re.findall(r"Found (\d+) starting", out)]
                 else:
                     took.append(json.loads(out.strip().splitlines()[-1])["seconds"])
-            return time.time() - t0, max(took)
+            return time.time() - t0, max(took), found
         # calibrate with one pattern per core, then size the sample for ~`seconds` of search time
-        wall1, took1 = run_shards(1)
+        wall1, took1, _ = run_shards(1)
         per = int(max(1, min(len(pats) // cores, seconds / max(took1, 1e-3))))
-        wall, took = run_shards(per)
+        wall, took, found = run_shards(per)
         val = per * cores / max(took, 1e-9)
         return {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
                 "sample": "%d patterns (%d per process x %d processes) of the same batch, %s; max 'bs took' %.2fs (index load excluded, wall %.1fs)" % (
                     per * cores, per, cores, note, took, wall),
-                "search_seconds": took}
+                "search_seconds": took, "counts": found, "n": per * cores}
     finally:
         shutil.rmtree(d, ignore_errors=True)
 
@@ -261,20 +262,23 @@ def main():
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop()
 
-    # ---- e2e: host buffers through edsbwt_search
-    counts_h = np.zeros(args.npat, dtype=np.uint32)
-    e2e_ms, d2h = 0.0, 0
-    for it in range(1 + args.steps):
+    # ---- e2e: host buffers through edsbwt_search_into (pinned caller buffers; H2D + D2H inside the timed region)
+    p_data = eb.pinned_empty(data.size, np.uint8); p_data[:] = data
+    p_off = eb.pinned_empty(off.size, np.uint64); p_off[:] = off
+    p_counts = eb.pinned_empty(args.npat, np.uint32)
+    p_occ = eb.pinned_empty(int(nocc) + 1024, eb.OCC_DTYPE)
+    e2e_ms, d2h, e2e_launches = 0.0, 0, 0
+    for it in range(2 + args.steps):
         barrier()
         t1 = time.perf_counter()
-        counts, occ = idx.search((data, off), locate=True)
+        got = idx.search_into(p_data, p_off, p_counts, p_occ, locate=True)
         dt = (time.perf_counter() - t1) * 1e3
-        if it > 0:
+        if it >= 2:
             e2e_ms += dt
-            d2h = counts.nbytes + occ.nbytes
+            d2h = p_counts.nbytes + got * eb.OCC_DTYPE.itemsize
     h2d = data.nbytes + off.nbytes
-    del counts_h
-
+    gpu_counts = np.array(p_counts, copy=True)
+    gpu_occ_total = int(got)
     def allmax(x):
         if world == 1:
             return x
@@ -341,7 +345,11 @@ def main():
     idx.close()
     if rank == 0 and world == 1 and not args.no_cpu:
         try:
-            out["cpu_baseline"] = cpu_reference_run(base, pats, args.cpu_seconds, os.cpu_count() or 1, "locate (RECOVERBW=1)")
+            cb = cpu_reference_run(base, pats, args.cpu_seconds, os.cpu_count() or 1, "locate (RECOVERBW=1)")
+            ref_counts, nref = cb.pop("counts"), cb.pop("n")
+            if len(ref_counts) == nref:         # full-size parity check on the sample: the reference's own counts
+                cb["parity_vs_gpu"] = "ok" if ref_counts == gpu_counts[:nref].tolist() else "MISMATCH"
+            out["cpu_baseline"] = cb
         except Exception as e:
             out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": "failed: %r" % (e,)}
     if world > 1:

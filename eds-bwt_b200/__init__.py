@@ -23,7 +23,8 @@ EXPORTS = [
     "edsbwt_search_device", "edsbwt_result_sizes", "edsbwt_result_device_ptrs", "edsbwt_result_fetch",
     "edsbwt_result_free", "edsbwt_last_stats", "edsbwt_set_stats", "edsbwt_write_csv", "edsbwt_read_patterns",
     "edsbwt_build_from_eds", "edsbwt_build_from_collection", "edsbwt_gather_bench", "edsbwt_free",
-    "edsbwt_strerror", "edsbwt_last_error", "edsbwt_version",
+    "edsbwt_strerror", "edsbwt_last_error", "edsbwt_version", "edsbwt_search_into", "edsbwt_host_alloc", "edsbwt_host_free",
+    "edsbwt_set_chunk",
 ]
 
 
@@ -35,14 +36,14 @@ class Info(C.Structure):
 
 class OpenOpts(C.Structure):
     _fields_ = [("seed_k", C.c_int32), ("locate_mode", C.c_int32), ("verify", C.c_int32), ("build_move", C.c_int32),
-                ("engine", C.c_int32), ("fused_cap", C.c_int32), ("reserved", C.c_int32 * 2)]
+                ("engine", C.c_int32), ("fused_cap", C.c_int32), ("fused_cap2", C.c_int32), ("reserved", C.c_int32 * 1)]
 
 
 class Stats(C.Structure):
     _fields_ = [("I", C.c_uint64), ("S", C.c_uint64), ("E", C.c_uint64), ("L", C.c_uint64), ("O", C.c_uint64),
                 ("steps", C.c_uint64), ("kernel_launches", C.c_uint64), ("lf_intervals", C.c_uint64),
                 ("lf_kernel_ms", C.c_double), ("locate_kernel_ms", C.c_double), ("total_ms", C.c_double),
-                ("frontier_peak", C.c_uint64), ("occ_blocks", C.c_uint64), ("overflow_patterns", C.c_uint64),
+                ("frontier_peak", C.c_uint64), ("occ_blocks", C.c_uint64), ("overflow_patterns", C.c_uint64), ("levelsync_patterns", C.c_uint64),
                 ("search_kernel_ms", C.c_double)]
 
     def as_dict(self):
@@ -79,6 +80,12 @@ def lib():
         L.edsbwt_index_info.argtypes = [C.c_void_p, C.POINTER(Info)]
         L.edsbwt_search.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
                                     C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+        L.edsbwt_search_into.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
+                                         C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.edsbwt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_uint64]
+        L.edsbwt_host_free.argtypes = [C.c_void_p]
+        L.edsbwt_host_free.restype = None
+        L.edsbwt_set_chunk.argtypes = [C.c_void_p, C.c_uint32]
         L.edsbwt_search_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32,
                                            C.c_int, C.c_int, C.POINTER(C.c_void_p)]
         L.edsbwt_result_sizes.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
@@ -115,10 +122,10 @@ class Index:
     """Device-resident EDS-BWT index (edsbwt_index_open_ex)."""
 
     def __init__(self, base, device=0, seed_k=-1, locate_mode=LOCATE_SA, verify=True, build_move=False,
-                 engine=ENGINE_FUSED, fused_cap=0):
+                 engine=ENGINE_FUSED, fused_cap=0, fused_cap2=0):
         self._h = C.c_void_p()
         o = OpenOpts(seed_k=seed_k, locate_mode=locate_mode, verify=int(verify), build_move=int(build_move),
-                     engine=engine, fused_cap=fused_cap)
+                     engine=engine, fused_cap=fused_cap, fused_cap2=fused_cap2)
         _check(lib().edsbwt_index_open_ex(os.fsencode(base), device, C.byref(o), C.byref(self._h)))
         self.device = device
 
@@ -171,6 +178,19 @@ class Index:
             lib().edsbwt_free(occ_p)
         return counts[:npat], occ
 
+    def search_into(self, data, off, counts, occ=None, locate=True, lf_variant=LF_RANK):
+        """Caller-owned host buffers (ideally from pinned_empty): counts uint32[npat], occ OCC_DTYPE[cap].
+        -> number of occurrences; raises EdsbwtError(code -7) when occ is too small."""
+        npat = len(off) - 1
+        nocc = C.c_uint64(0)
+        _check(lib().edsbwt_search_into(self._h, data.ctypes.data, off.ctypes.data, npat, int(locate), lf_variant,
+                                        counts.ctypes.data, occ.ctypes.data if occ is not None else None,
+                                        len(occ) if occ is not None else 0, C.byref(nocc)))
+        return nocc.value
+
+    def set_chunk(self, patterns_per_chunk):
+        _check(lib().edsbwt_set_chunk(self._h, patterns_per_chunk))
+
     def search_device(self, d_bytes_ptr, d_off_ptr, npat, total_bytes, max_len, locate=True, lf_variant=LF_RANK):
         """Device-pointer variant; returns a DeviceResult (results stay in HBM)."""
         r = C.c_void_p()
@@ -207,6 +227,28 @@ class DeviceResult:
             self.free()
         except Exception:
             pass
+
+
+class _Pinned:
+    def __init__(self, nbytes):
+        self.p = C.c_void_p()
+        _check(lib().edsbwt_host_alloc(C.byref(self.p), nbytes))
+
+    def __del__(self):
+        try:
+            lib().edsbwt_host_free(self.p)
+        except Exception:
+            pass
+
+
+def pinned_empty(n, dtype):
+    """numpy array over page-locked host memory (edsbwt_host_alloc); freed with the array."""
+    dtype = np.dtype(dtype)
+    nbytes = max(1, int(n) * dtype.itemsize)
+    owner = _Pinned(nbytes)
+    buf = (C.c_uint8 * nbytes).from_address(owner.p.value)
+    buf._owner = owner          # the ctypes buffer is the base of the array and keeps the allocation alive
+    return np.frombuffer(buf, dtype=dtype, count=int(n))
 
 
 def occ_rows(occ, pat_base=0):

@@ -106,6 +106,77 @@ void edsbwt_result_free(edsbwt_result* res) {
     delete res;
 }
 
+// Pipelined host-buffer search: H2D of chunk i+1 | search of chunk i | D2H of chunk i-1 on three streams.
+// occ may be null (count-only or sizing pass).  *nocc receives the total number of occurrences even when it
+// exceeds occ_cap (then EDSBWT_E_NOSPACE is returned and only the first occ_cap tuples were copied).
+static int search_into_impl(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat, int locate, int lf_variant,
+                            uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc) {
+    Index& ix = idx->ix;
+    CUDA_OK(cudaSetDevice(ix.device));
+    if (!ix.pipe) {
+        ix.pipe = new Pipe;
+        CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->in, cudaStreamNonBlocking));
+        CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->outs, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) { CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_in[i], cudaEventDisableTiming)); CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_out[i], cudaEventDisableTiming)); }
+    }
+    Pipe& P = *ix.pipe;
+    const uint32_t chunk = ix.chunk_patterns ? ix.chunk_patterns : npat;
+    const uint32_t nchunks = (npat + chunk - 1) / chunk;
+    uint64_t total_occ = 0; bool nospace = false;
+    edsbwt_stats acc{}; 
+    auto issue_in = [&](uint32_t c) {
+        const uint32_t b = c * chunk, e = std::min<uint64_t>((uint64_t)b + chunk, npat);
+        const uint64_t nb = pat_off[e] - pat_off[b];
+        const int sl = c & 1;
+        P.bytes[sl].ensure(nb + 16); P.off[sl].ensure((size_t)(e - b) + 1);
+        if (nb) CUDA_OK(cudaMemcpyAsync(P.bytes[sl].p, pat_bytes + pat_off[b], nb, cudaMemcpyHostToDevice, P.in));
+        CUDA_OK(cudaMemcpyAsync(P.off[sl].p, pat_off + b, ((size_t)(e - b) + 1) * 8, cudaMemcpyHostToDevice, P.in));
+        CUDA_OK(cudaEventRecord(P.ev_in[sl], P.in));
+    };
+    issue_in(0);
+    for (uint32_t c = 0; c < nchunks; ++c) {
+        const uint32_t b = c * chunk, e = std::min<uint64_t>((uint64_t)b + chunk, npat);
+        const int sl = c & 1;
+        uint32_t max_len = 0;
+        for (uint32_t i = b; i < e; ++i) { uint64_t l = pat_off[i + 1] - pat_off[i]; if (l > 0xffffffffull) EDS_FAIL(EDSBWT_E_ARG, "pattern %u too long", i); if (l > max_len) max_len = (uint32_t)l; }
+        if (c + 1 < nchunks) issue_in(c + 1);                       // overlaps the search below
+        if (c >= 2) CUDA_OK(cudaEventSynchronize(P.ev_out[sl]));     // result buffers of chunk c-2 are free again
+        CUDA_OK(cudaStreamWaitEvent(ix.stream, P.ev_in[sl], 0));
+        // offsets stay absolute: bias the byte pointer instead of rebasing npat offsets on the host
+        const uint8_t* d_bytes = (const uint8_t*)((uintptr_t)P.bytes[sl].p - (uintptr_t)pat_off[b]);
+        run_search(ix, d_bytes, P.off[sl].p, e - b, pat_off[e] - pat_off[b], max_len, locate != 0, lf_variant, P.res[sl], b);
+        const edsbwt_stats& st = ix.last;
+        acc.I += st.I; acc.S += st.S; acc.E += st.E; acc.L += st.L; acc.O += st.O; acc.steps += st.steps; acc.kernel_launches += st.kernel_launches;
+        acc.lf_intervals += st.lf_intervals; acc.lf_kernel_ms += st.lf_kernel_ms; acc.locate_kernel_ms += st.locate_kernel_ms; acc.total_ms += st.total_ms;
+        acc.frontier_peak = std::max(acc.frontier_peak, st.frontier_peak); acc.occ_blocks += st.occ_blocks; acc.overflow_patterns += st.overflow_patterns;
+        acc.levelsync_patterns += st.levelsync_patterns; acc.search_kernel_ms += st.search_kernel_ms;
+        // run_search returned with the compute stream idle: copy out on the third stream
+        CUDA_OK(cudaMemcpyAsync(counts + b, P.res[sl].counts.p, (size_t)(e - b) * 4, cudaMemcpyDeviceToHost, P.outs));
+        const uint64_t k = P.res[sl].nocc;
+        if (locate && k) {
+            if (occ && total_occ + k <= occ_cap) CUDA_OK(cudaMemcpyAsync(occ + total_occ, P.res[sl].occ.p, (size_t)k * sizeof(edsbwt_occ), cudaMemcpyDeviceToHost, P.outs));
+            else if (occ && total_occ < occ_cap) { CUDA_OK(cudaMemcpyAsync(occ + total_occ, P.res[sl].occ.p, (size_t)(occ_cap - total_occ) * sizeof(edsbwt_occ), cudaMemcpyDeviceToHost, P.outs)); nospace = true; }
+            else nospace = true;
+            total_occ += k;
+        }
+        CUDA_OK(cudaEventRecord(P.ev_out[sl], P.outs));
+    }
+    CUDA_OK(cudaStreamSynchronize(P.outs));
+    ix.last = acc;
+    if (nocc) *nocc = total_occ;
+    return (locate && nospace && (occ || occ_cap)) ? EDSBWT_E_NOSPACE : EDSBWT_OK;
+}
+
+int edsbwt_search_into(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat, int locate, int lf_variant,
+                       uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc) {
+    if (!idx || (npat && (!pat_off || !counts))) return EDSBWT_E_ARG;
+    if (nocc) *nocc = 0;
+    if (npat == 0) return EDSBWT_OK;
+    int rc2 = EDSBWT_OK;
+    int rc = guarded([&] { rc2 = search_into_impl(idx, pat_bytes, pat_off, npat, locate, lf_variant, counts, occ, occ_cap, nocc); });
+    return rc ? rc : rc2;
+}
+
 int edsbwt_search(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat, int locate, int lf_variant,
                   uint32_t* counts, edsbwt_occ** occ, uint64_t* nocc) {
     if (!idx || (npat && (!pat_off || !counts))) return EDSBWT_E_ARG;
@@ -113,33 +184,31 @@ int edsbwt_search(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* p
     if (occ) *occ = nullptr;
     if (nocc) *nocc = 0;
     if (npat == 0) return EDSBWT_OK;
-    edsbwt_result* r = nullptr;
-    int rc = guarded([&] {
-        CUDA_OK(cudaSetDevice(idx->ix.device));
-        uint64_t total = pat_off[npat] - pat_off[0];
-        uint32_t max_len = 0;
-        for (uint32_t i = 0; i < npat; ++i) { uint64_t l = pat_off[i + 1] - pat_off[i]; if (l > 0xffffffffull) EDS_FAIL(EDSBWT_E_ARG, "pattern %u too long", i); if (l > max_len) max_len = (uint32_t)l; }
-        DevBuf<uint8_t> d_bytes; DevBuf<uint64_t> d_off;
-        d_bytes.ensure(total + 16); d_off.ensure((size_t)npat + 1);
-        std::vector<uint64_t> rel((size_t)npat + 1);
-        for (uint32_t i = 0; i <= npat; ++i) rel[i] = pat_off[i] - pat_off[0];
-        if (total) CUDA_OK(cudaMemcpy(d_bytes.p, pat_bytes + pat_off[0], total, cudaMemcpyHostToDevice));
-        CUDA_OK(cudaMemcpy(d_off.p, rel.data(), rel.size() * 8, cudaMemcpyHostToDevice));
-        int rc2 = edsbwt_search_device(idx, d_bytes.p, d_off.p, npat, total, max_len, locate, lf_variant, &r);
-        if (rc2) throw Failure{rc2};
-        CUDA_OK(cudaMemcpy(counts, r->out.counts.p, (size_t)npat * 4, cudaMemcpyDeviceToHost));
-        if (locate) {
-            *nocc = r->out.nocc;
-            if (r->out.nocc) {
-                *occ = (edsbwt_occ*)malloc((size_t)r->out.nocc * sizeof(edsbwt_occ));
-                if (!*occ) EDS_FAIL(EDSBWT_E_IO, "host out of memory for %llu occurrences", (unsigned long long)r->out.nocc);
-                CUDA_OK(cudaMemcpy(*occ, r->out.occ.p, (size_t)r->out.nocc * sizeof(edsbwt_occ), cudaMemcpyDeviceToHost));
-            }
-        }
-    });
-    edsbwt_result_free(r);
-    if (rc && occ && *occ) { free(*occ); *occ = nullptr; }
-    return rc;
+    if (!locate) return edsbwt_search_into(idx, pat_bytes, pat_off, npat, 0, lf_variant, counts, nullptr, 0, nullptr);
+    // occurrences are malloc'ed for the caller: size them from the counts of a first attempt with a guessed capacity
+    uint64_t cap = (uint64_t)npat * 2 + 1024, got = 0;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        edsbwt_occ* buf = (edsbwt_occ*)malloc((size_t)cap * sizeof(edsbwt_occ));
+        if (!buf) { set_error("host out of memory for %llu occurrences", (unsigned long long)cap); return EDSBWT_E_IO; }
+        int rc = edsbwt_search_into(idx, pat_bytes, pat_off, npat, 1, lf_variant, counts, buf, cap, &got);
+        if (rc == EDSBWT_OK) { if (got == 0) { free(buf); buf = nullptr; } *occ = buf; *nocc = got; return EDSBWT_OK; }
+        free(buf);
+        if (rc != EDSBWT_E_NOSPACE) return rc;
+        cap = got;
+    }
+    return EDSBWT_E_UNSUPPORTED;
+}
+
+int edsbwt_host_alloc(void** p, uint64_t bytes) {
+    if (!p) return EDSBWT_E_ARG;
+    *p = nullptr;
+    return guarded([&] { CUDA_OK(cudaHostAlloc(p, bytes ? bytes : 1, cudaHostAllocPortable)); });
+}
+void edsbwt_host_free(void* p) { if (p) cudaFreeHost(p); }
+int edsbwt_set_chunk(edsbwt_index* idx, uint32_t patterns_per_chunk) {
+    if (!idx) return EDSBWT_E_ARG;
+    idx->ix.chunk_patterns = patterns_per_chunk;
+    return EDSBWT_OK;
 }
 
 int edsbwt_gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, double* gb_per_s) {

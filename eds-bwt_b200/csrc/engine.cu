@@ -371,7 +371,7 @@ __global__ void ls_finalize_kernel(const uint32_t* __restrict__ pat, const uint3
 // (indices_of_dollars_in_interval, EDSBWTsearch.cpp:1310-1332).  Output grouped by ascending pattern.
 template <bool WALK>
 __global__ void locate_kernel(IndexView ix, const uint2* __restrict__ plist, const uint32_t* __restrict__ occ_ofs, const uint2* __restrict__ staging,
-                              uint32_t npat, uint64_t nocc, edsbwt_occ* __restrict__ out, StatsDev* __restrict__ st) {
+                              uint32_t npat, uint64_t nocc, uint32_t pat_base, edsbwt_occ* __restrict__ out, StatsDev* __restrict__ st) {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t steps = 0;
     if (t < nocc) {
@@ -397,7 +397,7 @@ __global__ void locate_kernel(IndexView ix, const uint2* __restrict__ plist, con
             w = __ldg(ix.eof_flat + occ_rank_eof(ix.occ, row));
         } else { uint2 v = __ldg(ix.sa + row); w = v.x; off = v.y; }
         uint2 si = __ldg(ix.str_info + w);
-        edsbwt_occ o; o.pat = q; o.str = w; o.seg = si.x; o.idx_in_seg = si.y; o.off = off;
+        edsbwt_occ o; o.pat = q + pat_base; o.str = w; o.seg = si.x; o.idx_in_seg = si.y; o.off = off;
         out[t] = o;
         steps = off + 1;
     }
@@ -421,7 +421,7 @@ struct Workspace {
     DevBuf<uint8_t> cubtmp;
     DevBuf<unsigned int> scalars;        // [0] nvalid
     DevBuf<uint2> plist, staging;        // per-pattern final lists (fused + level-synchronous results)
-    DevBuf<uint32_t> fcursor, ovf_ids, occ_ofs;
+    DevBuf<uint32_t> fcursor, ovf_ids, ovf_ids2, occ_ofs;
     StatsDev* d_stats = nullptr;
     uint32_t* h_pin = nullptr;           // pinned read-back area
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr, evf0 = nullptr, evf1 = nullptr, evl0 = nullptr, evl1 = nullptr;
@@ -435,6 +435,7 @@ struct Workspace {
 Index::~Index() {
     for (SeedLevel* s : seed) delete s;
     delete ws;
+    delete pipe;
     if (stream) cudaStreamDestroy(stream);
 }
 uint64_t Index::device_bytes() const {
@@ -610,7 +611,9 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     ix.engine = o.engine == EDSBWT_ENGINE_LEVELSYNC ? EDSBWT_ENGINE_LEVELSYNC : EDSBWT_ENGINE_FUSED;
     ix.fused_cap = o.fused_cap > 0 ? (uint32_t)o.fused_cap : 24u;
     if (ix.fused_cap < 4) ix.fused_cap = 4;
-    if (ix.fused_cap > 192) ix.fused_cap = 192;             // 192 slots x 128 threads x 8 B = 192 KB of shared memory per CTA
+    if (ix.fused_cap > FUSED_BIG_CAP) ix.fused_cap = FUSED_BIG_CAP;
+    ix.fused_cap2 = o.fused_cap2 > 0 ? std::min<uint32_t>((uint32_t)o.fused_cap2, FUSED_BIG_CAP) : FUSED_BIG_CAP;
+    if (ix.fused_cap2 < 4) ix.fused_cap2 = 4;
     { Lut l = make_lut(h); ix.lut.ensure(256); CUDA_OK(cudaMemcpyAsync(ix.lut.p, l.code, 256, cudaMemcpyHostToDevice, s)); CUDA_OK(cudaStreamSynchronize(s)); }
     ws.scalars.ensure(16);
 
@@ -738,7 +741,7 @@ static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64
 }
 
 void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat, uint64_t total_bytes, uint32_t max_len,
-                bool locate, int lf_variant, SearchOut& out) {
+                bool locate, int lf_variant, SearchOut& out, uint32_t pat_base) {
     if (lf_variant != EDSBWT_LF_RANK) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "move-table LF variant not built into this handle");
     (void)total_bytes;
     CUDA_OK(cudaSetDevice(ix.device));
@@ -752,7 +755,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     CUDA_OK(cudaEventRecord(ws.ev0, s));
     out.npat = npat; out.nocc = 0;
     out.counts.ensure(npat ? npat : 1);
-    uint32_t steps = 0, novf = 0; uint64_t peak = 0;
+    uint32_t steps = 0, novf = 0, novf1 = 0; uint64_t peak = 0;
     bool fused_ran = false, locate_ran = false;
     if (npat) {
         ws.plist.ensure(npat); ws.fcursor.ensure(4);
@@ -766,15 +769,31 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             ws.staging.ensure(want); ws.ovf_ids.ensure(npat);
             SeedView sv{};
             for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; }
-            FusedOut fo{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.ovf_ids.p};
+            FusedOut fo{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 1, ws.ovf_ids.p};
             CUDA_OK(cudaEventRecord(ws.evf0, s));
-            launch_fused_search(ix.view, sv, ix.seed_k, d_bytes, d_off, npat, ix.lut.p, ix.fused_cap, fo, st, ix.canonical_k, s);
+            launch_fused_search(ix.view, sv, ix.seed_k, d_bytes, d_off, nullptr, npat, ix.lut.p, ix.fused_cap, fo, st, ix.canonical_k, s);
             CUDA_OK(cudaEventRecord(ws.evf1, s));
             ws.launches += 1; fused_ran = true;
             CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 8, cudaMemcpyDeviceToHost, s));
             CUDA_OK(cudaStreamSynchronize(s));
             nstage = ws.h_pin[0]; novf = ws.h_pin[1];
+            novf1 = novf;
             ids = ws.ovf_ids.p;
+            if (novf && ix.fused_cap < ix.fused_cap2) {
+                // ---- second pass: the same kernel with the largest frontier that fits one CTA per SM, only over the
+                //      patterns that did not fit; what still does not fit goes to the level-synchronous engine
+                ws.ovf_ids2.ensure(novf);
+                size_t want2 = (size_t)nstage + (size_t)novf * ix.fused_cap2;
+                if (want2 > 0xfffffff0ull) want2 = 0xfffffff0ull;
+                ws.staging.ensure(want2, s, true, nstage);
+                FusedOut fo2{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 2, ws.ovf_ids2.p};
+                launch_fused_search(ix.view, sv, ix.seed_k, d_bytes, d_off, ws.ovf_ids.p, novf, ix.lut.p, ix.fused_cap2, fo2, st, ix.canonical_k, s);
+                ws.launches += 1;
+                CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 12, cudaMemcpyDeviceToHost, s));
+                CUDA_OK(cudaStreamSynchronize(s));
+                nstage = ws.h_pin[0]; novf = ws.h_pin[2];
+                ids = ws.ovf_ids2.p;
+            }
         } else {
             CUDA_OK(cudaMemsetAsync(out.counts.p, 0, (size_t)npat * 4, s));
             CUDA_OK(cudaMemsetAsync(ws.plist.p, 0, (size_t)npat * 8, s));
@@ -812,9 +831,9 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
                 out.occ.ensure(nocc);
                 CUDA_OK(cudaEventRecord(ws.evl0, s));
                 if (ix.locate_mode == EDSBWT_LOCATE_WALK)
-                    locate_kernel<true><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, out.occ.p, st);
+                    locate_kernel<true><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, pat_base, out.occ.p, st);
                 else
-                    locate_kernel<false><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, out.occ.p, st);
+                    locate_kernel<false><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, pat_base, out.occ.p, st);
                 CUDA_OK(cudaEventRecord(ws.evl1, s));
                 ws.launches += 1; locate_ran = true;
             }
@@ -830,7 +849,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     ls = edsbwt_stats{};
     ls.I = hs.I; ls.S = hs.S; ls.E = hs.E; ls.L = hs.L; ls.O = hs.O; ls.lf_intervals = hs.lf_intervals; ls.occ_blocks = hs.occ_blocks;
     ls.steps = steps; ls.kernel_launches = ws.launches; ls.lf_kernel_ms = ws.lf_ms; ls.total_ms = ms; ls.frontier_peak = peak;
-    ls.overflow_patterns = ix.engine == EDSBWT_ENGINE_FUSED ? novf : 0;
+    ls.overflow_patterns = ix.engine == EDSBWT_ENGINE_FUSED ? novf1 : 0; ls.levelsync_patterns = novf;
     if (fused_ran) { float fm = 0; CUDA_OK(cudaEventElapsedTime(&fm, ws.evf0, ws.evf1)); ls.search_kernel_ms = fm; }
     if (locate_ran) { float lm = 0; CUDA_OK(cudaEventElapsedTime(&lm, ws.evl0, ws.evl1)); ls.locate_kernel_ms = lm; }
 }

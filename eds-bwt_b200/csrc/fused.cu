@@ -54,7 +54,8 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 template <bool STATS>
 __global__ void __launch_bounds__(FUSED_THREADS)
 fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ poff,
-                    uint32_t npat, const uint8_t* __restrict__ lut, uint32_t cap, FusedOut out, StatsDev* __restrict__ st, uint32_t kc) {
+                    const uint32_t* __restrict__ ids, uint32_t npat, const uint8_t* __restrict__ lut, uint32_t cap, FusedOut out,
+                    StatsDev* __restrict__ st, uint32_t kc) {
     extern __shared__ uint2 s_list[];                 // [cap][FUSED_THREADS]
     __shared__ uint8_t s_lut[256];
     for (int i = threadIdx.x; i < 256; i += FUSED_THREADS) s_lut[i] = lut[i];
@@ -62,8 +63,9 @@ fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __rest
 #define LIST(j) s_list[(j) * FUSED_THREADS + threadIdx.x]
 #define DOL(i) s_list[(cap - 1 - (i)) * FUSED_THREADS + threadIdx.x]
 
-    const uint32_t q = blockIdx.x * FUSED_THREADS + threadIdx.x;
-    const bool live = q < npat;
+    const uint32_t tq = blockIdx.x * FUSED_THREADS + threadIdx.x;
+    const bool live = tq < npat;
+    const uint32_t q = live ? (ids ? ids[tq] : tq) : 0u;      // second pass (large cap): only the patterns listed in ids
     uint32_t nF = 0, m = 0, L0 = 0;
     uint64_t base = 0;
     bool ovf = false;
@@ -185,7 +187,7 @@ fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __rest
         for (uint32_t j = 0; j < nF; ++j) out.staging[my + j] = LIST(j);
         out.plist[q] = make_uint2(my, nF);
         out.counts[q] = cnt;
-        if (ovf) out.ovf_ids[atomicAdd(out.cursor + 1, 1u)] = q;
+        if (ovf) out.ovf_ids[atomicAdd(out.ovf_count, 1u)] = q;
     }
     if (STATS) {
         if (ovf) sI = sS = sE = sLF = sBlk = 0;          // the level-synchronous engine redoes (and recounts) this pattern
@@ -201,17 +203,17 @@ fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __rest
 #undef DOL
 }
 
-void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat,
-                         const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s) {
+void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
+                         const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s) {
     if (npat == 0) return;
     const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
     static bool attr_set[2] = {false, false};
     if (st) {
         if (!attr_set[1]) { CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr_set[1] = true; }
-        fused_search_kernel<true><<<(npat + FUSED_THREADS - 1) / FUSED_THREADS, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, npat, d_lut, cap, out, st, kc);
+        fused_search_kernel<true><<<(npat + FUSED_THREADS - 1) / FUSED_THREADS, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
     } else {
         if (!attr_set[0]) { CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr_set[0] = true; }
-        fused_search_kernel<false><<<(npat + FUSED_THREADS - 1) / FUSED_THREADS, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, npat, d_lut, cap, out, st, kc);
+        fused_search_kernel<false><<<(npat + FUSED_THREADS - 1) / FUSED_THREADS, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
     }
     CUDA_OK(cudaGetLastError());
 }

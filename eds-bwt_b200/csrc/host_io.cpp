@@ -275,6 +275,7 @@ const char* edsbwt_strerror(int code) {
         case EDSBWT_E_CUDA: return "CUDA error / no device";
         case EDSBWT_E_ARG: return "bad argument";
         case EDSBWT_E_UNSUPPORTED: return "unsupported";
+        case EDSBWT_E_NOSPACE: return "occurrence buffer too small";
         default: return "unknown error";
     }
 }

@@ -56,6 +56,8 @@ struct DevBuf {
 // letter and of '#' (rank_# = pos - sum of letter ranks) come out of the same 64 bytes.
 // ---------------------------------------------------------------------------------------------------
 constexpr uint32_t OCC_ROWS = 128;
+constexpr int FUSED_THREADS = 128;
+constexpr uint32_t FUSED_BIG_CAP = 192;      // 192 slots x 128 threads x 8 B = 192 KB of shared memory: one CTA per SM
 
 struct IndexView {
     const uint4* occ;            // (n/128 + 1) blocks
@@ -158,6 +160,19 @@ struct SeedView { const uint32_t* off[17]; const uint2* iv[17]; };
 struct StatsDev { unsigned long long I, S, E, L, O, lf_intervals, occ_blocks, overflow; };
 
 struct Workspace;   // engine.cu
+struct SearchOut {
+    DevBuf<uint32_t> counts; DevBuf<edsbwt_occ> occ; uint32_t npat = 0; uint64_t nocc = 0;
+};
+// host-buffer searches (edsbwt_search / edsbwt_search_into): chunks of the batch are copied in on one stream while the
+// previous chunk is searched on the compute stream and the chunk before that is copied out on a third
+struct Pipe {
+    cudaStream_t in = nullptr, outs = nullptr;
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+    DevBuf<uint8_t> bytes[2]; DevBuf<uint64_t> off[2];
+    SearchOut res[2];
+    ~Pipe() { for (int i = 0; i < 2; ++i) { if (ev_in[i]) cudaEventDestroy(ev_in[i]); if (ev_out[i]) cudaEventDestroy(ev_out[i]); }
+              if (in) cudaStreamDestroy(in); if (outs) cudaStreamDestroy(outs); }
+};
 
 struct Index {
     int device = 0;
@@ -174,33 +189,32 @@ struct Index {
     std::vector<SeedLevel*> seed;       // seed[L] for L = 1..seed_k (index 0 unused)
     uint64_t seed_intervals = 0;
     Workspace* ws = nullptr;
+    Pipe* pipe = nullptr;
+    uint32_t chunk_patterns = 1u << 21;     // patterns per pipeline chunk of the host-buffer searches
     edsbwt_stats last{};
     int collect_counters = 0; uint32_t canonical_k = 12;
-    int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 24;
+    int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 24, fused_cap2 = FUSED_BIG_CAP;
     uint64_t device_bytes() const;
     ~Index();
 };
 
 // engine.cu
 void build_device_index(Index& ix, const edsbwt_open_opts& o);
-struct SearchOut {
-    DevBuf<uint32_t> counts; DevBuf<edsbwt_occ> occ; uint32_t npat = 0; uint64_t nocc = 0;
-};
 void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat, uint64_t total_bytes,
-                uint32_t max_len, bool locate, int lf_variant, SearchOut& out);
+                uint32_t max_len, bool locate, int lf_variant, SearchOut& out, uint32_t pat_base = 0);
 
 // fused.cu -- one thread per pattern, whole backward search in one launch
-constexpr int FUSED_THREADS = 128;
 struct FusedOut {
     uint2*    plist;        // [npat] (first slot in staging, number of final intervals)
     uint32_t* counts;       // [npat] number of occurrences ("Found N")
     uint2*    staging;      // final (lo,hi) row intervals, contiguous per pattern
     uint32_t  staging_cap;
-    uint32_t* cursor;       // [0] slots used in staging, [1] number of patterns handed to the level-synchronous engine
-    uint32_t* ovf_ids;      // [npat] those patterns
+    uint32_t* cursor;       // slots used in staging
+    uint32_t* ovf_count;    // number of patterns whose frontier did not fit
+    uint32_t* ovf_ids;      // those patterns
 };
-void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat,
-                         const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s);
+void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
+                         const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s);
 
 // builder.cu
 void build_index_files(const uint8_t* letters, const uint64_t* str_off, uint32_t nstr, const uint8_t* seg_first,

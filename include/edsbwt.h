@@ -22,6 +22,7 @@ extern "C" {
 #define EDSBWT_E_CUDA       -4   /* no device / CUDA runtime error / out of device memory                    */
 #define EDSBWT_E_ARG        -5   /* bad argument                                                             */
 #define EDSBWT_E_UNSUPPORTED -6
+#define EDSBWT_E_NOSPACE     -7   /* caller's occurrence buffer too small; *nocc holds the size needed             */
 
 typedef struct edsbwt_index edsbwt_index;     /* opaque, immutable after open; one handle per GPU */
 typedef struct edsbwt_result edsbwt_result;   /* opaque, device-resident result of edsbwt_search_device */
@@ -64,7 +65,8 @@ typedef struct {
     int32_t  build_move;        /* 1 = also build the move table (EDSBWT_LF_MOVE searches)                    */
     int32_t  engine;            /* EDSBWT_ENGINE_FUSED (default) / _LEVELSYNC                                 */
     int32_t  fused_cap;         /* frontier slots per pattern of the fused kernel (0 = default 24)            */
-    int32_t  reserved[2];
+    int32_t  fused_cap2;        /* slots of the second pass over the patterns that outgrew the first (0 = 192) */
+    int32_t  reserved[1];
 } edsbwt_open_opts;
 
 /* Canonical byte-model counters of DESIGN.md + engine statistics of the last search. */
@@ -78,7 +80,8 @@ typedef struct {
     double   total_ms;          /* CUDA-event time of the whole search on the library's stream                 */
     uint64_t frontier_peak;     /* largest frontier (intervals) over all steps of the level-synchronous engine  */
     uint64_t occ_blocks;        /* 64-byte Occ blocks fetched by the search kernels (collect_counters only)     */
-    uint64_t overflow_patterns; /* patterns the fused kernel handed to the level-synchronous engine            */
+    uint64_t overflow_patterns; /* patterns whose frontier outgrew the first pass of the fused kernel          */
+    uint64_t levelsync_patterns;/* patterns finally run by the level-synchronous engine                        */
     double   search_kernel_ms;  /* CUDA-event time of the fused search kernel                                   */
 } edsbwt_stats;
 
@@ -102,6 +105,16 @@ void edsbwt_index_close(edsbwt_index* idx);
  *     behaviour); empty patterns yield 0. */
 int  edsbwt_search(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat,
                    int locate, int lf_variant, uint32_t* counts, edsbwt_occ** occ, uint64_t* nocc);
+
+/* The same search into CALLER-OWNED host buffers (no allocation inside the call): counts[npat], occ[occ_cap].
+ * The batch is cut into chunks that are copied in, searched and copied out on three streams, so that PCIe
+ * traffic overlaps the kernels; buffers from edsbwt_host_alloc (pinned) make the copies truly asynchronous.
+ * Returns EDSBWT_E_NOSPACE when more than occ_cap occurrences exist (*nocc = number needed, counts valid). */
+int  edsbwt_search_into(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat,
+                        int locate, int lf_variant, uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc);
+int  edsbwt_host_alloc(void** p, uint64_t bytes);      /* page-locked host memory for the buffers above */
+void edsbwt_host_free(void* p);
+int  edsbwt_set_chunk(edsbwt_index* idx, uint32_t patterns_per_chunk);   /* pipeline granularity, default 2^21; 0 = one chunk */
 
 /* Same search with the packed patterns already resident in HBM and the results left there (the `value`
  * leg of bench.py).  d_* are DEVICE pointers on the handle's device.  total_bytes = pat_off[npat]. */

@@ -60,8 +60,8 @@ def test_random_vs_port(eb, oracle_built, tmp_path, seed, kw, seed_k):
     c_port = rows_port = None
     # the fused kernel (default), the fused kernel with a tiny frontier capacity (most patterns fall through to the
     # level-synchronous engine), and the level-synchronous engine alone: same counts, rows and byte-model counters
-    for engine, cap in [(eb.ENGINE_FUSED, 0), (eb.ENGINE_FUSED, 4), (eb.ENGINE_LEVELSYNC, 0)]:
-        with eb.Index(base, seed_k=seed_k, locate_mode=0, engine=engine, fused_cap=cap) as idx:
+    for engine, cap, cap2 in [(eb.ENGINE_FUSED, 0, 0), (eb.ENGINE_FUSED, 4, 0), (eb.ENGINE_FUSED, 4, 7), (eb.ENGINE_LEVELSYNC, 0, 0)]:
+        with eb.Index(base, seed_k=seed_k, locate_mode=0, engine=engine, fused_cap=cap, fused_cap2=cap2) as idx:
             k = idx.info().seed_k
             idx.set_stats(True, canonical_k=k)
             if c_port is None:
@@ -75,6 +75,7 @@ def test_random_vs_port(eb, oracle_built, tmp_path, seed, kw, seed_k):
                 assert st[key] == st_port[key], (engine, cap, key, st[key], st_port[key])
             if engine == eb.ENGINE_FUSED and cap == 4:
                 assert st["overflow_patterns"] > 0
+                assert cap2 == 0 or st["levelsync_patterns"] > 0
             idx.set_stats(False)
             counts, occ = idx.search(file_pats, locate=True)
             assert counts.tolist() == c_port and eb.occ_rows(occ) == sorted(rows_port)
@@ -198,3 +199,35 @@ def test_synthetic_generators_search_parity(eb, oracle_built, tmp_path):
         assert counts.tolist() == c_port
         assert eb.occ_rows(occ) == sorted(rows_port)
         assert sum(c_port) > 0.5 * npat
+
+
+def test_search_into_pipelined_chunks(eb, oracle_built, tmp_path):
+    """Caller-owned (pinned) buffers, batch cut into pipeline chunks: same counts / rows as one call; E_NOSPACE."""
+    rng = np.random.default_rng(91)
+    segs = E.random_eds(rng, n_seg=1500, max_var=4, max_len=6, p_empty=0.15, nondeg_len=(1, 40))
+    _, base = _index_files(tmp_path, segs)
+    pats = E.sample_patterns(rng, segs, 1000, [4, 9, 16, 32, 33, 64])
+    data, off = eb.pack_patterns(pats)
+    with eb.Index(base) as idx:
+        c_ref, o_ref = idx.search(pats, locate=True)
+        p_data = eb.pinned_empty(data.size, np.uint8); p_data[:] = data
+        p_off = eb.pinned_empty(off.size, np.uint64); p_off[:] = off
+        for chunk in [0, 1000, 333, 64, 1]:
+            idx.set_chunk(chunk)
+            counts = eb.pinned_empty(len(pats), np.uint32); counts[:] = 0xffffffff
+            occ = eb.pinned_empty(len(o_ref) + 5, eb.OCC_DTYPE)
+            n = idx.search_into(p_data, p_off, counts, occ, locate=True)
+            assert n == len(o_ref) and counts.tolist() == c_ref.tolist()
+            assert eb.occ_rows(occ[:n]) == eb.occ_rows(o_ref)
+            assert np.all(np.diff(occ[:n]["pat"].astype(np.int64)) >= 0)
+            counts[:] = 0
+            assert idx.search_into(p_data, p_off, counts, None, locate=False) == 0 and counts.tolist() == c_ref.tolist()
+        idx.set_chunk(100)
+        small = eb.pinned_empty(max(1, len(o_ref) // 2), eb.OCC_DTYPE)
+        with pytest.raises(eb.EdsbwtError) as ei:
+            idx.search_into(p_data, p_off, counts, small, locate=True)
+        assert ei.value.code == -7
+        # plain (pageable) numpy buffers work too
+        idx.set_chunk(1 << 21)
+        counts2 = np.zeros(len(pats), np.uint32); occ2 = np.zeros(len(o_ref), eb.OCC_DTYPE)
+        assert idx.search_into(data, off, counts2, occ2) == len(o_ref) and eb.occ_rows(occ2) == eb.occ_rows(o_ref)
