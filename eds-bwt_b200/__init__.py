@@ -24,7 +24,7 @@ EXPORTS = [
     "edsbwt_result_free", "edsbwt_last_stats", "edsbwt_set_stats", "edsbwt_write_csv", "edsbwt_read_patterns",
     "edsbwt_build_from_eds", "edsbwt_build_from_collection", "edsbwt_gather_bench", "edsbwt_free",
     "edsbwt_strerror", "edsbwt_last_error", "edsbwt_version", "edsbwt_search_into", "edsbwt_host_alloc", "edsbwt_host_free",
-    "edsbwt_set_chunk",
+    "edsbwt_set_chunk", "edsbwt_search_trace",
 ]
 
 
@@ -82,6 +82,7 @@ def lib():
                                     C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
         L.edsbwt_search_into.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
                                          C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.edsbwt_search_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
         L.edsbwt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_uint64]
         L.edsbwt_host_free.argtypes = [C.c_void_p]
         L.edsbwt_host_free.restype = None
@@ -177,6 +178,15 @@ class Index:
             occ = np.frombuffer(buf, dtype=OCC_DTYPE).copy()
             lib().edsbwt_free(occ_p)
         return counts[:npat], occ
+
+    def search_trace(self, patterns, lf_variant=LF_RANK):
+        """count-only search + the reference's "interrupted in position" value per pattern (0 = no such line)."""
+        data, off = pack_patterns(patterns)
+        npat = len(off) - 1
+        counts = np.zeros(max(npat, 1), dtype=np.uint32)
+        pos = np.zeros(max(npat, 1), dtype=np.uint32)
+        _check(lib().edsbwt_search_trace(self._h, data.ctypes.data, off.ctypes.data, npat, lf_variant, counts.ctypes.data, pos.ctypes.data))
+        return counts[:npat], pos[:npat]
 
     def search_into(self, data, off, counts, occ=None, locate=True, lf_variant=LF_RANK):
         """Caller-owned host buffers (ideally from pinned_empty): counts uint32[npat], occ OCC_DTYPE[cap].

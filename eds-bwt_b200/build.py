@@ -22,7 +22,7 @@ def _newer(target, deps):
 
 def build(force=False, verbose=False):
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
-    hdrs = [os.path.join(CSRC, "internal.cuh"), os.path.join(HERE, "..", "include", "edsbwt.h")]
+    hdrs = [os.path.join(CSRC, "internal.cuh"), os.path.join(HERE, "..", "include", "edsbwt.h"), os.path.join(CSRC, "cli_common.hpp")]
     objs = []
     for src in LIB_SRCS:
         sp = os.path.join(CSRC, src)

@@ -74,35 +74,37 @@ int edsbwt_search_device(edsbwt_index* idx, const uint8_t* d_pat_bytes, const ui
                          uint64_t total_bytes, uint32_t max_len, int locate, int lf_variant, edsbwt_result** res) {
     if (!idx || !res || (npat && (!d_pat_off))) return EDSBWT_E_ARG;
     *res = nullptr;
-    edsbwt_result* r = new edsbwt_result; r->device = idx->ix.device;
-    int rc = guarded([&] { run_search(idx->ix, d_pat_bytes, d_pat_off, npat, total_bytes, max_len, locate != 0, lf_variant, r->out); });
-    if (rc) { cudaSetDevice(idx->ix.device); delete r; return rc; }
+    edsbwt_result* r = new edsbwt_result; r->device = idx->ix.device; r->pool = idx->ix.pool; r->outp = r->pool->get();
+    r->outp->want_alive = false;
+    int rc = guarded([&] { run_search(idx->ix, d_pat_bytes, d_pat_off, npat, total_bytes, max_len, locate != 0, lf_variant, *r->outp); });
+    if (rc) { cudaSetDevice(idx->ix.device); r->pool->put(r->outp); delete r; return rc; }
     *res = r;
     return EDSBWT_OK;
 }
 int edsbwt_result_sizes(const edsbwt_result* res, uint32_t* npat, uint64_t* nocc) {
     if (!res) return EDSBWT_E_ARG;
-    if (npat) *npat = res->out.npat;
-    if (nocc) *nocc = res->out.nocc;
+    if (npat) *npat = res->outp->npat;
+    if (nocc) *nocc = res->outp->nocc;
     return EDSBWT_OK;
 }
 int edsbwt_result_device_ptrs(const edsbwt_result* res, const uint32_t** d_counts, const edsbwt_occ** d_occ) {
     if (!res) return EDSBWT_E_ARG;
-    if (d_counts) *d_counts = res->out.counts.p;
-    if (d_occ) *d_occ = res->out.occ.p;
+    if (d_counts) *d_counts = res->outp->counts.p;
+    if (d_occ) *d_occ = res->outp->occ.p;
     return EDSBWT_OK;
 }
 int edsbwt_result_fetch(const edsbwt_result* res, uint32_t* counts, edsbwt_occ* occ) {
     if (!res) return EDSBWT_E_ARG;
     return guarded([&] {
         CUDA_OK(cudaSetDevice(res->device));
-        if (counts && res->out.npat) CUDA_OK(cudaMemcpy(counts, res->out.counts.p, (size_t)res->out.npat * 4, cudaMemcpyDeviceToHost));
-        if (occ && res->out.nocc) CUDA_OK(cudaMemcpy(occ, res->out.occ.p, (size_t)res->out.nocc * sizeof(edsbwt_occ), cudaMemcpyDeviceToHost));
+        if (counts && res->outp->npat) CUDA_OK(cudaMemcpy(counts, res->outp->counts.p, (size_t)res->outp->npat * 4, cudaMemcpyDeviceToHost));
+        if (occ && res->outp->nocc) CUDA_OK(cudaMemcpy(occ, res->outp->occ.p, (size_t)res->outp->nocc * sizeof(edsbwt_occ), cudaMemcpyDeviceToHost));
     });
 }
 void edsbwt_result_free(edsbwt_result* res) {
     if (!res) return;
     cudaSetDevice(res->device);
+    res->pool->put(res->outp);
     delete res;
 }
 
@@ -197,6 +199,34 @@ int edsbwt_search(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* p
         cap = got;
     }
     return EDSBWT_E_UNSUPPORTED;
+}
+
+int edsbwt_search_trace(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat, int lf_variant,
+                        uint32_t* counts, uint32_t* interrupted) {
+    if (!idx || (npat && (!pat_off || !counts || !interrupted))) return EDSBWT_E_ARG;
+    if (npat == 0) return EDSBWT_OK;
+    return guarded([&] {
+        Index& ix = idx->ix;
+        CUDA_OK(cudaSetDevice(ix.device));
+        const uint64_t nb = pat_off[npat] - pat_off[0];
+        uint32_t max_len = 0;
+        for (uint32_t i = 0; i < npat; ++i) { uint64_t l = pat_off[i + 1] - pat_off[i]; if (l > 0xffffffffull) EDS_FAIL(EDSBWT_E_ARG, "pattern %u too long", i); if (l > max_len) max_len = (uint32_t)l; }
+        DevBuf<uint8_t> d_bytes; DevBuf<uint64_t> d_off; d_bytes.ensure(nb + 16); d_off.ensure((size_t)npat + 1);
+        if (nb) CUDA_OK(cudaMemcpy(d_bytes.p, pat_bytes + pat_off[0], nb, cudaMemcpyHostToDevice));
+        CUDA_OK(cudaMemcpy(d_off.p, pat_off, ((size_t)npat + 1) * 8, cudaMemcpyHostToDevice));
+        SearchOut out; out.want_alive = true;
+        run_search(ix, (const uint8_t*)((uintptr_t)d_bytes.p - (uintptr_t)pat_off[0]), d_off.p, npat, nb, max_len, false, lf_variant, out);
+        CUDA_OK(cudaMemcpy(counts, out.counts.p, (size_t)npat * 4, cudaMemcpyDeviceToHost));
+        CUDA_OK(cudaMemcpy(interrupted, out.alive.p, (size_t)npat * 4, cudaMemcpyDeviceToHost));
+        for (uint32_t i = 0; i < npat; ++i) {
+            // alive = longest suffix with a non-empty frontier; the reference's loop index when it gives up is m - alive,
+            // except that its initial interval of an absent letter survives until the first step (posSymb = m-1)
+            const uint32_t m = (uint32_t)(pat_off[i + 1] - pat_off[i]), alive = interrupted[i];
+            uint32_t pos = 0;
+            if (m >= 2 && counts[i] == 0 && alive < m) { pos = m - alive; if (pos > m - 1) pos = m - 1; }
+            interrupted[i] = pos;
+        }
+    });
 }
 
 int edsbwt_host_alloc(void** p, uint64_t bytes) {

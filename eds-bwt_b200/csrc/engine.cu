@@ -694,7 +694,7 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     CUDA_OK(cudaStreamSynchronize(s));
     // ---- seed table
     int k = o.seed_k;
-    if (k < 0) { k = 1; while (k < 12 && (1ull << (2 * (k + 2))) <= (uint64_t)h.n) ++k; }
+    if (k < 0) { k = 1; while (k < 14 && (1ull << (2 * (k + 1))) <= (uint64_t)h.n) ++k; }      // floor(log4 n), at most 14
     if (k < 1) k = 1;
     if (k > 14) k = 14;
     ix.seed_k = (uint32_t)k;
@@ -710,15 +710,41 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
 // ---------------------------------------------------------------------------------------------------
 // Level-synchronous search of a subset (ids == nullptr: the whole batch).  Leaves the final frontier, grouped by LOCAL
 // pattern index, in ws.cur and returns its length.
+// alive[g] = longest suffix of pattern g with a non-empty frontier (edsbwt_search_trace): seed part ...
+__global__ void ls_alive_init_kernel(PatView pv, SeedView sv, const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ ids, uint32_t* __restrict__ alive) {
+    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= pv.npat) return;
+    uint32_t m = pv.len[q], la = 0;
+    if (m) {
+        uint32_t L0 = m < pv.k ? m : pv.k;
+        if (cnt[q]) la = L0;
+        else for (uint32_t L = L0 - 1; L >= 1; --L) {
+            uint32_t key = 0;
+            for (uint32_t i = 0; i < L; ++i) key |= pat_char(pv, q, m - L + i) << (2 * i);
+            if (__ldg(sv.off[L] + key + 1) > __ldg(sv.off[L] + key)) { la = L; break; }
+        }
+    }
+    alive[ids ? ids[q] : q] = la;
+}
+// ... and one mark per backward step for every pattern still present in the frontier
+__global__ void ls_alive_mark_kernel(PatView pv, uint32_t step, const uint32_t* __restrict__ pat, uint32_t nF, const uint32_t* __restrict__ ids, uint32_t* __restrict__ alive) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nF) return;
+    uint32_t q = pat[i];
+    if (i && pat[i - 1] == q) return;
+    uint32_t m = pv.len[q], L = (m < pv.k ? m : pv.k) + step + 1;
+    alive[ids ? ids[q] : q] = L < m ? L : m;
+}
+
 static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, const uint32_t* ids, uint32_t nsub, uint32_t max_len,
-                                 StatsDev* st, uint32_t& steps, uint64_t& peak) {
+                                 StatsDev* st, uint32_t& steps, uint64_t& peak, uint32_t* d_alive, uint32_t k_eff) {
     Workspace& ws = *ix.ws;
     cudaStream_t s = ix.stream;
     uint32_t words = (max_len + 31) / 32; if (!words) words = 1;
     ws.ppack.ensure((size_t)nsub * words); ws.plen.ensure(nsub);
     Lut lut = make_lut(ix.host);
     encode_patterns_kernel<<<grid_for(nsub, 128), 128, 0, s>>>(d_bytes, d_off, ids, nsub, lut, words, ws.ppack.p, ws.plen.p);
-    PatView pv{ws.ppack.p, ws.plen.p, words, nsub, ix.seed_k};
+    PatView pv{ws.ppack.p, ws.plen.p, words, nsub, k_eff};
     SeedView sv{};
     for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; }
     ws.cnt.ensure(nsub + 1); ws.src.ensure(nsub); ws.base.ensure(nsub + 1);
@@ -727,12 +753,14 @@ static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64
     exclusive_sum(ws, ws.cnt.p, ws.base.p, (size_t)nsub + 1, s);
     ws.launches += 2;
     uint32_t nF = read_u32(ws, ws.base.p + nsub, s);
+    if (d_alive) { ls_alive_init_kernel<<<grid_for(nsub, 256), 256, 0, s>>>(pv, sv, ws.cnt.p, ids, d_alive); ws.launches += 1; }
     ws.cur.ensure(nF ? nF : 1);
     if (nF) { seed_scatter_kernel<<<grid_for(nF, 256), 256, 0, s>>>(pv, sv, ws.base.p, ws.src.p, nF, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p); ws.launches += 1; }
     if (nF > peak) peak = nF;
-    uint32_t total_steps = max_len > ix.seed_k ? max_len - ix.seed_k : 0;
+    uint32_t total_steps = max_len > k_eff ? max_len - k_eff : 0;
     for (uint32_t t = 0; t < total_steps && nF; ++t) {
         nF = engine_step<false>(ix, ws, pv, t, nF, st, ix.canonical_k, true);
+        if (d_alive && nF) { ls_alive_mark_kernel<<<grid_for(nF, 256), 256, 0, s>>>(pv, t, ws.cur.pat.p, nF, ids, d_alive); ws.launches += 1; }
         ++steps;
         if (nF > peak) peak = nF;
     }
@@ -750,11 +778,16 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     cudaStream_t s = ix.stream;
     ws.launches = 0; ws.lf_ms = 0;
     const bool stats = ix.collect_counters != 0;
+    // counters are defined relative to the canonical seed depth: a counting run starts from the seed level
+    // min(k, canonical_k) so that every step beyond the canonical depth is really executed and counted
+    const uint32_t k_eff = stats ? std::min(ix.seed_k, ix.canonical_k) : ix.seed_k;
     StatsDev* st = stats ? ws.d_stats : nullptr;
     CUDA_OK(cudaMemsetAsync(ws.d_stats, 0, sizeof(StatsDev), s));
     CUDA_OK(cudaEventRecord(ws.ev0, s));
     out.npat = npat; out.nocc = 0;
     out.counts.ensure(npat ? npat : 1);
+    uint32_t* d_alive = nullptr;
+    if (out.want_alive) { out.alive.ensure(npat ? npat : 1); d_alive = out.alive.p; }
     uint32_t steps = 0, novf = 0, novf1 = 0; uint64_t peak = 0;
     bool fused_ran = false, locate_ran = false;
     if (npat) {
@@ -769,9 +802,9 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             ws.staging.ensure(want); ws.ovf_ids.ensure(npat);
             SeedView sv{};
             for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; }
-            FusedOut fo{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 1, ws.ovf_ids.p};
+            FusedOut fo{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 1, ws.ovf_ids.p, d_alive};
             CUDA_OK(cudaEventRecord(ws.evf0, s));
-            launch_fused_search(ix.view, sv, ix.seed_k, d_bytes, d_off, nullptr, npat, ix.lut.p, ix.fused_cap, fo, st, ix.canonical_k, s);
+            launch_fused_search(ix.view, sv, k_eff, d_bytes, d_off, nullptr, npat, ix.lut.p, ix.fused_cap, fo, st, ix.canonical_k, s);
             CUDA_OK(cudaEventRecord(ws.evf1, s));
             ws.launches += 1; fused_ran = true;
             CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 8, cudaMemcpyDeviceToHost, s));
@@ -786,8 +819,8 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
                 size_t want2 = (size_t)nstage + (size_t)novf * ix.fused_cap2;
                 if (want2 > 0xfffffff0ull) want2 = 0xfffffff0ull;
                 ws.staging.ensure(want2, s, true, nstage);
-                FusedOut fo2{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 2, ws.ovf_ids2.p};
-                launch_fused_search(ix.view, sv, ix.seed_k, d_bytes, d_off, ws.ovf_ids.p, novf, ix.lut.p, ix.fused_cap2, fo2, st, ix.canonical_k, s);
+                FusedOut fo2{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 2, ws.ovf_ids2.p, d_alive};
+                launch_fused_search(ix.view, sv, k_eff, d_bytes, d_off, ws.ovf_ids.p, novf, ix.lut.p, ix.fused_cap2, fo2, st, ix.canonical_k, s);
                 ws.launches += 1;
                 CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 12, cudaMemcpyDeviceToHost, s));
                 CUDA_OK(cudaStreamSynchronize(s));
@@ -801,7 +834,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
         }
         if (novf) {
             // ---- level-synchronous engine: the whole batch (ENGINE_LEVELSYNC) or the patterns whose frontier outgrew the fused kernel
-            uint32_t nF = levelsync_search(ix, d_bytes, d_off, ids, novf, max_len, st, steps, peak);
+            uint32_t nF = levelsync_search(ix, d_bytes, d_off, ids, novf, max_len, st, steps, peak, d_alive, k_eff);
             if (nF) {
                 if ((uint64_t)nstage + nF > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 result intervals in one batch; split the batch");
                 ws.staging.ensure((size_t)nstage + nF, s, true, nstage);

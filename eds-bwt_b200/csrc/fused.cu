@@ -66,7 +66,7 @@ fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __rest
     const uint32_t tq = blockIdx.x * FUSED_THREADS + threadIdx.x;
     const bool live = tq < npat;
     const uint32_t q = live ? (ids ? ids[tq] : tq) : 0u;      // second pass (large cap): only the patterns listed in ids
-    uint32_t nF = 0, m = 0, L0 = 0;
+    uint32_t nF = 0, m = 0, L0 = 0, key = 0;
     uint64_t base = 0;
     bool ovf = false;
     unsigned long long sI = 0, sS = 0, sE = 0, sLF = 0, sBlk = 0;
@@ -76,7 +76,6 @@ fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __rest
         m = len64 > 0xffffffffull ? 0u : (uint32_t)len64;
         L0 = m < k ? m : k;
         bool ok = m > 0;
-        uint32_t key = 0;
         for (uint32_t i = 0; i < m; ++i) {
             uint32_t c = s_lut[__ldg(bytes + base + i)];
             if (c > 3) { ok = false; c = 0; }
@@ -169,6 +168,18 @@ fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __rest
         nF = nout;
     }
     if (STATS && !ovf && live && m && L0 + s == mk) sI += nF;            // frontier left at suffix length min(m, kc)
+    if (out.alive && live && !ovf) {
+        // where the frontier died ("Pattern not found, interrupted in position", EDSBWTsearch.cpp:714-717)
+        uint32_t la = 0;
+        if (m == 0) la = 0;
+        else if (nF) la = m;
+        else if (s > 0) la = L0 + s - 1;
+        else for (uint32_t L = L0 - 1; L >= 1; --L) {                     // empty seed entry: longest shorter suffix that is not
+            const uint32_t kl = key >> (2 * (L0 - L));
+            if (__ldg(sv.off[L] + kl + 1) > __ldg(sv.off[L] + kl)) { la = L; break; }
+        }
+        out.alive[q] = la;
+    }
     // ---- results: per-pattern count + the final interval list, staged contiguously per warp
     uint32_t cnt = 0;
     if (ovf) nF = 0;

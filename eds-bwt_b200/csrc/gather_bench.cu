@@ -9,10 +9,13 @@ __global__ void __launch_bounds__(256) gather64_kernel(const uint4* __restrict__
     uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     uint32_t acc = 0;
+    // 4 independent gathers in flight per thread (the search kernels get their memory-level parallelism from
+    // occupancy; the denominator should not be handicapped by a dependent loop)
+    #pragma unroll 4
     for (uint64_t g = gid; g < n_access * 4; g += stride) {
         uint64_t i = g >> 2; uint32_t lane4 = (uint32_t)g & 3;
         uint64_t h = (i + seed) * 0x9E3779B97F4A7C15ull; h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
-        uint64_t blk = h % nblocks;
+        uint64_t blk = ((h >> 32) * nblocks) >> 32;         // nblocks < 2^32: multiply-shift instead of a 64-bit modulo
         uint4 v = __ldg(buf + blk * 4 + lane4);
         acc += v.x ^ v.y ^ v.z ^ v.w;
     }

@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -162,6 +163,7 @@ struct StatsDev { unsigned long long I, S, E, L, O, lf_intervals, occ_blocks, ov
 struct Workspace;   // engine.cu
 struct SearchOut {
     DevBuf<uint32_t> counts; DevBuf<edsbwt_occ> occ; uint32_t npat = 0; uint64_t nocc = 0;
+    DevBuf<uint32_t> alive; bool want_alive = false;    // alive[q] = longest suffix of pattern q whose frontier is non-empty
 };
 // host-buffer searches (edsbwt_search / edsbwt_search_into): chunks of the batch are copied in on one stream while the
 // previous chunk is searched on the compute stream and the chunk before that is copied out on a third
@@ -172,6 +174,15 @@ struct Pipe {
     SearchOut res[2];
     ~Pipe() { for (int i = 0; i < 2; ++i) { if (ev_in[i]) cudaEventDestroy(ev_in[i]); if (ev_out[i]) cudaEventDestroy(ev_out[i]); }
               if (in) cudaStreamDestroy(in); if (outs) cudaStreamDestroy(outs); }
+};
+
+// device buffers of finished searches are recycled: edsbwt_result_free hands them back instead of cudaFree (which
+// synchronises the device and costs more than the locate kernel at cfg4 sizes)
+struct ResultPool {
+    std::mutex mu; std::vector<SearchOut*> free_list;
+    SearchOut* get() { std::lock_guard<std::mutex> l(mu); if (free_list.empty()) return new SearchOut; SearchOut* r = free_list.back(); free_list.pop_back(); return r; }
+    void put(SearchOut* r) { { std::lock_guard<std::mutex> l(mu); if (free_list.size() < 4) { free_list.push_back(r); return; } } delete r; }
+    ~ResultPool() { for (SearchOut* r : free_list) delete r; }
 };
 
 struct Index {
@@ -190,6 +201,7 @@ struct Index {
     uint64_t seed_intervals = 0;
     Workspace* ws = nullptr;
     Pipe* pipe = nullptr;
+    std::shared_ptr<ResultPool> pool = std::make_shared<ResultPool>();
     uint32_t chunk_patterns = 1u << 21;     // patterns per pipeline chunk of the host-buffer searches
     edsbwt_stats last{};
     int collect_counters = 0; uint32_t canonical_k = 12;
@@ -212,6 +224,7 @@ struct FusedOut {
     uint32_t* cursor;       // slots used in staging
     uint32_t* ovf_count;    // number of patterns whose frontier did not fit
     uint32_t* ovf_ids;      // those patterns
+    uint32_t* alive;        // optional [npat]: longest pattern suffix with a non-empty frontier (edsbwt_search_trace)
 };
 void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
                          const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s);
@@ -225,4 +238,4 @@ double gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, int it
 }  // namespace edsbwt
 
 struct edsbwt_index { edsbwt::Index ix; };
-struct edsbwt_result { edsbwt::SearchOut out; int device; };
+struct edsbwt_result { edsbwt::SearchOut* outp; std::shared_ptr<edsbwt::ResultPool> pool; int device; };

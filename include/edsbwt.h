@@ -112,6 +112,12 @@ int  edsbwt_search(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* 
  * Returns EDSBWT_E_NOSPACE when more than occ_cap occurrences exist (*nocc = number needed, counts valid). */
 int  edsbwt_search_into(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat,
                         int locate, int lf_variant, uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc);
+/* Count-only search that also reports where each not-found pattern died, for the RECOVERBW=0 stderr line
+ * "Pattern not found, interrupted in position <posSymb>" (EDSBWTsearch.cpp:714-717): interrupted[i] = that posSymb
+ * (the frontier became empty when character posSymb-1 of the pattern was prepended), 0 = no such line (pattern
+ * found, single-character pattern, or pattern rejected for a byte outside the alphabet). */
+int  edsbwt_search_trace(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat,
+                         int lf_variant, uint32_t* counts, uint32_t* interrupted);
 int  edsbwt_host_alloc(void** p, uint64_t bytes);      /* page-locked host memory for the buffers above */
 void edsbwt_host_free(void* p);
 int  edsbwt_set_chunk(edsbwt_index* idx, uint32_t patterns_per_chunk);   /* pipeline granularity, default 2^21; 0 = one chunk */

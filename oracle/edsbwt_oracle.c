@@ -213,7 +213,8 @@ typedef struct { IvVec F, Dol; U32Vec d; IvBWVec R, R2; } Scratch;
 
 /* backwardSearch, EDSBWTsearch.cpp:619-772 */
 static uint32_t backward_search(const Index *ix, const uint8_t *P, uint32_t m, uint32_t patNo, int do_locate,
-                                uint32_t kseed, Scratch *sc, RowVec *rows, Counters *ct) {
+                                uint32_t kseed, Scratch *sc, RowVec *rows, Counters *ct, uint32_t *interrupted) {
+    *interrupted = 0;
     if (m == 0) return 0;
     for (uint32_t i = 0; i < m; i++) if (ix->alpha[P[i]] <= 0) return 0;      /* App. C.2 deviation */
     int p = ix->alpha[P[m - 1]];
@@ -235,6 +236,7 @@ static uint32_t backward_search(const Index *ix, const uint8_t *P, uint32_t m, u
         IvVec t = sc->F; sc->F = sc->Dol; sc->Dol = t;
         p = c; suffix_len++;
         if (suffix_len == (m < kseed ? m : kseed)) ct->I += sc->F.n;
+        if (!sc->F.n) *interrupted = pos;     /* "Pattern not found, interrupted in position", :714-717 (RECOVERBW=0) */
     }
     uint32_t res = 0;
     for (size_t t = 0; t < sc->F.n; t++) res += sc->F.a[t].e - sc->F.a[t].s + 1;
@@ -249,11 +251,12 @@ static uint32_t backward_search(const Index *ix, const uint8_t *P, uint32_t m, u
 static double now_s(void) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec + 1e-9 * ts.tv_nsec; }
 
 int main(int argc, char **argv) {
-    if (argc < 3) { fprintf(stderr, "usage: %s indexBase patternsFile [--csv F] [--counts F] [--locate 0|1] [--threads T] [--k K] [--limit N]\n", argv[0]); return 1; }
-    const char *csv = NULL, *cntf = NULL; int do_locate = 1, threads = 1; uint32_t kseed = 12; long limit = -1;
+    if (argc < 3) { fprintf(stderr, "usage: %s indexBase patternsFile [--csv F] [--counts F] [--interrupted F] [--locate 0|1] [--threads T] [--k K] [--limit N]\n", argv[0]); return 1; }
+    const char *csv = NULL, *cntf = NULL, *intf = NULL; int do_locate = 1, threads = 1; uint32_t kseed = 12; long limit = -1;
     for (int i = 3; i + 1 < argc; i += 2) {
         if (!strcmp(argv[i], "--csv")) csv = argv[i + 1];
         else if (!strcmp(argv[i], "--counts")) cntf = argv[i + 1];
+        else if (!strcmp(argv[i], "--interrupted")) intf = argv[i + 1];
         else if (!strcmp(argv[i], "--locate")) do_locate = atoi(argv[i + 1]);
         else if (!strcmp(argv[i], "--threads")) threads = atoi(argv[i + 1]);
         else if (!strcmp(argv[i], "--k")) kseed = (uint32_t)atoi(argv[i + 1]);
@@ -272,6 +275,7 @@ int main(int argc, char **argv) {
     }
     if (limit >= 0 && (size_t)limit < npat) npat = (size_t)limit;
     uint32_t *counts = calloc(npat ? npat : 1, 4);
+    uint32_t *interr = calloc(npat ? npat : 1, 4);
     RowVec *prow = calloc(npat ? npat : 1, sizeof(RowVec));
     Counters tot = {0, 0, 0, 0, 0};
 #ifdef _OPENMP
@@ -285,7 +289,7 @@ int main(int argc, char **argv) {
         Scratch sc; memset(&sc, 0, sizeof sc); Counters ct = {0, 0, 0, 0, 0};
 #pragma omp for schedule(dynamic, 16)
         for (long i = 0; i < (long)npat; i++)
-            counts[i] = backward_search(&ix, pbuf + pstart[i], pl[i], (uint32_t)i + 1, do_locate, kseed, &sc, &prow[i], &ct);
+            counts[i] = backward_search(&ix, pbuf + pstart[i], pl[i], (uint32_t)i + 1, do_locate, kseed, &sc, &prow[i], &ct, &interr[i]);
 #pragma omp critical
         { tot.I += ct.I; tot.S += ct.S; tot.E += ct.E; tot.L += ct.L; tot.O += ct.O; }
         free(sc.F.a); free(sc.Dol.a); free(sc.d.a); free(sc.R.a); free(sc.R2.a);
@@ -298,6 +302,7 @@ int main(int argc, char **argv) {
         for (size_t i = 0; i < npat; i++) for (size_t r = 0; r < prow[i].n; r++) { Row *q = &prow[i].a[r]; fprintf(f, "%u\t%u\t%u\t%u\t%u\n", q->pat, q->w, q->seg, q->j, q->off); }
         fclose(f);
     }
+    if (intf) { FILE *f = fopen(intf, "w"); if (!f) return 1; for (size_t i = 0; i < npat; i++) fprintf(f, "%u\n", interr[i]); fclose(f); }
     if (cntf) { FILE *f = fopen(cntf, "w"); if (!f) return 1; for (size_t i = 0; i < npat; i++) fprintf(f, "%u\n", counts[i]); fclose(f); }
     printf("{\"patterns\": %zu, \"found\": %zu, \"seconds\": %.6f, \"threads\": %d, \"k\": %u, \"I\": %llu, \"S\": %llu, \"E\": %llu, \"L\": %llu, \"O\": %llu}\n",
            npat, found, t1 - t0, threads, kseed, (unsigned long long)tot.I, (unsigned long long)tot.S, (unsigned long long)tot.E,

@@ -32,7 +32,7 @@ def run_port(base, patterns_file, locate=True, threads=1, k=12, limit=None):
     """-> (counts list, sorted rows list or None, stats dict)."""
     with tempfile.TemporaryDirectory() as d:
         cmd = [PORT, base, patterns_file, "--counts", d + "/c", "--locate", "1" if locate else "0",
-               "--threads", str(threads), "--k", str(k)]
+               "--threads", str(threads), "--k", str(k), "--interrupted", d + "/i"]
         if locate:
             cmd += ["--csv", d + "/o.csv"]
         if limit is not None:
@@ -40,6 +40,7 @@ def run_port(base, patterns_file, locate=True, threads=1, k=12, limit=None):
         r = subprocess.run(cmd, capture_output=True, text=True, check=True)
         stats = json.loads(r.stdout.strip().splitlines()[-1])
         counts = [int(x) for x in open(d + "/c").read().split()]
+        stats["interrupted"] = [int(x) for x in open(d + "/i").read().split()]
         rows = None
         if locate:
             rows = []

@@ -33,6 +33,15 @@ def make(name, eds_text, patterns, note):
         c0, _, _, p0 = R.run_ref(base, pf, "rb0")
     assert p1.returncode == 1 and p0.returncode == 1, (p1.returncode, p0.returncode)
     assert c0 == c1 and len(c1) == len(patterns)
+    # RECOVERBW=0 stderr: one "Pattern not found, interrupted in position <posSymb>" per pattern whose frontier dies
+    # inside the loop (EDSBWTsearch.cpp:714-717); never printed for single-character patterns
+    import re
+    pos = [int(x) for x in re.findall(r"interrupted in position (\d+)", p0.stderr)]
+    who = [i for i, p in enumerate(patterns) if c0[i] == 0 and len(p) >= 2]
+    assert len(pos) == len(who), (name, len(pos), len(who))
+    interrupted = [0] * len(patterns)
+    for i, v in zip(who, pos):
+        interrupted[i] = v
     bf = []
     for i, p in enumerate(patterns):
         bf += [(i + 1,) + t for t in E.brute_force(segs, p)]
@@ -42,6 +51,7 @@ def make(name, eds_text, patterns, note):
         "eds": eds_text.decode() if isinstance(eds_text, bytes) else eds_text,
         "patterns": [p.decode() for p in patterns],
         "counts": c1,
+        "interrupted": interrupted,
         "rows_reference_order": rows,
         "ebwt": ix.ebwt.decode(), "n": ix.n, "n_text": ix.n_text,
     }

@@ -231,3 +231,68 @@ def test_search_into_pipelined_chunks(eb, oracle_built, tmp_path):
         idx.set_chunk(1 << 21)
         counts2 = np.zeros(len(pats), np.uint32); occ2 = np.zeros(len(o_ref), eb.OCC_DTYPE)
         assert idx.search_into(data, off, counts2, occ2) == len(o_ref) and eb.occ_rows(occ2) == eb.occ_rows(o_ref)
+
+
+# ---- count-only trace (RECOVERBW=0 stderr line) and the two drop-in executables ---------------------------------
+@pytest.mark.parametrize("name", golden_names())
+@pytest.mark.parametrize("seed_k,engine,cap", [(-1, 0, 0), (1, 0, 0), (4, 0, 4), (3, 1, 0)])
+def test_trace_interrupted_positions(eb, tmp_path, name, seed_k, engine, cap):
+    g = load_golden(name)
+    _, base = _index_files(tmp_path, E.parse_eds(g["eds"]))
+    with eb.Index(base, seed_k=seed_k, engine=engine, fused_cap=cap) as idx:
+        counts, pos = idx.search_trace(g["patterns"])
+    assert counts.tolist() == g["counts"]
+    assert pos.tolist() == g["interrupted"]
+
+
+def test_trace_vs_port_random(eb, oracle_built, tmp_path):
+    rng = np.random.default_rng(31)
+    segs = E.random_eds(rng, n_seg=2500, max_var=5, max_len=6, p_empty=0.2, nondeg_len=(1, 50))
+    _, base = _index_files(tmp_path, segs)
+    pats = E.sample_patterns(rng, segs, 800, [1, 2, 3, 5, 8, 13, 21, 32, 50, 64])
+    pf = str(tmp_path / "p.txt")
+    E.write_patterns(pf, pats)
+    c_port, _, st = oracle_built.run_port(base, pf, locate=False)
+    for seed_k, cap in [(-1, 0), (5, 4), (2, 0)]:
+        with eb.Index(base, seed_k=seed_k, fused_cap=cap) as idx:
+            counts, pos = idx.search_trace(pats)
+        assert counts.tolist() == c_port
+        assert pos.tolist() == st["interrupted"]
+
+
+def _run_cli(exe, base, pf, env=None):
+    import subprocess
+    e = dict(os.environ)
+    e.update(env or {})
+    return subprocess.run([exe, base, pf], capture_output=True, text=True, env=e)
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_cli_edsbwtsearch_dropin(eb, tmp_path, name):
+    """EDSBWTsearch <index> <patterns>: exit status 1, "Found N" lines, <patterns>output.csv rows, count_found lines;
+    EDSBWT_RECOVERBW=0: no csv, "interrupted in position" lines (the reference's -DRECOVERBW=0 build)."""
+    import re
+    g = load_golden(name)
+    _, base = _index_files(tmp_path, E.parse_eds(g["eds"]))
+    pf = str(tmp_path / "kmers.txt")
+    E.write_patterns(pf, g["patterns"])
+    exe = os.path.join(os.path.dirname(eb.__file__), "EDSBWTsearch")
+    r = _run_cli(exe, base, pf)
+    assert r.returncode == 1, r.stderr
+    assert [int(x) for x in re.findall(r"Found (\d+) starting positions of occurrences of pattern number \d+", r.stdout)] == g["counts"]
+    assert re.search(r"bs took:[0-9.e+-]+$", r.stdout)
+    nfound = sum(1 for c in g["counts"] if c > 0)
+    assert "count_found = %d\n" % nfound in r.stderr and "count_not_found = %d\n" % (len(g["counts"]) - nfound) in r.stderr
+    assert "The csv file is ready!" in r.stderr and r.stderr.endswith("The End!\n")
+    header, rows = E.read_csv_rows(pf + "output.csv")
+    assert header == "#Pat\t$_i\tD[i]\tS_j\tS_j[r]\n"
+    assert sorted(rows) == sorted(g["rows_reference_order"])
+    os.remove(pf + "output.csv")
+    r0 = _run_cli(exe, base, pf, {"EDSBWT_RECOVERBW": "0"})
+    assert r0.returncode == 1 and not os.path.exists(pf + "output.csv")
+    assert [int(x) for x in re.findall(r"interrupted in position (\d+)", r0.stderr)] == [v for v in g["interrupted"] if v]
+    assert "The search is finished!" in r0.stderr
+    # usage error: exit(1) with the usage text on stderr (mainEDS-BWT.cpp:42-48)
+    import subprocess
+    u = subprocess.run([exe, base], capture_output=True, text=True)
+    assert u.returncode == 1 and u.stderr.startswith("usage: ")
