@@ -24,19 +24,20 @@ EXPORTS = [
     "edsbwt_result_free", "edsbwt_last_stats", "edsbwt_set_stats", "edsbwt_write_csv", "edsbwt_read_patterns",
     "edsbwt_build_from_eds", "edsbwt_build_from_collection", "edsbwt_gather_bench", "edsbwt_free",
     "edsbwt_strerror", "edsbwt_last_error", "edsbwt_version", "edsbwt_search_into", "edsbwt_host_alloc", "edsbwt_host_free",
-    "edsbwt_set_chunk", "edsbwt_search_trace",
+    "edsbwt_set_chunk", "edsbwt_search_trace", "edsbwt_move_table_build", "edsbwt_move_table_fetch",
 ]
 
 
 class Info(C.Structure):
     _fields_ = [("n", C.c_uint32), ("n_text", C.c_uint32), ("n_seg", C.c_uint32), ("sigma", C.c_uint32),
                 ("alphabet", C.c_uint8 * 8), ("table_occ", C.c_uint32 * 25), ("seed_k", C.c_uint32),
-                ("locate_mode", C.c_uint32), ("device_bytes", C.c_uint64), ("seed_intervals", C.c_uint64)]
+                ("locate_mode", C.c_uint32), ("device_bytes", C.c_uint64), ("seed_intervals", C.c_uint64),
+                ("move_runs", C.c_uint32), ("move_intervals", C.c_uint32), ("move_a", C.c_uint32), ("move_rounds", C.c_uint32)]
 
 
 class OpenOpts(C.Structure):
     _fields_ = [("seed_k", C.c_int32), ("locate_mode", C.c_int32), ("verify", C.c_int32), ("build_move", C.c_int32),
-                ("engine", C.c_int32), ("fused_cap", C.c_int32), ("fused_cap2", C.c_int32), ("reserved", C.c_int32 * 1)]
+                ("engine", C.c_int32), ("fused_cap", C.c_int32), ("fused_cap2", C.c_int32), ("move_a", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -83,6 +84,8 @@ def lib():
         L.edsbwt_search_into.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
                                          C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.edsbwt_search_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
+        L.edsbwt_move_table_build.argtypes = [C.c_void_p]
+        L.edsbwt_move_table_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
         L.edsbwt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_uint64]
         L.edsbwt_host_free.argtypes = [C.c_void_p]
         L.edsbwt_host_free.restype = None
@@ -123,10 +126,10 @@ class Index:
     """Device-resident EDS-BWT index (edsbwt_index_open_ex)."""
 
     def __init__(self, base, device=0, seed_k=-1, locate_mode=LOCATE_SA, verify=True, build_move=False,
-                 engine=ENGINE_FUSED, fused_cap=0, fused_cap2=0):
+                 engine=ENGINE_FUSED, fused_cap=0, fused_cap2=0, move_a=0):
         self._h = C.c_void_p()
         o = OpenOpts(seed_k=seed_k, locate_mode=locate_mode, verify=int(verify), build_move=int(build_move),
-                     engine=engine, fused_cap=fused_cap, fused_cap2=fused_cap2)
+                     engine=engine, fused_cap=fused_cap, fused_cap2=fused_cap2, move_a=move_a)
         _check(lib().edsbwt_index_open_ex(os.fsencode(base), device, C.byref(o), C.byref(self._h)))
         self.device = device
 
@@ -178,6 +181,14 @@ class Index:
             occ = np.frombuffer(buf, dtype=OCC_DTYPE).copy()
             lib().edsbwt_free(occ_p)
         return counts[:npat], occ
+
+    def move_table(self):
+        """-> (p, q, dest, sym) columns of the move table (builds it when needed)."""
+        r = C.c_uint32()
+        _check(lib().edsbwt_move_table_fetch(self._h, None, None, None, None, 0, C.byref(r)))
+        p = np.zeros(r.value, np.uint32); q = np.zeros(r.value, np.uint32); d = np.zeros(r.value, np.uint32); sy = np.zeros(r.value, np.uint8)
+        _check(lib().edsbwt_move_table_fetch(self._h, p.ctypes.data, q.ctypes.data, d.ctypes.data, sy.ctypes.data, r.value, C.byref(r)))
+        return p, q, d, sy
 
     def search_trace(self, patterns, lf_variant=LF_RANK):
         """count-only search + the reference's "interrupted in position" value per pattern (0 = no such line)."""

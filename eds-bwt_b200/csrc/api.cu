@@ -56,6 +56,7 @@ int edsbwt_index_info(const edsbwt_index* idx, edsbwt_info* info) {
     for (uint32_t i = 0; i < h.sigma * h.sigma && i < 25; ++i) info->table_occ[i] = h.table_occ[i];
     info->seed_k = idx->ix.seed_k; info->locate_mode = (uint32_t)idx->ix.locate_mode;
     info->device_bytes = idx->ix.device_bytes(); info->seed_intervals = idx->ix.seed_intervals;
+    if (const MoveTable* mt = idx->ix.move) { info->move_runs = mt->r_runs; info->move_intervals = mt->r; info->move_a = mt->a; info->move_rounds = mt->rounds; }
     return EDSBWT_OK;
 }
 
@@ -225,6 +226,31 @@ int edsbwt_search_trace(edsbwt_index* idx, const uint8_t* pat_bytes, const uint6
             uint32_t pos = 0;
             if (m >= 2 && counts[i] == 0 && alive < m) { pos = m - alive; if (pos > m - 1) pos = m - 1; }
             interrupted[i] = pos;
+        }
+    });
+}
+
+int edsbwt_move_table_build(edsbwt_index* idx) {
+    if (!idx) return EDSBWT_E_ARG;
+    return guarded([&] { std::lock_guard<std::mutex> lock(idx->ix.mu); build_move_table(idx->ix); });
+}
+int edsbwt_move_table_fetch(edsbwt_index* idx, uint32_t* p, uint32_t* q, uint32_t* dest, uint8_t* sym, uint32_t cap, uint32_t* r) {
+    if (!idx || !r) return EDSBWT_E_ARG;
+    int rc = edsbwt_move_table_build(idx);
+    if (rc) return rc;
+    return guarded([&] {
+        const MoveTable& mt = *idx->ix.move;
+        *r = mt.r;
+        if (!p && !q && !dest && !sym) return;
+        if (cap < mt.r) EDS_FAIL(EDSBWT_E_NOSPACE, "move table has %u intervals, caller arrays hold %u", mt.r, cap);
+        CUDA_OK(cudaSetDevice(idx->ix.device));
+        std::vector<uint4> h(mt.r);
+        CUDA_OK(cudaMemcpy(h.data(), mt.T.p, (size_t)mt.r * sizeof(uint4), cudaMemcpyDeviceToHost));
+        for (uint32_t i = 0; i < mt.r; ++i) {
+            if (p) p[i] = h[i].x;
+            if (q) q[i] = h[i].y;
+            if (dest) dest[i] = h[i].z;
+            if (sym) sym[i] = idx->ix.host.alphabet[h[i].w];
         }
     });
 }

@@ -43,7 +43,6 @@ static inline unsigned grid_for(size_t n, unsigned block) { return (unsigned)((n
 // K1: Occ structure from the raw eBWT bytes  (replaces computeVectorOcc, EDSBWTsearch.cpp:1338-1442,
 //     and the rrr rank supports of recoverInfo, :1586-1604)
 // ===================================================================================================
-struct Lut { uint8_t code[256]; };     // 0..3 letter code, 4 = end-marker, 255 = not in the alphabet
 
 __global__ void occ_pack_kernel(const uint8_t* __restrict__ bytes, uint32_t n, Lut lut, uint4* __restrict__ occ,
                                 uint4* __restrict__ blkcnt, uint32_t ngroups, unsigned int* bad) {
@@ -77,6 +76,31 @@ __global__ void occ_counts_kernel(uint4* __restrict__ occ, const uint4* __restri
     uint4 p = prefix[g >> 2];
     uint32_t j = g & 3;
     occ[g].x = j == 0 ? p.x : j == 1 ? p.y : j == 2 ? p.z : p.w;
+}
+
+// bytes (alphabet characters) -> interleaved Occ blocks; tot[c] = occurrences of letter c, *bad = 1 + first row whose byte
+// is outside the alphabet (0: none).  Used for the eBWT and for the run-head string L' of the move table.
+void build_occ_blocks(const uint8_t* d_bytes, uint32_t n, const Lut& lut, DevBuf<uint4>& occ, DevBuf<uint8_t>& cubtmp, cudaStream_t s,
+                      uint32_t tot[4], unsigned int* bad_out) {
+    uint32_t nblk = n / OCC_ROWS + 1, ngroups = nblk * 4;
+    occ.ensure(ngroups);
+    DevBuf<uint4> blkcnt, prefix; blkcnt.ensure(nblk); prefix.ensure(nblk);
+    DevBuf<unsigned int> bad; bad.ensure(1);
+    CUDA_OK(cudaMemsetAsync(bad.p, 0, 4, s));
+    occ_pack_kernel<<<grid_for(ngroups, 256), 256, 0, s>>>(d_bytes, n, lut, occ.p, blkcnt.p, ngroups, bad.p);
+    size_t tmp = 0;
+    CUDA_OK(cub::DeviceScan::ExclusiveScan(nullptr, tmp, blkcnt.p, prefix.p, AddU4(), make_uint4(0, 0, 0, 0), (int)nblk, s));
+    cubtmp.ensure(tmp);
+    CUDA_OK(cub::DeviceScan::ExclusiveScan(cubtmp.p, tmp, blkcnt.p, prefix.p, AddU4(), make_uint4(0, 0, 0, 0), (int)nblk, s));
+    occ_counts_kernel<<<grid_for(ngroups, 256), 256, 0, s>>>(occ.p, prefix.p, ngroups);
+    unsigned int hbad = 0;
+    uint4 last_prefix, last_cnt;
+    CUDA_OK(cudaMemcpyAsync(&hbad, bad.p, 4, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(&last_prefix, prefix.p + (nblk - 1), 16, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaMemcpyAsync(&last_cnt, blkcnt.p + (nblk - 1), 16, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    tot[0] = last_prefix.x + last_cnt.x; tot[1] = last_prefix.y + last_cnt.y; tot[2] = last_prefix.z + last_cnt.z; tot[3] = last_prefix.w + last_cnt.w;
+    if (bad_out) *bad_out = hbad;
 }
 
 // ===================================================================================================
@@ -436,11 +460,13 @@ Index::~Index() {
     for (SeedLevel* s : seed) delete s;
     delete ws;
     delete pipe;
+    delete move;
     if (stream) cudaStreamDestroy(stream);
 }
 uint64_t Index::device_bytes() const {
     uint64_t b = occ.bytes() + eof_flat.bytes() + str_seg.bytes() + seg_first.bytes() + seg_low.bytes() + sa.bytes() + link_rec.bytes() + str_info.bytes();
     for (SeedLevel* s : seed) if (s) b += s->off.bytes() + s->iv.bytes();
+    if (move) b += move->bytes();
     return b;
 }
 
@@ -456,7 +482,7 @@ static uint32_t read_u32(Workspace& ws, const uint32_t* d, cudaStream_t s) {
     CUDA_OK(cudaStreamSynchronize(s));
     return ws.h_pin[0];
 }
-static Lut make_lut(const HostIndex& h) {
+Lut make_lut(const HostIndex& h) {
     Lut l; memset(l.code, 255, sizeof l.code);
     l.code[h.alphabet[0]] = 4;
     for (uint32_t a = 1; a < h.sigma; ++a) l.code[h.alphabet[a]] = (uint8_t)(a - 1);
@@ -622,30 +648,13 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     for (uint32_t c = 0; c < 5; ++c) v.Cl[c] = c < h.sigma - 1 ? h.pile_start[c + 1] : h.n;
 
     // ---- K1: Occ blocks
-    uint32_t nblk = h.n / OCC_ROWS + 1, ngroups = nblk * 4;
-    ix.occ.ensure(ngroups);
     {
         DevBuf<uint8_t> d_bytes; d_bytes.ensure((size_t)h.n + 64);
-        DevBuf<uint4> blkcnt, prefix; blkcnt.ensure(nblk); prefix.ensure(nblk);
-        DevBuf<unsigned int> bad; bad.ensure(1);
         CUDA_OK(cudaMemcpyAsync(d_bytes.p, h.ebwt.data(), h.n, cudaMemcpyHostToDevice, s));
-        CUDA_OK(cudaMemsetAsync(bad.p, 0, 4, s));
-        Lut lut = make_lut(h);
-        occ_pack_kernel<<<grid_for(ngroups, 256), 256, 0, s>>>(d_bytes.p, h.n, lut, ix.occ.p, blkcnt.p, ngroups, bad.p);
-        size_t tmp = 0;
-        CUDA_OK(cub::DeviceScan::ExclusiveScan(nullptr, tmp, blkcnt.p, prefix.p, AddU4(), make_uint4(0, 0, 0, 0), (int)nblk, s));
-        ws.cubtmp.ensure(tmp);
-        CUDA_OK(cub::DeviceScan::ExclusiveScan(ws.cubtmp.p, tmp, blkcnt.p, prefix.p, AddU4(), make_uint4(0, 0, 0, 0), (int)nblk, s));
-        occ_counts_kernel<<<grid_for(ngroups, 256), 256, 0, s>>>(ix.occ.p, prefix.p, ngroups);
-        unsigned int hbad = 0;
-        CUDA_OK(cudaMemcpyAsync(&hbad, bad.p, 4, cudaMemcpyDeviceToHost, s));
-        // totals of the last block must reproduce the pile sizes implied by tableOcc
-        uint4 last_prefix, last_cnt;
-        CUDA_OK(cudaMemcpyAsync(&last_prefix, prefix.p + (nblk - 1), 16, cudaMemcpyDeviceToHost, s));
-        CUDA_OK(cudaMemcpyAsync(&last_cnt, blkcnt.p + (nblk - 1), 16, cudaMemcpyDeviceToHost, s));
-        CUDA_OK(cudaStreamSynchronize(s));
+        uint32_t tot[4]; unsigned int hbad = 0;
+        build_occ_blocks(d_bytes.p, h.n, make_lut(h), ix.occ, ws.cubtmp, s, tot, &hbad);
         if (hbad) EDS_FAIL(EDSBWT_E_FORMAT, "eBWT row %u holds a byte outside the alphabet of info.aux", hbad - 1);
-        uint32_t tot[4] = {last_prefix.x + last_cnt.x, last_prefix.y + last_cnt.y, last_prefix.z + last_cnt.z, last_prefix.w + last_cnt.w};
+        // totals must reproduce the pile sizes implied by tableOcc
         for (uint32_t c = 0; c + 1 < h.sigma; ++c) {
             uint32_t expect = 0;
             for (uint32_t p = 0; p < h.sigma; ++p) expect += h.table_occ[p * h.sigma + c + 1];
@@ -700,6 +709,8 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     ix.seed_k = (uint32_t)k;
     build_seed_table(ix, ix.seed_k);
     CUDA_OK(cudaGetLastError());
+    ix.move_a = o.move_a > 0 ? (uint32_t)o.move_a : 8u;
+    if (o.build_move) build_move_table(ix);
     h.ebwt.clear(); h.ebwt.shrink_to_fit();
     h.seg_first_bit.clear(); h.seg_first_bit.shrink_to_fit();
     h.eof_flat.clear(); h.eof_flat.shrink_to_fit();
@@ -770,10 +781,13 @@ static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64
 
 void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat, uint64_t total_bytes, uint32_t max_len,
                 bool locate, int lf_variant, SearchOut& out, uint32_t pat_base) {
-    if (lf_variant != EDSBWT_LF_RANK) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "move-table LF variant not built into this handle");
+    if (lf_variant != EDSBWT_LF_RANK && lf_variant != EDSBWT_LF_MOVE) EDS_FAIL(EDSBWT_E_ARG, "unknown LF variant %d", lf_variant);
+    const bool move = lf_variant == EDSBWT_LF_MOVE;
+    if (move && out.want_alive) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "edsbwt_search_trace is an EDSBWTsearch (RECOVERBW=0) feature; MOVE_EDSBWTSearch always locates");
     (void)total_bytes;
     CUDA_OK(cudaSetDevice(ix.device));
     std::lock_guard<std::mutex> lock(ix.mu);
+    if (move) build_move_table(ix);            // no-op once built
     Workspace& ws = *ix.ws;
     cudaStream_t s = ix.stream;
     ws.launches = 0; ws.lf_ms = 0;
@@ -795,7 +809,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
         CUDA_OK(cudaMemsetAsync(ws.fcursor.p, 0, 16, s));
         uint32_t nstage = 0;
         const uint32_t* ids = nullptr;
-        if (ix.engine == EDSBWT_ENGINE_FUSED) {
+        if (ix.engine == EDSBWT_ENGINE_FUSED || move) {
             // ---- the hot kernel: one thread per pattern
             size_t want = (size_t)npat * 2 + (1u << 16);
             if (want > 0xfffffff0ull) want = 0xfffffff0ull;
@@ -804,7 +818,12 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; }
             FusedOut fo{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 1, ws.ovf_ids.p, d_alive};
             CUDA_OK(cudaEventRecord(ws.evf0, s));
-            launch_fused_search(ix.view, sv, k_eff, d_bytes, d_off, nullptr, npat, ix.lut.p, ix.fused_cap, fo, st, ix.canonical_k, s);
+            // MOVE: 16-byte frontier entries (b, e, b', e'), so half the slots fit the same shared memory
+            const uint32_t cap1 = move ? std::min<uint32_t>(ix.fused_cap, FUSED_BIG_CAP / 2) : ix.fused_cap;
+            const uint32_t cap2 = move ? std::min<uint32_t>(ix.fused_cap2, FUSED_BIG_CAP / 2) : ix.fused_cap2;
+            if (move) { MoveOut mo{fo.plist, fo.counts, fo.staging, fo.staging_cap, fo.cursor, fo.ovf_count, fo.ovf_ids};
+                        launch_move_search(ix.view, ix.move->view, sv, k_eff, d_bytes, d_off, nullptr, npat, ix.lut.p, cap1, mo, s); }
+            else launch_fused_search(ix.view, sv, k_eff, d_bytes, d_off, nullptr, npat, ix.lut.p, cap1, fo, st, ix.canonical_k, s);
             CUDA_OK(cudaEventRecord(ws.evf1, s));
             ws.launches += 1; fused_ran = true;
             CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 8, cudaMemcpyDeviceToHost, s));
@@ -812,15 +831,17 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             nstage = ws.h_pin[0]; novf = ws.h_pin[1];
             novf1 = novf;
             ids = ws.ovf_ids.p;
-            if (novf && ix.fused_cap < ix.fused_cap2) {
+            if (novf && cap1 < cap2) {
                 // ---- second pass: the same kernel with the largest frontier that fits one CTA per SM, only over the
                 //      patterns that did not fit; what still does not fit goes to the level-synchronous engine
                 ws.ovf_ids2.ensure(novf);
-                size_t want2 = (size_t)nstage + (size_t)novf * ix.fused_cap2;
+                size_t want2 = (size_t)nstage + (size_t)novf * cap2;
                 if (want2 > 0xfffffff0ull) want2 = 0xfffffff0ull;
                 ws.staging.ensure(want2, s, true, nstage);
                 FusedOut fo2{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 2, ws.ovf_ids2.p, d_alive};
-                launch_fused_search(ix.view, sv, k_eff, d_bytes, d_off, ws.ovf_ids.p, novf, ix.lut.p, ix.fused_cap2, fo2, st, ix.canonical_k, s);
+                if (move) { MoveOut mo{fo2.plist, fo2.counts, fo2.staging, fo2.staging_cap, fo2.cursor, fo2.ovf_count, fo2.ovf_ids};
+                            launch_move_search(ix.view, ix.move->view, sv, k_eff, d_bytes, d_off, ws.ovf_ids.p, novf, ix.lut.p, cap2, mo, s); }
+                else launch_fused_search(ix.view, sv, k_eff, d_bytes, d_off, ws.ovf_ids.p, novf, ix.lut.p, cap2, fo2, st, ix.canonical_k, s);
                 ws.launches += 1;
                 CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 12, cudaMemcpyDeviceToHost, s));
                 CUDA_OK(cudaStreamSynchronize(s));
@@ -863,7 +884,8 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             if (nocc) {
                 out.occ.ensure(nocc);
                 CUDA_OK(cudaEventRecord(ws.evl0, s));
-                if (ix.locate_mode == EDSBWT_LOCATE_WALK)
+                if (move) launch_move_locate(ix.view, ix.move->view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, pat_base, out.occ.p, st, s);
+                else if (ix.locate_mode == EDSBWT_LOCATE_WALK)
                     locate_kernel<true><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, pat_base, out.occ.p, st);
                 else
                     locate_kernel<false><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, pat_base, out.occ.p, st);
@@ -882,7 +904,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     ls = edsbwt_stats{};
     ls.I = hs.I; ls.S = hs.S; ls.E = hs.E; ls.L = hs.L; ls.O = hs.O; ls.lf_intervals = hs.lf_intervals; ls.occ_blocks = hs.occ_blocks;
     ls.steps = steps; ls.kernel_launches = ws.launches; ls.lf_kernel_ms = ws.lf_ms; ls.total_ms = ms; ls.frontier_peak = peak;
-    ls.overflow_patterns = ix.engine == EDSBWT_ENGINE_FUSED ? novf1 : 0; ls.levelsync_patterns = novf;
+    ls.overflow_patterns = (ix.engine == EDSBWT_ENGINE_FUSED || move) ? novf1 : 0; ls.levelsync_patterns = novf;
     if (fused_ran) { float fm = 0; CUDA_OK(cudaEventElapsedTime(&fm, ws.evf0, ws.evf1)); ls.search_kernel_ms = fm; }
     if (locate_ran) { float lm = 0; CUDA_OK(cudaEventElapsedTime(&lm, ws.evl0, ws.evl1)); ls.locate_kernel_ms = lm; }
 }

@@ -218,12 +218,11 @@ void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, co
                          const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s) {
     if (npat == 0) return;
     const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
-    static bool attr_set[2] = {false, false};
     if (st) {
-        if (!attr_set[1]) { CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr_set[1] = true; }
+        CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
         fused_search_kernel<true><<<(npat + FUSED_THREADS - 1) / FUSED_THREADS, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
     } else {
-        if (!attr_set[0]) { CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); attr_set[0] = true; }
+        CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         fused_search_kernel<false><<<(npat + FUSED_THREADS - 1) / FUSED_THREADS, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
     }
     CUDA_OK(cudaGetLastError());

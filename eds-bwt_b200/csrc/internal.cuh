@@ -176,6 +176,29 @@ struct Pipe {
               if (in) cudaStreamDestroy(in); if (outs) cudaStreamDestroy(outs); }
 };
 
+// ---------------------------------------------------------------------------------------------------
+// move table (MOVE_EDSBWTSearch variant; csrc/move.cu).  Input intervals = runs of the eBWT where every end-marker is a
+// run of its own (da_to_everything.cpp:440-442), split further until a-balanced.  One 16-byte entry per interval:
+//   .x p   first row of the interval          .y q   LF(p)
+//   .z idx input interval containing q        .w c   symbol of the run: 0 = '#', 1 + letter code otherwise
+// T[r] = {n, n, r, 0xff} is a sentinel.  L' (the run symbols) additionally lives in an Occ-block structure over RUN
+// indices (rank of a letter / of '#' among the run heads) with a select array per letter.
+// ---------------------------------------------------------------------------------------------------
+struct MoveView {
+    const uint4* T; uint32_t r;
+    const uint4* occL;             // Occ blocks over L'
+    const uint32_t* sel;           // sel[selbase[c] + k] = k-th run (0-based) whose symbol is letter c
+    uint32_t selbase[5];           // [4] = number of letter runs
+    const uint32_t* coarse;        // coarse[b] = number of intervals starting before row 128*b  (b = 0 .. n/128 + 1)
+    const uint32_t* row_run0;      // interval containing pile-0 row i (M_LF_Dollar_Input_interval, MOVE_EDSBWTSearch.cpp:200-205)
+};
+struct MoveTable {
+    DevBuf<uint4> T, occL; DevBuf<uint32_t> sel, coarse, row_run0;
+    uint32_t r = 0, r_runs = 0, a = 8, rounds = 0;
+    MoveView view{};
+    uint64_t bytes() const { return T.bytes() + occL.bytes() + sel.bytes() + coarse.bytes() + row_run0.bytes(); }
+};
+
 // device buffers of finished searches are recycled: edsbwt_result_free hands them back instead of cudaFree (which
 // synchronises the device and costs more than the locate kernel at cfg4 sizes)
 struct ResultPool {
@@ -201,6 +224,8 @@ struct Index {
     uint64_t seed_intervals = 0;
     Workspace* ws = nullptr;
     Pipe* pipe = nullptr;
+    MoveTable* move = nullptr;          // built at open (opts.build_move) or by the first EDSBWT_LF_MOVE search
+    uint32_t move_a = 8;
     std::shared_ptr<ResultPool> pool = std::make_shared<ResultPool>();
     uint32_t chunk_patterns = 1u << 21;     // patterns per pipeline chunk of the host-buffer searches
     edsbwt_stats last{};
@@ -211,6 +236,10 @@ struct Index {
 };
 
 // engine.cu
+struct Lut { uint8_t code[256]; };     // 0..3 letter code, 4 = end-marker, 255 = not in the alphabet
+Lut make_lut(const HostIndex& h);
+void build_occ_blocks(const uint8_t* d_bytes, uint32_t n, const Lut& lut, DevBuf<uint4>& occ, DevBuf<uint8_t>& cubtmp, cudaStream_t s,
+                      uint32_t tot[4], unsigned int* bad_out);
 void build_device_index(Index& ix, const edsbwt_open_opts& o);
 void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat, uint64_t total_bytes,
                 uint32_t max_len, bool locate, int lf_variant, SearchOut& out, uint32_t pat_base = 0);
@@ -229,6 +258,15 @@ struct FusedOut {
 void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
                          const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s);
 
+// move.cu
+void build_move_table(Index& ix);
+struct MoveOut {            // what the move search leaves for the common result path of run_search
+    uint2* plist; uint32_t* counts; uint2* staging; uint32_t staging_cap; uint32_t* cursor; uint32_t* ovf_count; uint32_t* ovf_ids;
+};
+void launch_move_search(const IndexView& ix, const MoveView& mv, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
+                        const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const MoveOut& out, cudaStream_t s);
+void launch_move_locate(const IndexView& ix, const MoveView& mv, const uint2* plist, const uint32_t* occ_ofs, const uint2* staging,
+                        uint32_t npat, uint64_t nocc, uint32_t pat_base, edsbwt_occ* out, StatsDev* st, cudaStream_t s);
 // builder.cu
 void build_index_files(const uint8_t* letters, const uint64_t* str_off, uint32_t nstr, const uint8_t* seg_first,
                        const std::string& out_base, int device);

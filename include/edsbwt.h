@@ -49,6 +49,10 @@ typedef struct {
     uint32_t locate_mode;       /* EDSBWT_LOCATE_*                                             */
     uint64_t device_bytes;      /* HBM held by the handle                                      */
     uint64_t seed_intervals;    /* total intervals stored in the seed table                    */
+    uint32_t move_runs;         /* move table: runs of the eBWT (every end-marker its own run); 0 = table not built */
+    uint32_t move_intervals;    /* move table: input intervals after a-balancing (Move-r's r')   */
+    uint32_t move_a;            /* balancing parameter                                          */
+    uint32_t move_rounds;       /* balancing rounds the builder needed                          */
 } edsbwt_info;
 
 #define EDSBWT_LOCATE_SA    0   /* row -> (string, offset) table in HBM: one gather per occurrence           */
@@ -66,7 +70,7 @@ typedef struct {
     int32_t  engine;            /* EDSBWT_ENGINE_FUSED (default) / _LEVELSYNC                                 */
     int32_t  fused_cap;         /* frontier slots per pattern of the fused kernel (0 = default 24)            */
     int32_t  fused_cap2;        /* slots of the second pass over the patterns that outgrew the first (0 = 192) */
-    int32_t  reserved[1];
+    int32_t  move_a;            /* balancing parameter a of the move table (build_MLF's <a>); 0 = default 8             */
 } edsbwt_open_opts;
 
 /* Canonical byte-model counters of DESIGN.md + engine statistics of the last search. */
@@ -133,6 +137,13 @@ void edsbwt_result_free(edsbwt_result* res);
 
 int  edsbwt_last_stats(const edsbwt_index* idx, edsbwt_stats* st);
 int  edsbwt_set_stats(edsbwt_index* idx, int collect_counters, uint32_t canonical_k);
+
+/* --- move table (replaces build_MLF.cpp:53-164 + MOVE_EDSBWT::retrieve_MLF, MOVE_EDSBWTSearch.cpp:178-218): built on the
+ *     GPU from the pile files, at open (opts.build_move) or by the first EDSBWT_LF_MOVE search.  edsbwt_move_table_fetch
+ *     copies the columns to host arrays of `cap` entries (test / inspection hook): p = first row of input interval i,
+ *     q = LF(p), dest = input interval containing q, sym = alphabet byte of the run.  *r = number of intervals. */
+int  edsbwt_move_table_build(edsbwt_index* idx);
+int  edsbwt_move_table_fetch(edsbwt_index* idx, uint32_t* p, uint32_t* q, uint32_t* dest, uint8_t* sym, uint32_t cap, uint32_t* r);
 
 /* --- output: replaces the csv writing of EDSBWT's constructor (:179-193) and of
  *     indices_of_dollars_in_interval (:1327).  Creates/truncates path, writes the header
