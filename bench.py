@@ -168,7 +168,20 @@ def cpu_reference_run(base, pats, seconds, cores, note):
 
 
 # ----------------------------------------------------------------------------------------------------
+_REAL_STDOUT = None
+
+
+def emit(obj):
+    """The ONE JSON line of the contract, on the process's real stdout."""
+    line = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, line)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -180,6 +193,10 @@ def main():
         sys.exit(subprocess.call(cmd))
     if args.impl == "reference" and rank != 0:
         return 0
+    # libraries (NCCL's version banner, torchrun notices) write to fd 1: keep stdout for the JSON line only
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
 
     import torch
     import torch.distributed as dist
@@ -284,6 +301,26 @@ def main():
     h2d = data.nbytes + off.nbytes
     gpu_counts = np.array(p_counts, copy=True)
     gpu_occ_total = int(got)
+    # ---- multi-GPU result gather (north star: "only an NCCL/NVLink gather of per-pattern counts and occurrence buffers"):
+    #      shard search + all-gather of the counts + gather-v of the tuples to rank 0, timed on the device
+    gather_ms, gather_bytes = 0.0, 0
+    if world > 1:
+        sh = importlib.import_module("eds-bwt_b200.sharded")
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for it in range(2 + args.steps):
+            barrier()
+            ev0.record()
+            r = idx.search_device(d_data.data_ptr(), d_off.data_ptr(), args.npat, total_bytes, args.plen, locate=True, pat_base=rank * args.npat)
+            c_loc, o_loc = sh.device_result_tensors(r, local_rank)
+            allc, allo, tots = sh.gather_results(c_loc, o_loc, args.npat * world, None, 0)
+            ev1.record()
+            torch.cuda.synchronize()
+            r.free()
+            if it >= 2:
+                gather_ms += ev0.elapsed_time(ev1)
+                gather_bytes = 4 * args.npat * world + 20 * sum(tots)
+            del allc, allo
+
     def allmax(x):
         if world == 1:
             return x
@@ -294,6 +331,7 @@ def main():
     dev_ms_max = allmax(dev_ms)
     wall_ms_max = allmax(wall_ms)
     e2e_ms_max = allmax(e2e_ms)
+    gather_ms_max = allmax(gather_ms) if world > 1 else 0.0
     total_pat = args.npat * world * args.steps
     value = total_pat / (dev_ms_max * 1e-3)
     e2e_val = total_pat / (e2e_ms_max * 1e-3)
@@ -333,6 +371,9 @@ def main():
             "occurrences_per_step": int(nocc),
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": e2e_ms_max / args.steps},
+            "gather": ({"value": total_pat / (gather_ms_max * 1e-3), "unit": UNIT, "ms_per_step": gather_ms_max / args.steps,
+                        "bytes_per_step": int(gather_bytes), "what": "shard search + ncclAllGather(counts) + gather-v(tuples) to rank 0, device-timed"}
+                       if world > 1 else None),
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "fused_search_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -361,7 +402,7 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(out), flush=True)
+        emit(out)
         if not args.keep and not os.environ.get("EDSBWT_BENCH_KEEP"):
             pass        # index files stay in the work dir for the reference arm that the driver runs next
     return 0
@@ -373,7 +414,7 @@ def reference_arm(args, eb, synth, workdir, base, done_flag):
     if not os.path.exists(done_flag):
         import torch
         if not torch.cuda.is_available():
-            print(json.dumps({"impl": "reference", "unavailable": "index files for cfg4 are built by the GPU suffix sorter; no CUDA device here"}))
+            emit({"impl": "reference", "unavailable": "index files for cfg4 are built by the GPU suffix sorter; no CUDA device here"})
             return 0
         build_index_files(eb, synth, args, base)
         open(done_flag, "w").close()
@@ -393,7 +434,7 @@ def reference_arm(args, eb, synth, workdir, base, done_flag):
            "data": "synthetic", "config": {"workload": workload_name(args)},
            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": base_info["kind"], "sample": base_info["sample"]},
            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(out), flush=True)
+    emit(out)
     return 0
 
 

@@ -24,7 +24,7 @@ EXPORTS = [
     "edsbwt_result_free", "edsbwt_last_stats", "edsbwt_set_stats", "edsbwt_write_csv", "edsbwt_read_patterns",
     "edsbwt_build_from_eds", "edsbwt_build_from_collection", "edsbwt_gather_bench", "edsbwt_free",
     "edsbwt_strerror", "edsbwt_last_error", "edsbwt_version", "edsbwt_search_into", "edsbwt_host_alloc", "edsbwt_host_free",
-    "edsbwt_set_chunk", "edsbwt_search_trace", "edsbwt_move_table_build", "edsbwt_move_table_fetch",
+    "edsbwt_set_chunk", "edsbwt_search_trace", "edsbwt_move_table_build", "edsbwt_move_table_fetch", "edsbwt_search_device_at", "edsbwt_gather_bench_ex",
 ]
 
 
@@ -92,6 +92,8 @@ def lib():
         L.edsbwt_set_chunk.argtypes = [C.c_void_p, C.c_uint32]
         L.edsbwt_search_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32,
                                            C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.edsbwt_search_device_at.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32,
+                                              C.c_int, C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]
         L.edsbwt_result_sizes.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
         L.edsbwt_result_device_ptrs.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
         L.edsbwt_result_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
@@ -102,6 +104,7 @@ def lib():
         L.edsbwt_build_from_eds.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         L.edsbwt_build_from_collection.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_char_p, C.c_int]
         L.edsbwt_gather_bench.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_double)]
+        L.edsbwt_gather_bench_ex.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_double)]
         _lib = L
     return _lib
 
@@ -212,11 +215,12 @@ class Index:
     def set_chunk(self, patterns_per_chunk):
         _check(lib().edsbwt_set_chunk(self._h, patterns_per_chunk))
 
-    def search_device(self, d_bytes_ptr, d_off_ptr, npat, total_bytes, max_len, locate=True, lf_variant=LF_RANK):
-        """Device-pointer variant; returns a DeviceResult (results stay in HBM)."""
+    def search_device(self, d_bytes_ptr, d_off_ptr, npat, total_bytes, max_len, locate=True, lf_variant=LF_RANK, pat_base=0):
+        """Device-pointer variant; returns a DeviceResult (results stay in HBM).  pat_base: index of the first pattern
+        of this shard inside the whole batch (added to the pat field of the tuples)."""
         r = C.c_void_p()
-        _check(lib().edsbwt_search_device(self._h, C.c_void_p(d_bytes_ptr), C.c_void_p(d_off_ptr), npat, total_bytes,
-                                          max_len, int(locate), lf_variant, C.byref(r)))
+        _check(lib().edsbwt_search_device_at(self._h, C.c_void_p(d_bytes_ptr), C.c_void_p(d_off_ptr), npat, total_bytes,
+                                             max_len, int(locate), lf_variant, pat_base, C.byref(r)))
         return DeviceResult(r)
 
 
@@ -306,7 +310,7 @@ def build_from_collection(text, str_off, seg_first, out_base, device=0):
                                               seg_first.ctypes.data, os.fsencode(out_base), device))
 
 
-def gather_bench(device=0, buffer_bytes=4 << 30, n_access=1 << 26, iters=5):
+def gather_bench(device=0, buffer_bytes=4 << 30, n_access=1 << 26, iters=5, granule=64):
     g = C.c_double()
-    _check(lib().edsbwt_gather_bench(device, buffer_bytes, n_access, iters, C.byref(g)))
+    _check(lib().edsbwt_gather_bench_ex(device, buffer_bytes, n_access, iters, granule, C.byref(g)))
     return g.value

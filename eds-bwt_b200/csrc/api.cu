@@ -73,11 +73,15 @@ int edsbwt_last_stats(const edsbwt_index* idx, edsbwt_stats* st) {
 
 int edsbwt_search_device(edsbwt_index* idx, const uint8_t* d_pat_bytes, const uint64_t* d_pat_off, uint32_t npat,
                          uint64_t total_bytes, uint32_t max_len, int locate, int lf_variant, edsbwt_result** res) {
+    return edsbwt_search_device_at(idx, d_pat_bytes, d_pat_off, npat, total_bytes, max_len, locate, lf_variant, 0, res);
+}
+int edsbwt_search_device_at(edsbwt_index* idx, const uint8_t* d_pat_bytes, const uint64_t* d_pat_off, uint32_t npat,
+                            uint64_t total_bytes, uint32_t max_len, int locate, int lf_variant, uint32_t pat_base, edsbwt_result** res) {
     if (!idx || !res || (npat && (!d_pat_off))) return EDSBWT_E_ARG;
     *res = nullptr;
     edsbwt_result* r = new edsbwt_result; r->device = idx->ix.device; r->pool = idx->ix.pool; r->outp = r->pool->get();
     r->outp->want_alive = false;
-    int rc = guarded([&] { run_search(idx->ix, d_pat_bytes, d_pat_off, npat, total_bytes, max_len, locate != 0, lf_variant, *r->outp); });
+    int rc = guarded([&] { run_search(idx->ix, d_pat_bytes, d_pat_off, npat, total_bytes, max_len, locate != 0, lf_variant, *r->outp, pat_base); });
     if (rc) { cudaSetDevice(idx->ix.device); r->pool->put(r->outp); delete r; return rc; }
     *res = r;
     return EDSBWT_OK;
@@ -140,8 +144,7 @@ static int search_into_impl(edsbwt_index* idx, const uint8_t* pat_bytes, const u
     for (uint32_t c = 0; c < nchunks; ++c) {
         const uint32_t b = c * chunk, e = std::min<uint64_t>((uint64_t)b + chunk, npat);
         const int sl = c & 1;
-        uint32_t max_len = 0;
-        for (uint32_t i = b; i < e; ++i) { uint64_t l = pat_off[i + 1] - pat_off[i]; if (l > 0xffffffffull) EDS_FAIL(EDSBWT_E_ARG, "pattern %u too long", i); if (l > max_len) max_len = (uint32_t)l; }
+        const uint32_t max_len = 0;                                  // found on the device if the level-synchronous tier is needed
         if (c + 1 < nchunks) issue_in(c + 1);                       // overlaps the search below
         if (c >= 2) CUDA_OK(cudaEventSynchronize(P.ev_out[sl]));     // result buffers of chunk c-2 are free again
         CUDA_OK(cudaStreamWaitEvent(ix.stream, P.ev_in[sl], 0));
@@ -210,8 +213,7 @@ int edsbwt_search_trace(edsbwt_index* idx, const uint8_t* pat_bytes, const uint6
         Index& ix = idx->ix;
         CUDA_OK(cudaSetDevice(ix.device));
         const uint64_t nb = pat_off[npat] - pat_off[0];
-        uint32_t max_len = 0;
-        for (uint32_t i = 0; i < npat; ++i) { uint64_t l = pat_off[i + 1] - pat_off[i]; if (l > 0xffffffffull) EDS_FAIL(EDSBWT_E_ARG, "pattern %u too long", i); if (l > max_len) max_len = (uint32_t)l; }
+        const uint32_t max_len = 0;
         DevBuf<uint8_t> d_bytes; DevBuf<uint64_t> d_off; d_bytes.ensure(nb + 16); d_off.ensure((size_t)npat + 1);
         if (nb) CUDA_OK(cudaMemcpy(d_bytes.p, pat_bytes + pat_off[0], nb, cudaMemcpyHostToDevice));
         CUDA_OK(cudaMemcpy(d_off.p, pat_off, ((size_t)npat + 1) * 8, cudaMemcpyHostToDevice));
@@ -272,6 +274,13 @@ int edsbwt_gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, in
     int rc = require_device(device);
     if (rc) return rc;
     return guarded([&] { *gb_per_s = gather_bench(device, buffer_bytes, n_access, iters); });
+}
+
+int edsbwt_gather_bench_ex(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, int granule_bytes, double* gb_per_s) {
+    if (!gb_per_s) return EDSBWT_E_ARG;
+    int rc = require_device(device);
+    if (rc) return rc;
+    return guarded([&] { *gb_per_s = gather_bench(device, buffer_bytes, n_access, iters, granule_bytes); });
 }
 
 int edsbwt_build_from_collection(const uint8_t* text, const uint64_t* str_off, uint32_t nstr, const uint8_t* seg_first,

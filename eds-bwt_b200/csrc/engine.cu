@@ -664,6 +664,30 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
         }
     }
     v.occ = ix.occ.p;
+    // ---- keep the Occ blocks resident in L2 (B200: 126 MB; the cfg4 Occ array is 142 MB): every search step is one random
+    //      64-byte fetch from this array, everything else the search touches (seed table, patterns, results) streams through.
+    //      MEASURED (profiles/r01_l2_persist_ab.txt): 4.84 ms with the window vs 4.54 ms without at cfg4 / k = 14 -- the
+    //      carve-out takes more from the streaming traffic than it gives the Occ fetches, so it is OFF unless
+    //      EDSBWT_L2_PERSIST=1.
+    {
+        const char* e = getenv("EDSBWT_L2_PERSIST");
+        cudaDeviceProp prop{};
+        if (e && e[0] == '1' && cudaGetDeviceProperties(&prop, ix.device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0) {
+            size_t occ_bytes = (size_t)(h.n / OCC_ROWS + 1) * 64;
+            size_t carve = std::min<size_t>(occ_bytes, (size_t)prop.persistingL2CacheMaxSize);
+            size_t win = std::min<size_t>(occ_bytes, (size_t)prop.accessPolicyMaxWindowSize);
+            if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) == cudaSuccess && win) {
+                cudaStreamAttrValue attr{};
+                attr.accessPolicyWindow.base_ptr = (void*)ix.occ.p;
+                attr.accessPolicyWindow.num_bytes = win;
+                attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)carve / (double)win);
+                attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                if (cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr) == cudaSuccess) ix.l2_persist_bytes = carve;
+            }
+            cudaGetLastError();
+        }
+    }
     // ---- end-marker array and segment structure (rank/select on .bitvector, closure through empty strings)
     ix.eof_flat.ensure(h.n_text + 1); ix.str_seg.ensure(h.n_text + 1); ix.seg_first.ensure((size_t)h.n_seg + 3); ix.seg_low.ensure((size_t)h.n_seg + 2);
     {
@@ -745,6 +769,16 @@ __global__ void ls_alive_mark_kernel(PatView pv, uint32_t step, const uint32_t* 
     if (i && pat[i - 1] == q) return;
     uint32_t m = pv.len[q], L = (m < pv.k ? m : pv.k) + step + 1;
     alive[ids ? ids[q] : q] = L < m ? L : m;
+}
+
+// longest pattern of a subset (only needed by the level-synchronous tier; computed on demand so that the host never
+// walks the offsets of a batch)
+__global__ void max_len_kernel(const uint64_t* __restrict__ off, const uint32_t* __restrict__ ids, uint32_t nsub, unsigned int* __restrict__ out) {
+    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t m = 0;
+    if (q < nsub) { uint32_t g = ids ? ids[q] : q; uint64_t l = off[g + 1] - off[g]; m = l > 0xffffffffull ? 0u : (uint32_t)l; }
+    for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
 }
 
 static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, const uint32_t* ids, uint32_t nsub, uint32_t max_len,
@@ -855,6 +889,12 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
         }
         if (novf) {
             // ---- level-synchronous engine: the whole batch (ENGINE_LEVELSYNC) or the patterns whose frontier outgrew the fused kernel
+            if (max_len == 0) {
+                CUDA_OK(cudaMemsetAsync(ws.scalars.p + 2, 0, 4, s));
+                max_len_kernel<<<grid_for(novf, 256), 256, 0, s>>>(d_off, ids, novf, ws.scalars.p + 2);
+                max_len = read_u32(ws, ws.scalars.p + 2, s);
+                ws.launches += 1;
+            }
             uint32_t nF = levelsync_search(ix, d_bytes, d_off, ids, novf, max_len, st, steps, peak, d_alive, k_eff);
             if (nF) {
                 if ((uint64_t)nstage + nF > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 result intervals in one batch; split the batch");

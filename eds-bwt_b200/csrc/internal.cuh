@@ -226,6 +226,7 @@ struct Index {
     Pipe* pipe = nullptr;
     MoveTable* move = nullptr;          // built at open (opts.build_move) or by the first EDSBWT_LF_MOVE search
     uint32_t move_a = 8;
+    uint64_t l2_persist_bytes = 0;      // persisting-L2 carve-out granted for the Occ array
     std::shared_ptr<ResultPool> pool = std::make_shared<ResultPool>();
     uint32_t chunk_patterns = 1u << 21;     // patterns per pipeline chunk of the host-buffer searches
     edsbwt_stats last{};
@@ -271,7 +272,7 @@ void launch_move_locate(const IndexView& ix, const MoveView& mv, const uint2* pl
 void build_index_files(const uint8_t* letters, const uint64_t* str_off, uint32_t nstr, const uint8_t* seg_first,
                        const std::string& out_base, int device);
 // gather_bench.cu
-double gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, int iters);
+double gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, int granule = 64);
 
 }  // namespace edsbwt
 

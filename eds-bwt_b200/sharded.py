@@ -1,0 +1,130 @@
+"""Multi-GPU search: patterns sharded across the ranks of one box, index replicated on every GPU.
+
+One process per GPU (torchrun); `torch.distributed` is plumbing only.  The search itself has no exchange step: rank g
+searches the contiguous block [g*N/G, (g+1)*N/G) of the pattern list on its own copy of the index.  The only
+collectives are the result gather the north star names:
+
+    counts   all_gather_into_tensor of the per-pattern counts (u32, shards padded to ceil(N/G))   -> ncclAllGather
+    tuples   per-rank occurrence totals all-gathered (8 B each), then a gather-v of the 20-byte tuples to `dst`
+             as one batch of isend/irecv                                                          -> ncclGroupStart{Send/Recv}
+
+Tuples carry batch-global pattern indices (the library adds the shard base), so the gathered buffer is already grouped by
+ascending pattern: shards are contiguous and each shard's tuples are grouped by pattern.
+
+The functions below only move tensors; they run unchanged on CPU tensors over gloo (tests/test_sharded.py, world size 2).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def shard_range(npat, world, rank):
+    """Contiguous block of the pattern list owned by `rank`: [rank*N/G, (rank+1)*N/G)."""
+    return (npat * rank) // world, (npat * (rank + 1)) // world
+
+
+def shard_pad(npat, world):
+    """Largest shard size = the per-rank slot of the counts all-gather."""
+    return max(shard_range(npat, world, r)[1] - shard_range(npat, world, r)[0] for r in range(world)) if world else 0
+
+
+def gather_results(counts_local, occ_local, npat, group=None, dst=0):
+    """counts_local: int32 tensor [shard size] (u32 bit patterns); occ_local: int32 tensor [k, 5] (edsbwt_occ rows).
+    -> (counts of the whole batch, int32 [npat], on every rank;
+        tuples of the whole batch, int32 [total, 5], on rank `dst` and None elsewhere;
+        per-rank occurrence totals, python list)"""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = counts_local.device
+    b, e = shard_range(npat, world, rank)
+    assert counts_local.numel() == e - b, (counts_local.numel(), b, e)
+    pad = shard_pad(npat, world)
+    # ---- counts: one all-gather of equal slots
+    slot = torch.zeros(pad, dtype=torch.int32, device=dev)
+    slot[: e - b] = counts_local
+    allc = torch.empty(pad * world, dtype=torch.int32, device=dev)
+    dist.all_gather_into_tensor(allc, slot, group=group)
+    parts = []
+    for r in range(world):
+        rb, re_ = shard_range(npat, world, r)
+        parts.append(allc[r * pad: r * pad + (re_ - rb)])
+    counts = torch.cat(parts) if parts else allc[:0]
+    # ---- occurrence totals of every rank (exclusive scan = where each rank's tuples land)
+    k = int(occ_local.shape[0])
+    tot = torch.tensor([k], dtype=torch.int64, device=dev)
+    tots = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(tots, tot, group=group)
+    tots = [int(x) for x in tots.tolist()]
+    # ---- gather-v of the tuples to dst
+    occ = None
+    ops = []
+    if rank == dst:
+        occ = torch.empty((sum(tots), 5), dtype=torch.int32, device=dev)
+        ofs = 0
+        for r in range(world):
+            if r == dst:
+                if tots[r]:
+                    occ[ofs: ofs + tots[r]] = occ_local
+            elif tots[r]:
+                ops.append(dist.P2POp(dist.irecv, occ[ofs: ofs + tots[r]], _global_rank(r, group), group))
+            ofs += tots[r]
+    elif k:
+        ops.append(dist.P2POp(dist.isend, occ_local.contiguous(), _global_rank(dst, group), group))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    return counts, occ, tots
+
+
+def _global_rank(r, group):
+    return r if group is None else dist.get_global_rank(group, r)
+
+
+class _DevArray:
+    """Zero-copy view of library-owned device memory for torch (``torch.as_tensor(_DevArray(...), device=...)``)."""
+
+    def __init__(self, ptr, shape, typestr="<i4"):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 3}
+
+
+def device_result_tensors(res, device):
+    """DeviceResult -> (counts int32 [npat], tuples int32 [nocc, 5]) views over the library's HBM buffers."""
+    c_ptr, o_ptr = res.device_ptrs()
+    dev = torch.device("cuda", device)
+    counts = torch.as_tensor(_DevArray(c_ptr, (res.npat,)), device=dev) if res.npat else torch.zeros(0, dtype=torch.int32, device=dev)
+    occ = torch.as_tensor(_DevArray(o_ptr, (res.nocc, 5)), device=dev) if res.nocc else torch.zeros((0, 5), dtype=torch.int32, device=dev)
+    return counts, occ
+
+
+class ShardedSearcher:
+    """Index replicated per GPU + pattern sharding + NCCL result gather.  `index` is an eds-bwt_b200 Index on this rank's GPU."""
+
+    def __init__(self, index, group=None):
+        self.index = index
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+
+    def search(self, data, off, locate=True, lf_variant=0, dst=0):
+        """data/off: the WHOLE batch as packed host arrays (uint8 bytes, uint64 offsets[npat+1]), identical on every rank.
+        -> (counts uint32[npat] on every rank, structured occurrence array on rank dst / None elsewhere)"""
+        from . import OCC_DTYPE       # noqa: the package name carries a hyphen; relative import works
+        npat = len(off) - 1
+        b, e = shard_range(npat, self.world, self.rank)
+        dev = torch.device("cuda", self.index.device)
+        lo, hi = int(off[b]), int(off[e])
+        d_data = torch.from_numpy(np.ascontiguousarray(data[lo:hi]) if hi > lo else np.zeros(1, np.uint8)).to(dev)
+        d_off = torch.from_numpy((off[b:e + 1] - off[b]).astype(np.int64)).to(dev)
+        max_len = int((off[b + 1:e + 1] - off[b:e]).max()) if e > b else 0
+        res = self.index.search_device(d_data.data_ptr(), d_off.data_ptr(), e - b, hi - lo, max_len, locate=locate,
+                                       lf_variant=lf_variant, pat_base=b)
+        try:
+            c_loc, o_loc = device_result_tensors(res, self.index.device)
+            counts, occ, _ = gather_results(c_loc, o_loc, npat, self.group, dst)
+            counts_np = counts.cpu().numpy().view(np.uint32)
+            occ_np = None
+            if occ is not None:
+                occ_np = occ.cpu().numpy().view(np.uint32).reshape(-1).view(OCC_DTYPE) if occ.numel() else np.zeros(0, OCC_DTYPE)
+        finally:
+            res.free()
+        return counts_np, occ_np

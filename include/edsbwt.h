@@ -127,9 +127,13 @@ void edsbwt_host_free(void* p);
 int  edsbwt_set_chunk(edsbwt_index* idx, uint32_t patterns_per_chunk);   /* pipeline granularity, default 2^21; 0 = one chunk */
 
 /* Same search with the packed patterns already resident in HBM and the results left there (the `value`
- * leg of bench.py).  d_* are DEVICE pointers on the handle's device.  total_bytes = pat_off[npat]. */
+ * leg of bench.py).  d_* are DEVICE pointers on the handle's device.  total_bytes = pat_off[npat]; max_len = length of
+ * the longest pattern, or 0 when unknown (found on the device if needed). */
 int  edsbwt_search_device(edsbwt_index* idx, const uint8_t* d_pat_bytes, const uint64_t* d_pat_off, uint32_t npat,
                           uint64_t total_bytes, uint32_t max_len, int locate, int lf_variant, edsbwt_result** res);
+/* The same for one shard of a larger batch (multi-GPU: patterns sharded, index replicated): tuples carry pat + pat_base. */
+int  edsbwt_search_device_at(edsbwt_index* idx, const uint8_t* d_pat_bytes, const uint64_t* d_pat_off, uint32_t npat,
+                             uint64_t total_bytes, uint32_t max_len, int locate, int lf_variant, uint32_t pat_base, edsbwt_result** res);
 int  edsbwt_result_sizes(const edsbwt_result* res, uint32_t* npat, uint64_t* nocc);
 int  edsbwt_result_device_ptrs(const edsbwt_result* res, const uint32_t** d_counts, const edsbwt_occ** d_occ);
 int  edsbwt_result_fetch(const edsbwt_result* res, uint32_t* counts, edsbwt_occ* occ); /* D2H into host buffers */
@@ -166,6 +170,7 @@ int  edsbwt_build_from_collection(const uint8_t* text, const uint64_t* str_off, 
 
 /* --- roofline denominator: 64-byte random gather over buffer_bytes of HBM (kernel K7). */
 int  edsbwt_gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, double* gb_per_s);
+int  edsbwt_gather_bench_ex(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, int granule_bytes /* 32, 64, 128 */, double* gb_per_s);
 
 void        edsbwt_free(void* p);
 const char* edsbwt_strerror(int code);

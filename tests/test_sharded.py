@@ -1,0 +1,148 @@
+"""Multi-GPU plumbing: pattern sharding + result gather.  The collectives are exercised on CPU tensors over
+gloo with world sizes 2 and 3 (the local search is played by the oracle -- tests only); on a GPU box the same code runs
+over NCCL through ShardedSearcher (world size = number of visible GPUs, at least 1)."""
+import importlib
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import eds_index as E
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_shard_range_partitions():
+    sh = importlib.import_module("eds-bwt_b200.sharded")
+    for n in [0, 1, 2, 7, 8, 9, 1000003]:
+        for w in [1, 2, 3, 4, 8]:
+            r = [sh.shard_range(n, w, g) for g in range(w)]
+            assert r[0][0] == 0 and r[-1][1] == n
+            assert all(r[g][1] == r[g + 1][0] for g in range(w - 1))
+            assert max(e - b for b, e in r) - min(e - b for b, e in r) <= 1
+            assert sh.shard_pad(n, w) == max(e - b for b, e in r)
+
+
+def _gloo_worker(rank, world, port, base, pf, npat, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        sh = importlib.import_module("eds-bwt_b200.sharded")
+        from oracle import run as R
+        b, e = sh.shard_range(npat, world, rank)
+        # local "search" of this rank's shard: the oracle on lines [b, e) of the pattern file
+        lines = open(pf, "rb").read().split(b"\n")[:npat]
+        spf = "%s.%d" % (pf, rank)
+        with open(spf, "wb") as f:
+            f.write(b"\n".join(lines[b:e]))
+        if e > b:
+            counts, rows, _ = R.run_port(base, spf, locate=True)
+        else:
+            counts, rows = [], []
+        c_loc = torch.tensor(np.array(counts, dtype=np.uint32).view(np.int32), dtype=torch.int32)
+        o = np.array([(p - 1 + b, w, s, j, r) for (p, w, s, j, r) in rows], dtype=np.uint32).reshape(-1, 5)
+        o_loc = torch.from_numpy(o.view(np.int32).copy())
+        allc, occ, tots = sh.gather_results(c_loc, o_loc, npat, None, dst=0)
+        q.put((rank, allc.numpy().view(np.uint32).tolist(), None if occ is None else occ.numpy().view(np.uint32).tolist(), tots))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,npat", [(2, 41), (3, 10), (2, 1)])
+def test_gather_over_gloo(world, npat, oracle_built, tmp_path):
+    rng = np.random.default_rng(5 + world)
+    segs = E.random_eds(rng, n_seg=200, max_var=4, max_len=5, p_empty=0.2)
+    ix = E.build_index(segs)
+    base = str(tmp_path / "idx")
+    E.write_index(ix, base)
+    pats = E.sample_patterns(rng, segs, npat, [2, 3, 5, 8, 12])
+    pf = str(tmp_path / "p.txt")
+    E.write_patterns(pf, pats)
+    c_ref, rows_ref, _ = oracle_built.run_port(base, pf, locate=True)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, world, port, base, pf, npat, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    got.sort()
+    for rank, counts, occ, tots in got:
+        assert counts == c_ref                                  # every rank holds the counts of the whole batch
+        assert sum(tots) == len(rows_ref)
+        if rank == 0:
+            rows = [(p + 1, w, s, j, r) for (p, w, s, j, r) in occ]
+            assert sorted(rows) == sorted(rows_ref)
+            assert [r[0] for r in rows] == sorted(r[0] for r in rows)      # grouped by ascending pattern without sorting
+        else:
+            assert occ is None
+
+
+# ---- GPU: the real thing over NCCL -------------------------------------------------------------------------------------
+def _nccl_worker(rank, world, port, base, pats, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        eb = importlib.import_module("eds-bwt_b200")
+        sh = importlib.import_module("eds-bwt_b200.sharded")
+        data, off = eb.pack_patterns(pats)
+        with eb.Index(base, device=rank) as idx:
+            s = sh.ShardedSearcher(idx)
+            out = []
+            for lf in (eb.LF_RANK, eb.LF_MOVE):
+                counts, occ = s.search(data, off, locate=True, lf_variant=lf)
+                out.append((counts.tolist(), None if occ is None else eb.occ_rows(occ)))
+        q.put((rank, out))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_sharded_search_nccl(oracle_built, tmp_path):
+    world = min(torch.cuda.device_count(), 2)
+    assert world >= 1
+    rng = np.random.default_rng(17)
+    segs = E.random_eds(rng, n_seg=1500, max_var=4, max_len=6, p_empty=0.15, nondeg_len=(1, 40))
+    ix = E.build_index(segs)
+    base = str(tmp_path / "idx")
+    E.write_index(ix, base)
+    pats = E.sample_patterns(rng, segs, 501, [4, 9, 16, 32, 33])
+    pf = str(tmp_path / "p.txt")
+    E.write_patterns(pf, pats)
+    c_ref, rows_ref, _ = oracle_built.run_port(base, pf, locate=True)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, base, pats, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    for rank, out in got:
+        for counts, rows in out:
+            assert counts == c_ref
+            if rank == 0:
+                assert rows == sorted(rows_ref)
+            else:
+                assert rows is None
