@@ -107,7 +107,7 @@ void build_occ_blocks(const uint8_t* d_bytes, uint32_t n, const Lut& lut, DevBuf
 // SA table: row -> (string, offset), by walking every string backwards from its end-marker row
 // (the inverse of the reference's locate rounds, findMultipleDollarsBackward :349-603)
 // ===================================================================================================
-__global__ void sa_walk_kernel(IndexView ix, uint2* __restrict__ sa, uint32_t* __restrict__ slen) {
+__global__ void sa_walk_kernel(const __grid_constant__ IndexView ix, uint2* __restrict__ sa, uint32_t* __restrict__ slen) {
     uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= ix.n_text) return;
     uint32_t row = w, d = 0;                     // pile-0 row w is the suffix "$_w"
@@ -233,7 +233,7 @@ __global__ void key_offsets_kernel(const uint32_t* __restrict__ pat, uint32_t nF
 //   otherwise : the character comes from the packed pattern; finished patterns pass through unchanged
 template <bool KEYMODE>
 __global__ void __launch_bounds__(256)
-lf_step_kernel(IndexView ix, PatView pv, uint32_t step, const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo,
+lf_step_kernel(const __grid_constant__ IndexView ix, PatView pv, uint32_t step, const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo,
                const uint32_t* __restrict__ hi, uint32_t nF, uint32_t* __restrict__ olo, uint32_t* __restrict__ ohi,
                uint32_t* __restrict__ dcnt, uint32_t* __restrict__ dstart, uint32_t* __restrict__ keep,
                StatsDev* __restrict__ st, uint32_t kc, int is_dol) {
@@ -394,7 +394,7 @@ __global__ void ls_finalize_kernel(const uint32_t* __restrict__ pat, const uint3
 // one thread per occurrence row: (string, offset) by table lookup or by LF-walk, then segment / index in segment
 // (indices_of_dollars_in_interval, EDSBWTsearch.cpp:1310-1332).  Output grouped by ascending pattern.
 template <bool WALK>
-__global__ void locate_kernel(IndexView ix, const uint2* __restrict__ plist, const uint32_t* __restrict__ occ_ofs, const uint2* __restrict__ staging,
+__global__ void locate_kernel(const __grid_constant__ IndexView ix, const uint2* __restrict__ plist, const uint32_t* __restrict__ occ_ofs, const uint2* __restrict__ staging,
                               uint32_t npat, uint64_t nocc, uint32_t pat_base, edsbwt_occ* __restrict__ out, StatsDev* __restrict__ st) {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t steps = 0;
@@ -635,7 +635,7 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     CUDA_OK(cudaEventCreate(&ws.ev0)); CUDA_OK(cudaEventCreate(&ws.ev1)); CUDA_OK(cudaEventCreate(&ws.evk0)); CUDA_OK(cudaEventCreate(&ws.evk1));
     CUDA_OK(cudaEventCreate(&ws.evf0)); CUDA_OK(cudaEventCreate(&ws.evf1)); CUDA_OK(cudaEventCreate(&ws.evl0)); CUDA_OK(cudaEventCreate(&ws.evl1));
     ix.engine = o.engine == EDSBWT_ENGINE_LEVELSYNC ? EDSBWT_ENGINE_LEVELSYNC : EDSBWT_ENGINE_FUSED;
-    ix.fused_cap = o.fused_cap > 0 ? (uint32_t)o.fused_cap : 24u;
+    ix.fused_cap = o.fused_cap > 0 ? (uint32_t)o.fused_cap : 20u;
     if (ix.fused_cap < 4) ix.fused_cap = 4;
     if (ix.fused_cap > FUSED_BIG_CAP) ix.fused_cap = FUSED_BIG_CAP;
     ix.fused_cap2 = o.fused_cap2 > 0 ? std::min<uint32_t>((uint32_t)o.fused_cap2, FUSED_BIG_CAP) : FUSED_BIG_CAP;

@@ -52,13 +52,20 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 }  // namespace
 
 template <bool STATS>
-__global__ void __launch_bounds__(FUSED_THREADS)
-fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ poff,
+__global__ void __launch_bounds__(FUSED_THREADS, 10)
+fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant__ SeedView sv, uint32_t k, const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ poff,
                     const uint32_t* __restrict__ ids, uint32_t npat, const uint8_t* __restrict__ lut, uint32_t cap, FusedOut out,
                     StatsDev* __restrict__ st, uint32_t kc) {
     extern __shared__ uint2 s_list[];                 // [cap][FUSED_THREADS]
     __shared__ uint8_t s_lut[256];
+    // kernel-parameter arrays indexed at run time (seed level, letter) would be copied to LOCAL memory by the compiler
+    // (ncu: 114 M local sectors per launch): keep them in shared memory instead
+    __shared__ const uint32_t* s_off[17];
+    __shared__ const uint2* s_iv[17];
+    __shared__ uint32_t s_Cl[5];
     for (int i = threadIdx.x; i < 256; i += FUSED_THREADS) s_lut[i] = lut[i];
+    if (threadIdx.x < 17) { s_off[threadIdx.x] = sv.off[threadIdx.x]; s_iv[threadIdx.x] = sv.iv[threadIdx.x]; }
+    if (threadIdx.x < 5) s_Cl[threadIdx.x] = ix.Cl[threadIdx.x];
     __syncthreads();
 #define LIST(j) s_list[(j) * FUSED_THREADS + threadIdx.x]
 #define DOL(i) s_list[(cap - 1 - (i)) * FUSED_THREADS + threadIdx.x]
@@ -82,9 +89,9 @@ fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __rest
             if (i >= m - L0) key |= c << (2 * (i - (m - L0)));
         }
         if (ok) {
-            uint32_t a = __ldg(sv.off[L0] + key), n0 = __ldg(sv.off[L0] + key + 1) - a;
+            uint32_t a = __ldg(s_off[L0] + key), n0 = __ldg(s_off[L0] + key + 1) - a;
             if (n0 > cap) ovf = true;
-            else { for (uint32_t j = 0; j < n0; ++j) LIST(j) = __ldg(sv.iv[L0] + a + j); nF = n0; }
+            else { for (uint32_t j = 0; j < n0; ++j) LIST(j) = __ldg(s_iv[L0] + a + j); nF = n0; }
         } else m = 0;
     }
     const uint32_t steps = m - L0;
@@ -93,7 +100,7 @@ fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __rest
     for (; s < steps && nF && !ovf; ++s) {
         const int c = (int)s_lut[__ldg(bytes + base + (m - L0 - s - 1))];
         const uint32_t x0 = (c & 1) ? 0u : 0xffffffffu, x1 = (c & 2) ? 0u : 0xffffffffu;
-        const uint32_t Cc = ix.Cl[c];
+        const uint32_t Cc = s_Cl[c];
         const bool beyond = STATS && (L0 + s >= kc);
         if (STATS && L0 + s == mk) sI += nF;
         uint32_t nout = 0, ndol = 0;
@@ -176,7 +183,7 @@ fused_search_kernel(IndexView ix, SeedView sv, uint32_t k, const uint8_t* __rest
         else if (s > 0) la = L0 + s - 1;
         else for (uint32_t L = L0 - 1; L >= 1; --L) {                     // empty seed entry: longest shorter suffix that is not
             const uint32_t kl = key >> (2 * (L0 - L));
-            if (__ldg(sv.off[L] + kl + 1) > __ldg(sv.off[L] + kl)) { la = L; break; }
+            if (__ldg(s_off[L] + kl + 1) > __ldg(s_off[L] + kl)) { la = L; break; }
         }
         out.alive[q] = la;
     }

@@ -231,7 +231,7 @@ struct Index {
     uint32_t chunk_patterns = 1u << 21;     // patterns per pipeline chunk of the host-buffer searches
     edsbwt_stats last{};
     int collect_counters = 0; uint32_t canonical_k = 12;
-    int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 24, fused_cap2 = FUSED_BIG_CAP;
+    int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 20, fused_cap2 = FUSED_BIG_CAP;
     uint64_t device_bytes() const;
     ~Index();
 };

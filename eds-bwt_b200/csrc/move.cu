@@ -242,8 +242,8 @@ __device__ __forceinline__ bool move_lf(const MoveView& mv, int c, uint32_t kb, 
 
 }  // namespace
 
-__global__ void __launch_bounds__(MOVE_THREADS)
-move_search_kernel(IndexView ix, MoveView mv, SeedView sv, uint32_t k, const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ poff,
+__global__ void __launch_bounds__(MOVE_THREADS, 4)
+move_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant__ MoveView mv, const __grid_constant__ SeedView sv, uint32_t k, const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ poff,
                    const uint32_t* __restrict__ ids, uint32_t npat, const uint8_t* __restrict__ lut, uint32_t cap, MoveOut out) {
     extern __shared__ uint4 m_list[];                 // [cap][MOVE_THREADS] of (b, e, b', e')
     __shared__ uint8_t s_lut[256];
@@ -364,7 +364,7 @@ move_search_kernel(IndexView ix, MoveView mv, SeedView sv, uint32_t k, const uin
 
 // one thread per occurrence row: walk M_LF.move until the run symbol is '#', counting the steps = offset in the string
 // (MOVE_EDSBWTSearch.cpp:340-368); then k = rank('#', run) over the run heads, w = EOF_ID_Copy[k], segment / index in segment
-__global__ void move_locate_kernel(IndexView ix, MoveView mv, const uint2* __restrict__ plist, const uint32_t* __restrict__ occ_ofs,
+__global__ void move_locate_kernel(const __grid_constant__ IndexView ix, const __grid_constant__ MoveView mv, const uint2* __restrict__ plist, const uint32_t* __restrict__ occ_ofs,
                                    const uint2* __restrict__ staging, uint32_t npat, uint64_t nocc, uint32_t pat_base,
                                    edsbwt_occ* __restrict__ out, StatsDev* __restrict__ st) {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
