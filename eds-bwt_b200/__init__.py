@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(HERE, "libedsbwt_cuda.so")
 LOCATE_SA, LOCATE_WALK = 0, 1
 LF_RANK, LF_MOVE = 0, 1
 ENGINE_FUSED, ENGINE_LEVELSYNC = 0, 1
+ROWS_GROUPED, ROWS_REFERENCE = 0, 1
 
 OCC_DTYPE = np.dtype([("pat", "<u4"), ("str", "<u4"), ("seg", "<u4"), ("idx_in_seg", "<u4"), ("off", "<u4")])
 
@@ -25,6 +26,7 @@ EXPORTS = [
     "edsbwt_build_from_eds", "edsbwt_build_from_collection", "edsbwt_gather_bench", "edsbwt_free",
     "edsbwt_strerror", "edsbwt_last_error", "edsbwt_version", "edsbwt_search_into", "edsbwt_host_alloc", "edsbwt_host_free",
     "edsbwt_set_chunk", "edsbwt_search_trace", "edsbwt_move_table_build", "edsbwt_move_table_fetch", "edsbwt_search_device_at", "edsbwt_gather_bench_ex",
+    "edsbwt_set_row_order", "edsbwt_result_write_csv", "edsbwt_search_to_csv",
 ]
 
 
@@ -100,6 +102,9 @@ def lib():
         L.edsbwt_last_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
         L.edsbwt_set_stats.argtypes = [C.c_void_p, C.c_int, C.c_uint32]
         L.edsbwt_write_csv.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_int]
+        L.edsbwt_set_row_order.argtypes = [C.c_void_p, C.c_int]
+        L.edsbwt_result_write_csv.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_uint64)]
+        L.edsbwt_search_to_csv.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_char_p, C.POINTER(C.c_uint64)]
         L.edsbwt_read_patterns.argtypes = [C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint32)]
         L.edsbwt_build_from_eds.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         L.edsbwt_build_from_collection.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_char_p, C.c_int]
@@ -212,6 +217,26 @@ class Index:
                                         len(occ) if occ is not None else 0, C.byref(nocc)))
         return nocc.value
 
+    def set_row_order(self, reference=True):
+        """ROWS_REFERENCE: tuples of a pattern in the reference's csv order."""
+        _check(lib().edsbwt_set_row_order(self._h, ROWS_REFERENCE if reference else ROWS_GROUPED))
+
+    def search_to_csv(self, patterns, csv_path, lf_variant=LF_RANK, header=True):
+        """The reference constructor's whole loop: search + locate, rows in reference order formatted on the device.
+        -> (counts, number of rows written)"""
+        data, off = pack_patterns(patterns) if isinstance(patterns, (list, tuple)) and not (
+            len(patterns) == 2 and isinstance(patterns[0], np.ndarray)) else patterns
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.uint64)
+        npat = len(off) - 1
+        counts = np.zeros(max(npat, 1), dtype=np.uint32)
+        if header:
+            write_csv(csv_path, np.zeros(0, dtype=OCC_DTYPE), move=(lf_variant == LF_MOVE))
+        nocc = C.c_uint64(0)
+        _check(lib().edsbwt_search_to_csv(self._h, data.ctypes.data, off.ctypes.data, npat, lf_variant, counts.ctypes.data,
+                                          os.fsencode(csv_path), C.byref(nocc)))
+        return counts[:npat], nocc.value
+
     def set_chunk(self, patterns_per_chunk):
         _check(lib().edsbwt_set_chunk(self._h, patterns_per_chunk))
 
@@ -235,6 +260,12 @@ class DeviceResult:
         c, o = C.c_void_p(), C.c_void_p()
         _check(lib().edsbwt_result_device_ptrs(self._h, C.byref(c), C.byref(o)))
         return c.value, o.value
+
+    def write_csv(self, index, path, move=False, append=False):
+        """rows formatted to decimal text on the device; -> bytes of row text written"""
+        nb = C.c_uint64(0)
+        _check(lib().edsbwt_result_write_csv(index._h, self._h, os.fsencode(path), int(move), int(append), C.byref(nb)))
+        return nb.value
 
     def fetch(self):
         counts = np.zeros(max(self.npat, 1), dtype=np.uint32)

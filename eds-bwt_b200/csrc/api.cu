@@ -232,6 +232,92 @@ int edsbwt_search_trace(edsbwt_index* idx, const uint8_t* pat_bytes, const uint6
     });
 }
 
+int edsbwt_set_row_order(edsbwt_index* idx, int order) {
+    if (!idx || (order != EDSBWT_ROWS_GROUPED && order != EDSBWT_ROWS_REFERENCE)) return EDSBWT_E_ARG;
+    idx->ix.row_order = order;
+    return EDSBWT_OK;
+}
+
+static const char* csv_header(int move) { return move ? "#Pat\t$_i\tD[i]\tS_j\tS_j[r] \n" : "#Pat\t$_i\tD[i]\tS_j\tS_j[r]\n"; }
+
+int edsbwt_result_write_csv(edsbwt_index* idx, const edsbwt_result* res, const char* path, int move, int append, uint64_t* bytes) {
+    if (!idx || !res || !path) return EDSBWT_E_ARG;
+    if (bytes) *bytes = 0;
+    FILE* f = fopen(path, append ? "ab" : "wb");
+    if (!f) { set_error("ERROR opening file %s to write output", path); return EDSBWT_E_IO; }
+    if (!append) fputs(csv_header(move), f);
+    int rc = guarded([&] {
+        Index& ix = idx->ix;
+        CUDA_OK(cudaSetDevice(ix.device));
+        std::lock_guard<std::mutex> lock(ix.mu);
+        uint64_t w = write_csv_device(ix, res->outp->occ.p, res->outp->nocc, 1, f, ix.stream, nullptr);   // tuples already carry pat_base
+        if (bytes) *bytes = w;
+    });
+    if (fclose(f) != 0 && !rc) { set_error("error closing %s", path); rc = EDSBWT_E_IO; }
+    return rc;
+}
+
+// search + locate + ordered rows + device formatting, chunk by chunk: H2D of chunk c+1 overlaps the search of chunk c
+int edsbwt_search_to_csv(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat, int lf_variant,
+                         uint32_t* counts, const char* csv_path, uint64_t* nocc) {
+    if (!idx || !csv_path || (npat && (!pat_off || !counts))) return EDSBWT_E_ARG;
+    if (nocc) *nocc = 0;
+    if (npat == 0) return EDSBWT_OK;
+    FILE* f = fopen(csv_path, "ab");
+    if (!f) { set_error("ERROR opening file %s to write output", csv_path); return EDSBWT_E_IO; }
+    int rc = guarded([&] {
+        Index& ix = idx->ix;
+        CUDA_OK(cudaSetDevice(ix.device));
+        if (!ix.pipe) {
+            ix.pipe = new Pipe;
+            CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->in, cudaStreamNonBlocking));
+            CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->outs, cudaStreamNonBlocking));
+            for (int i = 0; i < 2; ++i) { CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_in[i], cudaEventDisableTiming)); CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_out[i], cudaEventDisableTiming)); }
+        }
+        Pipe& P = *ix.pipe;
+        const int saved_order = ix.row_order;
+        ix.row_order = EDSBWT_ROWS_REFERENCE;
+        struct Restore { Index& ix; int o; ~Restore() { ix.row_order = o; } } restore{ix, saved_order};
+        const uint32_t chunk = ix.chunk_patterns ? ix.chunk_patterns : npat;
+        const uint32_t nchunks = (npat + chunk - 1) / chunk;
+        uint64_t total = 0, launches = 0;
+        edsbwt_stats acc{};
+        auto issue_in = [&](uint32_t c) {
+            const uint32_t b = c * chunk, e = (uint32_t)std::min<uint64_t>((uint64_t)b + chunk, npat);
+            const uint64_t nb = pat_off[e] - pat_off[b];
+            const int sl = c & 1;
+            P.bytes[sl].ensure(nb + 16); P.off[sl].ensure((size_t)(e - b) + 1);
+            if (nb) CUDA_OK(cudaMemcpyAsync(P.bytes[sl].p, pat_bytes + pat_off[b], nb, cudaMemcpyHostToDevice, P.in));
+            CUDA_OK(cudaMemcpyAsync(P.off[sl].p, pat_off + b, ((size_t)(e - b) + 1) * 8, cudaMemcpyHostToDevice, P.in));
+            CUDA_OK(cudaEventRecord(P.ev_in[sl], P.in));
+        };
+        issue_in(0);
+        for (uint32_t c = 0; c < nchunks; ++c) {
+            const uint32_t b = c * chunk, e = (uint32_t)std::min<uint64_t>((uint64_t)b + chunk, npat);
+            const int sl = c & 1;
+            if (c + 1 < nchunks) issue_in(c + 1);                   // the other slot is free (chunk c-1 fully written): overlaps the search below
+            CUDA_OK(cudaStreamWaitEvent(ix.stream, P.ev_in[sl], 0));
+            const uint8_t* d_bytes = (const uint8_t*)((uintptr_t)P.bytes[sl].p - (uintptr_t)pat_off[b]);
+            run_search(ix, d_bytes, P.off[sl].p, e - b, pat_off[e] - pat_off[b], 0, true, lf_variant, P.res[sl], b);
+            const edsbwt_stats st = ix.last;
+            acc.L += st.L; acc.O += st.O; acc.kernel_launches += st.kernel_launches; acc.total_ms += st.total_ms;
+            acc.search_kernel_ms += st.search_kernel_ms; acc.locate_kernel_ms += st.locate_kernel_ms; acc.overflow_patterns += st.overflow_patterns;
+            CUDA_OK(cudaMemcpyAsync(counts + b, P.res[sl].counts.p, (size_t)(e - b) * 4, cudaMemcpyDeviceToHost, ix.stream));
+            {
+                std::lock_guard<std::mutex> lock(ix.mu);
+                write_csv_device(ix, P.res[sl].occ.p, P.res[sl].nocc, 1, f, ix.stream, &launches);
+            }
+            CUDA_OK(cudaStreamSynchronize(ix.stream));
+            total += P.res[sl].nocc;
+        }
+        acc.kernel_launches += launches;
+        ix.last = acc;
+        if (nocc) *nocc = total;
+    });
+    if (fclose(f) != 0 && !rc) { set_error("error closing %s", csv_path); rc = EDSBWT_E_IO; }
+    return rc;
+}
+
 int edsbwt_move_table_build(edsbwt_index* idx) {
     if (!idx) return EDSBWT_E_ARG;
     return guarded([&] { std::lock_guard<std::mutex> lock(idx->ix.mu); build_move_table(idx->ix); });

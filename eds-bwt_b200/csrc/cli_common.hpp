@@ -101,13 +101,10 @@ inline int run_cli(int argc, char** argv, bool move) {
     std::vector<uint32_t> counts(npat ? npat : 1, 0), interrupted;
     edsbwt_occ* occ = nullptr; uint64_t nocc = 0;
     const int lf = move ? EDSBWT_LF_MOVE : EDSBWT_LF_RANK;
-    if (recover) rc = edsbwt_search(idx, bytes, off, npat, 1, lf, counts.data(), &occ, &nocc);
+    // locate: rows come out in the reference's csv order and are formatted to text on the device
+    if (recover) rc = edsbwt_search_to_csv(idx, bytes, off, npat, lf, counts.data(), csv.c_str(), &nocc);
     else { interrupted.assign(npat ? npat : 1, 0); rc = edsbwt_search_trace(idx, bytes, off, npat, lf, counts.data(), interrupted.data()); }
     if (rc) die("search failed", rc);
-    if (recover && nocc) {
-        rc = edsbwt_write_csv(csv.c_str(), occ, nocc, 0, move ? 1 : 0, 1);
-        if (rc) die("csv write failed", rc);
-    }
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 
     // ---- per-pattern report (:746 / MOVE :113,371)

@@ -461,10 +461,11 @@ Index::~Index() {
     delete ws;
     delete pipe;
     delete move;
+    free_csv_scratch(csv);
     if (stream) cudaStreamDestroy(stream);
 }
 uint64_t Index::device_bytes() const {
-    uint64_t b = occ.bytes() + eof_flat.bytes() + str_seg.bytes() + seg_first.bytes() + seg_low.bytes() + sa.bytes() + link_rec.bytes() + str_info.bytes();
+    uint64_t b = occ.bytes() + eof_flat.bytes() + eof_inv.bytes() + str_seg.bytes() + seg_first.bytes() + seg_low.bytes() + sa.bytes() + link_rec.bytes() + str_info.bytes();
     for (SeedLevel* s : seed) if (s) b += s->off.bytes() + s->iv.bytes();
     if (move) b += move->bytes();
     return b;
@@ -931,6 +932,8 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
                     locate_kernel<false><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, pat_base, out.occ.p, st);
                 CUDA_OK(cudaEventRecord(ws.evl1, s));
                 ws.launches += 1; locate_ran = true;
+                // csv row order of the reference; MOVE's order is the frontier order the kernel emits
+                if (ix.row_order == EDSBWT_ROWS_REFERENCE && !move) ws.launches += order_rows_reference(ix, out, ws.occ_ofs.p, npat, s);
             }
         }
     }

@@ -28,6 +28,42 @@ __device__ __forceinline__ void load_blk(const uint4* __restrict__ occ, uint32_t
     const uint4* p = occ + (size_t)blk * 4;
     ld256(p, b.w); ld256(p + 2, b.w + 8);
 }
+// Pattern characters travel as 2-bit codes in a 64-bit window, 32 characters per fetch: n <= 32 bytes at p -> codes
+// (character i at bits 2i, 2i+1).  Returns false when a byte is not a letter of the index alphabet.  One or two 128-bit
+// loads when p is 16-byte aligned (every fixed-length batch whose length is a multiple of 16), 32-bit loads when 4-byte
+// aligned, byte loads otherwise.  Reading the aligned 16-byte / 4-byte unit that holds the last valid byte stays inside
+// the allocation (cudaMalloc granularity), so short tails need no special case.
+__device__ __forceinline__ bool fetch_codes(const uint8_t* __restrict__ p, uint32_t n, const uint8_t* s_lut, uint64_t& codes) {
+    uint32_t w[8];
+    const uint32_t al = (uint32_t)(uintptr_t)p & 15u;
+    if (al == 0) {
+        const uint4 a = __ldg((const uint4*)p);
+        const uint4 b = n > 16 ? __ldg((const uint4*)p + 1) : make_uint4(0, 0, 0, 0);
+        w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
+    } else if ((al & 3u) == 0) {
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) w[j] = 4u * j < n ? __ldg((const uint32_t*)p + j) : 0u;
+    } else {
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            uint32_t v = 0;
+            #pragma unroll
+            for (int t = 0; t < 4; ++t) if (4u * j + t < n) v |= (uint32_t)__ldg(p + 4 * j + t) << (8 * t);
+            w[j] = v;
+        }
+    }
+    uint32_t lo = 0, hi = 0, bad = 0;                 // branch-free: codes of all 32 slots, invalid slots masked afterwards
+    #pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const uint32_t c0 = s_lut[(w[i >> 2] >> (8 * (i & 3))) & 255u];
+        const uint32_t c1 = s_lut[(w[4 + (i >> 2)] >> (8 * (i & 3))) & 255u];
+        lo |= (c0 & 3u) << (2 * i); hi |= (c1 & 3u) << (2 * i);
+        bad |= (c0 > 3u ? 1u : 0u) << i; bad |= (c1 > 3u ? 1u : 0u) << (16 + i);
+    }
+    const uint64_t cw = ((uint64_t)hi << 32) | lo;
+    codes = n >= 32 ? cw : cw & ((1ull << (2 * n)) - 1);
+    return (bad & (n >= 32 ? 0xffffffffu : ((1u << n) - 1u))) == 0;
+}
 // rank of letter c (x0/x1 = plane inversion masks of c) and number of '#' in rows [0,off) of the block, off in [0,128)
 __device__ __forceinline__ void rank_in_blk(const Blk& b, uint32_t off, int c, uint32_t x0, uint32_t x1, uint32_t& rc, uint32_t& nmk) {
     uint32_t r = c == 0 ? b.w[0] : c == 1 ? b.w[4] : c == 2 ? b.w[8] : b.w[12];
@@ -43,6 +79,51 @@ __device__ __forceinline__ void rank_in_blk(const Blk& b, uint32_t off, int c, u
     rc = r; nmk = k;
 }
 __device__ __forceinline__ uint32_t letters_before(const Blk& b) { return b.w[0] + b.w[4] + b.w[8] + b.w[12]; }
+// mask of the bits below position `below` of a 32-bit word, below clamped to [0, 32] (shl.b32 clamps its shift amount)
+__device__ __forceinline__ uint32_t low_mask(int below) {
+    uint32_t r; const int bb = below < 0 ? 0 : below;
+    asm("shl.b32 %0, 1, %1;" : "=r"(r) : "r"(bb));
+    return r - 1u;
+}
+// LF of the row range [a, b) by letter c: rca / rcb = rank of c before a / b; rda / rdb = rank of '#' before a / b (both 0
+// when the range holds no '#' and lies inside one block).  After the seed lookup nearly every range is one or a few rows
+// inside ONE block: that case is a single sweep over the four 32-row words (letter mask computed once, '#' ranks only
+// when a '#' is present).  nblk = Occ blocks fetched (1 or 2).
+__device__ __forceinline__ void lf_range(const uint4* __restrict__ occ, uint32_t a, uint32_t b, int c, uint32_t x0, uint32_t x1,
+                                         uint32_t& rca, uint32_t& rcb, uint32_t& rda, uint32_t& rdb, uint32_t& nblk) {
+    const uint32_t blkA = a >> 7, blkB = b >> 7;
+    Blk B;
+    load_blk(occ, blkA, B);
+    if (blkA == blkB) {
+        const int offA = (int)(a & 127u), offB = (int)(b & 127u);
+        uint32_t r = c == 0 ? B.w[0] : c == 1 ? B.w[4] : c == 2 ? B.w[8] : B.w[12];
+        uint32_t in = 0, hin = 0;
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t lmA = low_mask(offA - 32 * j), dm = low_mask(offB - 32 * j) & ~lmA;
+            const uint32_t M = (B.w[4 * j + 1] ^ x0) & (B.w[4 * j + 2] ^ x1) & ~B.w[4 * j + 3];
+            r += __popc(M & lmA); in += __popc(M & dm); hin |= B.w[4 * j + 3] & dm;
+        }
+        rca = r; rcb = r + in; rda = rdb = 0; nblk = 1;
+        if (hin) {
+            uint32_t ka = 0, kin = 0;
+            #pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t lmA = low_mask(offA - 32 * j), dm = low_mask(offB - 32 * j) & ~lmA;
+                ka += __popc(B.w[4 * j + 3] & lmA); kin += __popc(B.w[4 * j + 3] & dm);
+            }
+            rda = blkA * OCC_ROWS - letters_before(B) + ka; rdb = rda + kin;
+        }
+    } else {
+        uint32_t ka, kb;
+        rank_in_blk(B, a & 127u, c, x0, x1, rca, ka);
+        rda = blkA * OCC_ROWS - letters_before(B) + ka;
+        load_blk(occ, blkB, B);
+        rank_in_blk(B, b & 127u, c, x0, x1, rcb, kb);
+        rdb = blkB * OCC_ROWS - letters_before(B) + kb;
+        nblk = 2;
+    }
+}
 
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
     for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -73,8 +154,8 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     const uint32_t tq = blockIdx.x * FUSED_THREADS + threadIdx.x;
     const bool live = tq < npat;
     const uint32_t q = live ? (ids ? ids[tq] : tq) : 0u;      // second pass (large cap): only the patterns listed in ids
-    uint32_t nF = 0, m = 0, L0 = 0, key = 0;
-    uint64_t base = 0;
+    uint32_t nF = 0, m = 0, L0 = 0, key = 0, win_lo = 0;
+    uint64_t base = 0, win = 0;                       // win: 2-bit codes of pattern characters [win_lo, win_lo + 32)
     bool ovf = false;
     unsigned long long sI = 0, sS = 0, sE = 0, sLF = 0, sBlk = 0;
     if (live) {
@@ -83,12 +164,17 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         m = len64 > 0xffffffffull ? 0u : (uint32_t)len64;
         L0 = m < k ? m : k;
         bool ok = m > 0;
-        for (uint32_t i = 0; i < m; ++i) {
-            uint32_t c = s_lut[__ldg(bytes + base + i)];
-            if (c > 3) { ok = false; c = 0; }
-            if (i >= m - L0) key |= c << (2 * (i - (m - L0)));
+        // the whole pattern is checked against the alphabet first (a rejected pattern yields 0 and no trace position);
+        // the window keeps the last 32 characters, which hold the seed key
+        for (uint32_t hi = m; hi > 0 && ok; ) {
+            const uint32_t lo = hi > 32 ? hi - 32 : 0;
+            uint64_t cw;
+            ok = fetch_codes(bytes + base + lo, hi - lo, s_lut, cw);
+            if (hi == m) { win = cw; win_lo = lo; }
+            hi = lo;
         }
         if (ok) {
+            key = (uint32_t)(win >> (2 * (m - L0 - win_lo))) & (uint32_t)((1ull << (2 * L0)) - 1);
             uint32_t a = __ldg(s_off[L0] + key), n0 = __ldg(s_off[L0] + key + 1) - a;
             if (n0 > cap) ovf = true;
             else { for (uint32_t j = 0; j < n0; ++j) LIST(j) = __ldg(s_iv[L0] + a + j); nF = n0; }
@@ -98,7 +184,13 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     const uint32_t mk = m < kc ? m : kc;
     uint32_t s = 0;
     for (; s < steps && nF && !ovf; ++s) {
-        const int c = (int)s_lut[__ldg(bytes + base + (m - L0 - s - 1))];
+        const uint32_t ci = m - L0 - s - 1;
+        if (ci < win_lo) {                                                // the next 32 characters to the left
+            const uint32_t lo = win_lo > 32 ? win_lo - 32 : 0;
+            fetch_codes(bytes + base + lo, win_lo - lo, s_lut, win);
+            win_lo = lo;
+        }
+        const int c = (int)((win >> (2 * (ci - win_lo))) & 3u);
         const uint32_t x0 = (c & 1) ? 0u : 0xffffffffu, x1 = (c & 2) ? 0u : 0xffffffffu;
         const uint32_t Cc = s_Cl[c];
         const bool beyond = STATS && (L0 + s >= kc);
@@ -107,17 +199,9 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         // ---- pass 1: F' = LF_c(F) in place, and the set of pile-0 ranges reached through the '#' rows of F
         for (uint32_t j = 0; j < nF && !ovf; ++j) {
             const uint2 iv = LIST(j);
-            const uint32_t a = iv.x, b = iv.y + 1;
-            const uint32_t blkA = a >> 7, blkB = b >> 7;
-            Blk B;
-            load_blk(ix.occ, blkA, B);
-            uint32_t rca, ka, rcb, kb;
-            rank_in_blk(B, a & 127u, c, x0, x1, rca, ka);
-            const uint32_t rda = blkA * OCC_ROWS - letters_before(B) + ka;
-            if (blkB != blkA) load_blk(ix.occ, blkB, B);
-            rank_in_blk(B, b & 127u, c, x0, x1, rcb, kb);
-            const uint32_t rdb = blkB * OCC_ROWS - letters_before(B) + kb;
-            if (STATS) { sLF += 1; sBlk += blkB != blkA ? 2 : 1; if (beyond) { sS += 1; sE += rdb - rda; } }
+            uint32_t rca, rcb, rda, rdb, nblk;
+            lf_range(ix.occ, iv.x, iv.y + 1, c, x0, x1, rca, rcb, rda, rdb, nblk);
+            if (STATS) { sLF += 1; sBlk += nblk; if (beyond) { sS += 1; sE += rdb - rda; } }
             if (rcb > rca) {
                 const uint32_t nlo = Cc + rca, nhi = Cc + rcb - 1;
                 if (nout && LIST(nout - 1).y + 1 == nlo) LIST(nout - 1).y = nhi;
@@ -149,16 +233,9 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
             uint32_t ndp = 0;
             for (uint32_t i = 0; i < ndol; ++i) {
                 const uint2 iv = DOL(i);
-                const uint32_t a = iv.x, b = iv.y + 1;
-                const uint32_t blkA = a >> 7, blkB = b >> 7;
-                Blk B;
-                load_blk(ix.occ, blkA, B);
-                uint32_t rca, ka, rcb, kb;
-                rank_in_blk(B, a & 127u, c, x0, x1, rca, ka);
-                const uint32_t rda = blkA * OCC_ROWS - letters_before(B) + ka;
-                if (blkB != blkA) load_blk(ix.occ, blkB, B);
-                rank_in_blk(B, b & 127u, c, x0, x1, rcb, kb);
-                if (STATS) { sLF += 1; sBlk += blkB != blkA ? 2 : 1; if (beyond) { sS += 1; sE += (blkB * OCC_ROWS - letters_before(B) + kb) - rda; } }
+                uint32_t rca, rcb, rda, rdb, nblk;
+                lf_range(ix.occ, iv.x, iv.y + 1, c, x0, x1, rca, rcb, rda, rdb, nblk);
+                if (STATS) { sLF += 1; sBlk += nblk; if (beyond) { sS += 1; sE += rdb - rda; } }
                 if (rcb > rca) {
                     const uint32_t nlo = Cc + rca, nhi = Cc + rcb - 1;
                     if (ndp && DOL(ndp - 1).y + 1 == nlo) DOL(ndp - 1).y = nhi;
@@ -225,12 +302,13 @@ void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, co
                          const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s) {
     if (npat == 0) return;
     const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
+    const unsigned grid = (npat + FUSED_THREADS - 1) / FUSED_THREADS;
     if (st) {
         CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
-        fused_search_kernel<true><<<(npat + FUSED_THREADS - 1) / FUSED_THREADS, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+        fused_search_kernel<true><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
     } else {
         CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        fused_search_kernel<false><<<(npat + FUSED_THREADS - 1) / FUSED_THREADS, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+        fused_search_kernel<false><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
     }
     CUDA_OK(cudaGetLastError());
 }

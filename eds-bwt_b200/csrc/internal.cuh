@@ -161,6 +161,8 @@ struct SeedView { const uint32_t* off[17]; const uint2* iv[17]; };
 struct StatsDev { unsigned long long I, S, E, L, O, lf_intervals, occ_blocks, overflow; };
 
 struct Workspace;   // engine.cu
+struct CsvScratch;  // csv.cu
+void free_csv_scratch(CsvScratch* c);
 struct SearchOut {
     DevBuf<uint32_t> counts; DevBuf<edsbwt_occ> occ; uint32_t npat = 0; uint64_t nocc = 0;
     DevBuf<uint32_t> alive; bool want_alive = false;    // alive[q] = longest suffix of pattern q whose frontier is non-empty
@@ -225,6 +227,9 @@ struct Index {
     Workspace* ws = nullptr;
     Pipe* pipe = nullptr;
     MoveTable* move = nullptr;          // built at open (opts.build_move) or by the first EDSBWT_LF_MOVE search
+    CsvScratch* csv = nullptr;          // scratch of the row-order sort and of the device csv formatter (csv.cu)
+    DevBuf<uint32_t> eof_inv;           // string -> rank of its '#' row (inverse of eof_flat); built by the first ordered search
+    int row_order = EDSBWT_ROWS_GROUPED;
     uint32_t move_a = 8;
     uint64_t l2_persist_bytes = 0;      // persisting-L2 carve-out granted for the Occ array
     std::shared_ptr<ResultPool> pool = std::make_shared<ResultPool>();
@@ -268,6 +273,9 @@ void launch_move_search(const IndexView& ix, const MoveView& mv, const SeedView&
                         const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const MoveOut& out, cudaStream_t s);
 void launch_move_locate(const IndexView& ix, const MoveView& mv, const uint2* plist, const uint32_t* occ_ofs, const uint2* staging,
                         uint32_t npat, uint64_t nocc, uint32_t pat_base, edsbwt_occ* out, StatsDev* st, cudaStream_t s);
+// csv.cu
+uint64_t order_rows_reference(Index& ix, SearchOut& out, const uint32_t* d_occ_ofs, uint32_t npat, cudaStream_t s);   // -> kernels launched
+uint64_t write_csv_device(Index& ix, const edsbwt_occ* d_occ, uint64_t nocc, uint32_t pat_add, FILE* f, cudaStream_t s, uint64_t* launches);   // -> bytes
 // builder.cu
 void build_index_files(const uint8_t* letters, const uint64_t* str_off, uint32_t nstr, const uint8_t* seg_first,
                        const std::string& out_base, int device);

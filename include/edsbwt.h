@@ -62,6 +62,10 @@ typedef struct {
 #define EDSBWT_LF_RANK      0   /* EDSBWTsearch:      LF by blocked rank                                      */
 #define EDSBWT_LF_MOVE      1   /* MOVE_EDSBWTSearch: LF by move table                                        */
 
+#define EDSBWT_ROWS_GROUPED   0   /* tuples grouped by ascending pattern, order inside a pattern unspecified        */
+#define EDSBWT_ROWS_REFERENCE 1   /* inside a pattern: the reference's csv order (EDSBWTsearch: round-major, then    */
+                                  /* eBWT position of the string-start row; MOVE: frontier order, ascending row)     */
+
 typedef struct {
     int32_t  seed_k;            /* -1 = auto (min(12, floor(log4 n) - 1)), 0 = no seed table                  */
     int32_t  locate_mode;       /* EDSBWT_LOCATE_SA / _WALK                                                   */
@@ -154,6 +158,18 @@ int  edsbwt_move_table_fetch(edsbwt_index* idx, uint32_t* p, uint32_t* q, uint32
  *     "#Pat\t$_i\tD[i]\tS_j\tS_j[r]\n" (move != 0: the MOVE header ending "S_j[r] \n",
  *     MOVE_EDSBWTSearch.cpp:55-59) and one row per tuple with pat + pat_base + 1. */
 int  edsbwt_write_csv(const char* path, const edsbwt_occ* occ, uint64_t nocc, uint32_t pat_base, int move, int append);
+/* Row order of every later search on this handle (EDSBWT_ROWS_*).  EDSBWT_ROWS_REFERENCE reproduces the order in which
+ * findMultipleDollarsBackward (EDSBWTsearch.cpp:349-603) reaches indices_of_dollars_in_interval (:1310-1332), so that the
+ * csv equals the reference's byte for byte without sorting; costs one segmented sort of the tuples on the device. */
+int  edsbwt_set_row_order(edsbwt_index* idx, int order);
+/* The csv rows of a device-resident result, formatted to decimal text ON THE DEVICE (one thread per row) and appended to /
+ * written at path (append = 0 writes the header first).  *bytes = bytes of row text written. */
+int  edsbwt_result_write_csv(edsbwt_index* idx, const edsbwt_result* res, const char* path, int move, int append, uint64_t* bytes);
+/* Whole job of the reference's constructor loop (:207-241) for HOST patterns: search + locate in reference row order,
+ * rows formatted on the device and appended to csv_path (which must already hold the header: edsbwt_write_csv with
+ * nocc = 0, append = 0), counts[npat] filled.  The batch is processed in chunks (edsbwt_set_chunk). */
+int  edsbwt_search_to_csv(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat,
+                          int lf_variant, uint32_t* counts, const char* csv_path, uint64_t* nocc);
 
 /* --- pattern file: std::getline loop of the constructor (:200-241): one pattern per '\n'-separated line,
  *     last line may lack '\n'.  *bytes / *off are malloc'ed (edsbwt_free). */
