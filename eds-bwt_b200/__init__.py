@@ -26,7 +26,7 @@ EXPORTS = [
     "edsbwt_build_from_eds", "edsbwt_build_from_collection", "edsbwt_gather_bench", "edsbwt_free",
     "edsbwt_strerror", "edsbwt_last_error", "edsbwt_version", "edsbwt_search_into", "edsbwt_host_alloc", "edsbwt_host_free",
     "edsbwt_set_chunk", "edsbwt_search_trace", "edsbwt_move_table_build", "edsbwt_move_table_fetch", "edsbwt_search_device_at", "edsbwt_gather_bench_ex",
-    "edsbwt_set_row_order", "edsbwt_result_write_csv", "edsbwt_search_to_csv",
+    "edsbwt_set_row_order", "edsbwt_result_write_csv", "edsbwt_search_to_csv", "edsbwt_string_check",
 ]
 
 
@@ -105,6 +105,7 @@ def lib():
         L.edsbwt_set_row_order.argtypes = [C.c_void_p, C.c_int]
         L.edsbwt_result_write_csv.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_uint64)]
         L.edsbwt_search_to_csv.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_char_p, C.POINTER(C.c_uint64)]
+        L.edsbwt_string_check.argtypes = [C.c_char_p, C.c_char_p]
         L.edsbwt_read_patterns.argtypes = [C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_uint32)]
         L.edsbwt_build_from_eds.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         L.edsbwt_build_from_collection.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_char_p, C.c_int]
@@ -327,6 +328,11 @@ def read_patterns(path):
     lib().edsbwt_free(b)
     lib().edsbwt_free(o)
     return data, off
+
+
+def string_check(in_path, out_path):
+    """stringCheck (stringCheck.cpp): bracket the non-degenerate stretches of an EDS text; host-only."""
+    _check(lib().edsbwt_string_check(os.fsencode(in_path), os.fsencode(out_path)))
 
 
 def build_from_eds(eds_path, out_base, device=0):

@@ -301,6 +301,45 @@ int edsbwt_read_patterns(const char* path, uint8_t** bytes, uint64_t** off, uint
     } catch (const Failure& f) { return f.code; }
 }
 
+// stringCheck (stringCheck.cpp:11-84): brackets every non-degenerate stretch of an EDS text, drops <...> comments and
+// refuses the character the tool chain reserves for the empty word (EMPTY_CHAR 'Z', Parameters.h:34).  Same decisions,
+// in the same order, as the reference's get()/peek() loop -- including its treatment of a trailing newline as a letter.
+int edsbwt_string_check(const char* in_path, const char* out_path) {
+    if (!in_path || !out_path) return EDSBWT_E_ARG;
+    const uint8_t EMPTY = 'Z';
+    try {
+        const std::vector<uint8_t> f = read_file(in_path);
+        std::vector<uint8_t> o; o.reserve(f.size() + f.size() / 8 + 16);
+        const size_t n = f.size();
+        auto reserved = [&]() -> int {
+            set_error("the input contains character %c, which is used by this tool to represent an empty string", EMPTY);
+            return EDSBWT_E_FORMAT;
+        };
+        size_t i = 0;
+        if (n) {
+            const uint8_t c = f[i++];
+            if (c == EMPTY) return reserved();
+            if (c != '{') o.push_back('{');
+            o.push_back(c);
+        }
+        while (i < n) {
+            uint8_t c = f[i++];
+            if (c == EMPTY) return reserved();
+            const int next = i < n ? (int)f[i] : -1;
+            if (c == '}' && next != '{' && next != -1) { o.push_back('}'); o.push_back('{'); }
+            else if (c != '}' && next == '{') { o.push_back(c); o.push_back('}'); }
+            else if (c == '<') {
+                while (i < n && c != '>') c = f[i++];            // the comment, through its closing '>' (the reference never ends without one)
+                if (i < n && f[i] == '{') o.push_back('}');
+            }
+            else if (next == -1 && c != '}') { o.push_back(c); o.push_back('}'); }
+            else o.push_back(c);
+        }
+        write_file(out_path, o.data(), o.size());
+        return EDSBWT_OK;
+    } catch (const Failure& f) { return f.code; }
+}
+
 int edsbwt_write_csv(const char* path, const edsbwt_occ* occ, uint64_t nocc, uint32_t pat_base, int move, int append) {
     if (!path || (nocc && !occ)) return EDSBWT_E_ARG;
     FILE* f = fopen(path, append ? "ab" : "wb");

@@ -184,6 +184,12 @@ int  edsbwt_build_from_eds(const char* eds_path, const char* out_base, int devic
 int  edsbwt_build_from_collection(const uint8_t* text, const uint64_t* str_off, uint32_t nstr,
                                   const uint8_t* seg_first, const char* out_base, int device);
 
+/* --- EDS text hygiene (replaces stringCheck, stringCheck.cpp:11-84): adds the curly brackets around the
+ *     non-degenerate stretches of in_path, removes <...> comments, writes out_path (the caller appends ".eds" like the
+ *     reference's main, :99-106).  EDSBWT_E_FORMAT when the text holds the reserved empty-word character 'Z'
+ *     (Parameters.h:34; the reference exits).  Host-only text processing, as in the reference. */
+int  edsbwt_string_check(const char* in_path, const char* out_path);
+
 /* --- roofline denominator: 64-byte random gather over buffer_bytes of HBM (kernel K7). */
 int  edsbwt_gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, double* gb_per_s);
 int  edsbwt_gather_bench_ex(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, int granule_bytes /* 32, 64, 128 */, double* gb_per_s);
