@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--keep", action="store_true")
+    ap.add_argument("--chunk", type=int, default=0, help="patterns per pipeline chunk of the host-buffer search (0 = library default)")
     return ap.parse_args()
 
 
@@ -309,16 +310,30 @@ def main():
     p_off = eb.pinned_empty(off.size, np.uint64); p_off[:] = off
     p_counts = eb.pinned_empty(args.npat, np.uint32)
     p_occ = eb.pinned_empty(int(nocc) + 1024, eb.OCC_DTYPE)
-    e2e_ms, d2h, e2e_launches = 0.0, 0, 0
+    if args.chunk:
+        idx.set_chunk(args.chunk)
+    # (a) the generic call: pattern bytes + uint64 offsets (variable-length batches, the reference's pattern file)
+    e2o_ms = 0.0
     for it in range(2 + args.steps):
         barrier()
         t1 = time.perf_counter()
         got = idx.search_into(p_data, p_off, p_counts, p_occ, locate=True)
         dt = (time.perf_counter() - t1) * 1e3
         if it >= 2:
+            e2o_ms += dt
+    counts_generic = np.array(p_counts, copy=True)
+    # (b) the call for equal-length batches (this workload): no offset array crosses PCIe -- the headline e2e
+    e2e_ms, d2h, e2e_launches = 0.0, 0, 0
+    for it in range(2 + args.steps):
+        barrier()
+        t1 = time.perf_counter()
+        got = idx.search_into_fixed(p_data, args.plen, p_counts, p_occ, locate=True)
+        dt = (time.perf_counter() - t1) * 1e3
+        if it >= 2:
             e2e_ms += dt
             d2h = p_counts.nbytes + got * eb.OCC_DTYPE.itemsize
-    h2d = data.nbytes + off.nbytes
+    h2d = data.nbytes
+    assert np.array_equal(counts_generic, np.asarray(p_counts)), "fixed-length and offset-array entry points disagree"
     gpu_counts = np.array(p_counts, copy=True)
     gpu_occ_total = int(got)
     # ---- multi-GPU result gather (north star: "only an NCCL/NVLink gather of per-pattern counts and occurrence buffers"):
@@ -351,6 +366,7 @@ def main():
     dev_ms_max = allmax(dev_ms)
     wall_ms_max = allmax(wall_ms)
     e2e_ms_max = allmax(e2e_ms)
+    e2o_ms_max = allmax(e2o_ms)
     gather_ms_max = allmax(gather_ms) if world > 1 else 0.0
     total_pat = args.npat * world * args.steps
     value = total_pat / (dev_ms_max * 1e-3)
@@ -391,7 +407,9 @@ def main():
             "wall_ms_per_step": wall_ms_max / args.steps,
             "occurrences_per_step": int(nocc),
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": e2e_ms_max / args.steps},
+                    "ms_per_step": e2e_ms_max / args.steps, "call": "edsbwt_search_into_fixed (pinned host buffers, equal-length batch)",
+                    "with_offset_array": {"value": total_pat / (e2o_ms_max * 1e-3), "ms_per_step": e2o_ms_max / args.steps,
+                                          "h2d_bytes_per_step": int(data.nbytes + off.nbytes), "call": "edsbwt_search_into"}},
             "gather": ({"value": total_pat / (gather_ms_max * 1e-3), "unit": UNIT, "ms_per_step": gather_ms_max / args.steps,
                         "bytes_per_step": int(gather_bytes), "what": "shard search + ncclAllGather(counts) + gather-v(tuples) to rank 0, device-timed"}
                        if world > 1 else None),

@@ -26,7 +26,7 @@ EXPORTS = [
     "edsbwt_build_from_eds", "edsbwt_build_from_collection", "edsbwt_gather_bench", "edsbwt_free",
     "edsbwt_strerror", "edsbwt_last_error", "edsbwt_version", "edsbwt_search_into", "edsbwt_host_alloc", "edsbwt_host_free",
     "edsbwt_set_chunk", "edsbwt_search_trace", "edsbwt_move_table_build", "edsbwt_move_table_fetch", "edsbwt_search_device_at", "edsbwt_gather_bench_ex",
-    "edsbwt_set_row_order", "edsbwt_result_write_csv", "edsbwt_search_to_csv", "edsbwt_string_check",
+    "edsbwt_set_row_order", "edsbwt_result_write_csv", "edsbwt_search_to_csv", "edsbwt_string_check", "edsbwt_search_into_fixed",
 ]
 
 
@@ -85,6 +85,8 @@ def lib():
                                     C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
         L.edsbwt_search_into.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
                                          C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.edsbwt_search_into_fixed.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
+                                               C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.edsbwt_search_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
         L.edsbwt_move_table_build.argtypes = [C.c_void_p]
         L.edsbwt_move_table_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
@@ -216,6 +218,14 @@ class Index:
         _check(lib().edsbwt_search_into(self._h, data.ctypes.data, off.ctypes.data, npat, int(locate), lf_variant,
                                         counts.ctypes.data, occ.ctypes.data if occ is not None else None,
                                         len(occ) if occ is not None else 0, C.byref(nocc)))
+        return nocc.value
+
+    def search_into_fixed(self, data, pat_len, counts, occ=None, locate=True, lf_variant=LF_RANK):
+        """Equal-length patterns back to back in `data` (uint8, ideally pinned); no offset array crosses PCIe."""
+        npat = len(data) // pat_len
+        nocc = C.c_uint64(0)
+        _check(lib().edsbwt_search_into_fixed(self._h, data.ctypes.data, pat_len, npat, int(locate), lf_variant, counts.ctypes.data,
+                                              occ.ctypes.data if occ is not None else None, len(occ) if occ is not None else 0, C.byref(nocc)))
         return nocc.value
 
     def set_row_order(self, reference=True):

@@ -941,7 +941,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     CUDA_OK(cudaStreamSynchronize(s));
     CUDA_OK(cudaGetLastError());
     StatsDev hs{};
-    CUDA_OK(cudaMemcpy(&hs, ws.d_stats, sizeof hs, cudaMemcpyDeviceToHost));
+    if (stats) CUDA_OK(cudaMemcpy(&hs, ws.d_stats, sizeof hs, cudaMemcpyDeviceToHost));
     float ms = 0; CUDA_OK(cudaEventElapsedTime(&ms, ws.ev0, ws.ev1));
     edsbwt_stats& ls = ix.last;
     ls = edsbwt_stats{};

@@ -120,6 +120,10 @@ int  edsbwt_search(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* 
  * Returns EDSBWT_E_NOSPACE when more than occ_cap occurrences exist (*nocc = number needed, counts valid). */
 int  edsbwt_search_into(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat,
                         int locate, int lf_variant, uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc);
+/* The same for a batch of EQUAL-LENGTH patterns stored back to back (a k-mer file such as sample/test/kmers.txt without
+ * its newlines): pattern i = pat_bytes[i*pat_len .. (i+1)*pat_len).  No offset array crosses PCIe. */
+int  edsbwt_search_into_fixed(edsbwt_index* idx, const uint8_t* pat_bytes, uint32_t pat_len, uint32_t npat,
+                              int locate, int lf_variant, uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc);
 /* Count-only search that also reports where each not-found pattern died, for the RECOVERBW=0 stderr line
  * "Pattern not found, interrupted in position <posSymb>" (EDSBWTsearch.cpp:714-717): interrupted[i] = that posSymb
  * (the frontier became empty when character posSymb-1 of the pattern was prepended), 0 = no such line (pattern

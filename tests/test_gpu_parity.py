@@ -233,6 +233,32 @@ def test_search_into_pipelined_chunks(eb, oracle_built, tmp_path):
         assert idx.search_into(data, off, counts2, occ2) == len(o_ref) and eb.occ_rows(occ2) == eb.occ_rows(o_ref)
 
 
+@pytest.mark.parametrize("plen", [1, 7, 16, 32, 33, 70])
+def test_search_into_fixed_length_batches(eb, tmp_path, plen):
+    """edsbwt_search_into_fixed (offsets generated on the device) == edsbwt_search_into with an explicit offset array;
+    odd lengths exercise the unaligned pattern-window paths of the fused kernel"""
+    rng = np.random.default_rng(300 + plen)
+    segs = E.random_eds(rng, n_seg=1200, max_var=4, max_len=6, p_empty=0.15, nondeg_len=(1, 60))
+    _, base = _index_files(tmp_path, segs)
+    pats = E.sample_patterns(rng, segs, 900, [plen])
+    assert all(len(p) == plen for p in pats)
+    data, off = eb.pack_patterns(pats)
+    with eb.Index(base) as idx:
+        c_ref, o_ref = idx.search(pats, locate=True)
+        exp = []
+        for i, p in enumerate(pats[:60]):
+            exp.append(len(E.brute_force(segs, p)))
+        assert c_ref[:60].tolist() == exp
+        for chunk in [0, 257, 1]:
+            idx.set_chunk(chunk)
+            counts = eb.pinned_empty(len(pats), np.uint32); counts[:] = 0xffffffff
+            occ = eb.pinned_empty(len(o_ref) + 3, eb.OCC_DTYPE)
+            p_data = eb.pinned_empty(data.size, np.uint8); p_data[:] = data
+            n = idx.search_into_fixed(p_data, plen, counts, occ, locate=True)
+            assert n == len(o_ref) and counts.tolist() == c_ref.tolist()
+            assert eb.occ_rows(occ[:n]) == eb.occ_rows(o_ref)
+
+
 # ---- count-only trace (RECOVERBW=0 stderr line) and the two drop-in executables ---------------------------------
 @pytest.mark.parametrize("name", golden_names())
 @pytest.mark.parametrize("seed_k,engine,cap", [(-1, 0, 0), (1, 0, 0), (4, 0, 4), (3, 1, 0)])
