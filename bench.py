@@ -57,6 +57,7 @@ def parse_args():
     ap.add_argument("--len", type=int, default=32, dest="plen")
     ap.add_argument("--seed-k", type=int, default=-1)
     ap.add_argument("--fused-cap", type=int, default=0)
+    ap.add_argument("--fused-cap2", type=int, default=0)
     ap.add_argument("--workdir", default=os.environ.get("EDSBWT_BENCH_DIR", ""))
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
@@ -109,7 +110,7 @@ def workload_name(args):
         args.mbp, args.npat, args.plen)
 
 
-NCU_CAPTURE = "profiles/r01_fused_ncu_full_v3.txt"      # ncu --set full of fused_search_kernel at the default workload (cfg4, k = 14)
+NCU_CAPTURE = "profiles/r01_fused_ncu_full_v4.txt"      # ncu --set full of fused_search_kernel at the default workload (cfg4, k = 14)
 
 
 def ncu_traffic(args, seed_k):
@@ -247,7 +248,7 @@ def main():
     if world > 1:
         dist.barrier()
     t0 = time.time()
-    idx = eb.Index(base, device=local_rank, seed_k=args.seed_k, verify=False, fused_cap=args.fused_cap)
+    idx = eb.Index(base, device=local_rank, seed_k=args.seed_k, verify=False, fused_cap=args.fused_cap, fused_cap2=args.fused_cap2)
     info = idx.info()
     log("rank %d: index open in %.1fs: n=%d nText=%d nSeg=%d seed_k=%d seed_intervals=%d device_bytes=%.2f GB" % (
         rank, time.time() - t0, info.n, info.n_text, info.n_seg, info.seed_k, info.seed_intervals, info.device_bytes / 1e9))

@@ -636,7 +636,7 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     CUDA_OK(cudaEventCreate(&ws.ev0)); CUDA_OK(cudaEventCreate(&ws.ev1)); CUDA_OK(cudaEventCreate(&ws.evk0)); CUDA_OK(cudaEventCreate(&ws.evk1));
     CUDA_OK(cudaEventCreate(&ws.evf0)); CUDA_OK(cudaEventCreate(&ws.evf1)); CUDA_OK(cudaEventCreate(&ws.evl0)); CUDA_OK(cudaEventCreate(&ws.evl1));
     ix.engine = o.engine == EDSBWT_ENGINE_LEVELSYNC ? EDSBWT_ENGINE_LEVELSYNC : EDSBWT_ENGINE_FUSED;
-    ix.fused_cap = o.fused_cap > 0 ? (uint32_t)o.fused_cap : 20u;
+    ix.fused_cap = o.fused_cap > 0 ? (uint32_t)o.fused_cap : 12u;       // 12 slots: 12 CTAs/SM (40 registers) and >= 60 KB of L1 left (A/B: profiles/r01_ab_keep_sort_sizes.txt)
     if (ix.fused_cap < 4) ix.fused_cap = 4;
     if (ix.fused_cap > FUSED_BIG_CAP) ix.fused_cap = FUSED_BIG_CAP;
     ix.fused_cap2 = o.fused_cap2 > 0 ? std::min<uint32_t>((uint32_t)o.fused_cap2, FUSED_BIG_CAP) : FUSED_BIG_CAP;
@@ -854,7 +854,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             FusedOut fo{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 1, ws.ovf_ids.p, d_alive};
             CUDA_OK(cudaEventRecord(ws.evf0, s));
             // MOVE: 16-byte frontier entries (b, e, b', e'), so half the slots fit the same shared memory
-            const uint32_t cap1 = move ? std::min<uint32_t>(ix.fused_cap, FUSED_BIG_CAP / 2) : ix.fused_cap;
+            const uint32_t cap1 = move ? std::min<uint32_t>(ix.fused_cap, 12u) : ix.fused_cap;     // MOVE: 24 KB per CTA, 8 CTAs/SM
             const uint32_t cap2 = move ? std::min<uint32_t>(ix.fused_cap2, FUSED_BIG_CAP / 2) : ix.fused_cap2;
             if (move) { MoveOut mo{fo.plist, fo.counts, fo.staging, fo.staging_cap, fo.cursor, fo.ovf_count, fo.ovf_ids};
                         launch_move_search(ix.view, ix.move->view, sv, k_eff, d_bytes, d_off, nullptr, npat, ix.lut.p, cap1, mo, s); }

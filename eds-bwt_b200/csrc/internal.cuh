@@ -125,6 +125,115 @@ __device__ __forceinline__ uint32_t occ_rank_eof(const uint4* __restrict__ occ, 
     }
     return r;
 }
+
+// ---- one-thread-per-pattern kernels (fused.cu, move.cu): whole 64-byte blocks in registers, 2-bit pattern windows
+struct Blk { uint32_t w[16]; };      // w[4j] = count of letter j before the block, w[4j+1] plane0, w[4j+2] plane1, w[4j+3] '#' mask of rows 32j..32j+31
+
+__device__ __forceinline__ void ld256(const void* p, uint32_t* r) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "l"(p));
+}
+__device__ __forceinline__ void load_blk(const uint4* __restrict__ occ, uint32_t blk, Blk& b) {
+    const uint4* p = occ + (size_t)blk * 4;
+    ld256(p, b.w); ld256(p + 2, b.w + 8);
+}
+// Pattern characters travel as 2-bit codes in a 64-bit window, 32 characters per fetch: n <= 32 bytes at p -> codes
+// (character i at bits 2i, 2i+1).  Returns false when a byte is not a letter of the index alphabet.  One or two 128-bit
+// loads when p is 16-byte aligned (every fixed-length batch whose length is a multiple of 16), 32-bit loads when 4-byte
+// aligned, byte loads otherwise.  Reading the aligned 16-byte / 4-byte unit that holds the last valid byte stays inside
+// the allocation (cudaMalloc granularity), so short tails need no special case.
+__device__ __forceinline__ bool fetch_codes(const uint8_t* __restrict__ p, uint32_t n, const uint8_t* s_lut, uint64_t& codes) {
+    uint32_t w[8];
+    const uint32_t al = (uint32_t)(uintptr_t)p & 15u;
+    if (al == 0) {
+        const uint4 a = __ldg((const uint4*)p);
+        const uint4 b = n > 16 ? __ldg((const uint4*)p + 1) : make_uint4(0, 0, 0, 0);
+        w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
+    } else if ((al & 3u) == 0) {
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) w[j] = 4u * j < n ? __ldg((const uint32_t*)p + j) : 0u;
+    } else {
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            uint32_t v = 0;
+            #pragma unroll
+            for (int t = 0; t < 4; ++t) if (4u * j + t < n) v |= (uint32_t)__ldg(p + 4 * j + t) << (8 * t);
+            w[j] = v;
+        }
+    }
+    uint32_t lo = 0, hi = 0, bad = 0;                 // branch-free: codes of all 32 slots, invalid slots masked afterwards
+    #pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const uint32_t c0 = s_lut[(w[i >> 2] >> (8 * (i & 3))) & 255u];
+        const uint32_t c1 = s_lut[(w[4 + (i >> 2)] >> (8 * (i & 3))) & 255u];
+        lo |= (c0 & 3u) << (2 * i); hi |= (c1 & 3u) << (2 * i);
+        bad |= (c0 > 3u ? 1u : 0u) << i; bad |= (c1 > 3u ? 1u : 0u) << (16 + i);
+    }
+    const uint64_t cw = ((uint64_t)hi << 32) | lo;
+    codes = n >= 32 ? cw : cw & ((1ull << (2 * n)) - 1);
+    return (bad & (n >= 32 ? 0xffffffffu : ((1u << n) - 1u))) == 0;
+}
+// rank of letter c (x0/x1 = plane inversion masks of c) and number of '#' in rows [0,off) of the block, off in [0,128)
+__device__ __forceinline__ void rank_in_blk(const Blk& b, uint32_t off, int c, uint32_t x0, uint32_t x1, uint32_t& rc, uint32_t& nmk) {
+    uint32_t r = c == 0 ? b.w[0] : c == 1 ? b.w[4] : c == 2 ? b.w[8] : b.w[12];
+    uint32_t k = 0;
+    #pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        int below = (int)off - 32 * j;
+        uint32_t lm = below <= 0 ? 0u : (below >= 32 ? 0xffffffffu : ((1u << below) - 1u));
+        uint32_t mk = b.w[4 * j + 3] & lm;
+        r += __popc((b.w[4 * j + 1] ^ x0) & (b.w[4 * j + 2] ^ x1) & ~b.w[4 * j + 3] & lm);
+        k += __popc(mk);
+    }
+    rc = r; nmk = k;
+}
+__device__ __forceinline__ uint32_t letters_before(const Blk& b) { return b.w[0] + b.w[4] + b.w[8] + b.w[12]; }
+// mask of the bits below position `below` of a 32-bit word, below clamped to [0, 32] (shl.b32 clamps its shift amount)
+__device__ __forceinline__ uint32_t low_mask(int below) {
+    uint32_t r; const int bb = below < 0 ? 0 : below;
+    asm("shl.b32 %0, 1, %1;" : "=r"(r) : "r"(bb));
+    return r - 1u;
+}
+// LF of the row range [a, b) by letter c: rca / rcb = rank of c before a / b; rda / rdb = rank of '#' before a / b (both 0
+// when the range holds no '#' and lies inside one block).  After the seed lookup nearly every range is one or a few rows
+// inside ONE block: that case is a single sweep over the four 32-row words (letter mask computed once, '#' ranks only
+// when a '#' is present).  nblk = Occ blocks fetched (1 or 2).
+__device__ __forceinline__ void lf_range(const uint4* __restrict__ occ, uint32_t a, uint32_t b, int c, uint32_t x0, uint32_t x1,
+                                         uint32_t& rca, uint32_t& rcb, uint32_t& rda, uint32_t& rdb, uint32_t& nblk) {
+    const uint32_t blkA = a >> 7, blkB = b >> 7;
+    Blk B;
+    load_blk(occ, blkA, B);
+    if (blkA == blkB) {
+        const int offA = (int)(a & 127u), offB = (int)(b & 127u);
+        uint32_t r = c == 0 ? B.w[0] : c == 1 ? B.w[4] : c == 2 ? B.w[8] : B.w[12];
+        uint32_t in = 0, hin = 0;
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t lmA = low_mask(offA - 32 * j), dm = low_mask(offB - 32 * j) & ~lmA;
+            const uint32_t M = (B.w[4 * j + 1] ^ x0) & (B.w[4 * j + 2] ^ x1) & ~B.w[4 * j + 3];
+            r += __popc(M & lmA); in += __popc(M & dm); hin |= B.w[4 * j + 3] & dm;
+        }
+        rca = r; rcb = r + in; rda = rdb = 0; nblk = 1;
+        if (hin) {
+            uint32_t ka = 0, kin = 0;
+            #pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t lmA = low_mask(offA - 32 * j), dm = low_mask(offB - 32 * j) & ~lmA;
+                ka += __popc(B.w[4 * j + 3] & lmA); kin += __popc(B.w[4 * j + 3] & dm);
+            }
+            rda = blkA * OCC_ROWS - letters_before(B) + ka; rdb = rda + kin;
+        }
+    } else {
+        uint32_t ka, kb;
+        rank_in_blk(B, a & 127u, c, x0, x1, rca, ka);
+        rda = blkA * OCC_ROWS - letters_before(B) + ka;
+        load_blk(occ, blkB, B);
+        rank_in_blk(B, b & 127u, c, x0, x1, rcb, kb);
+        rdb = blkB * OCC_ROWS - letters_before(B) + kb;
+        nblk = 2;
+    }
+}
+
 #endif
 
 // ---------------------------------------------------------------------------------------------------
@@ -236,7 +345,7 @@ struct Index {
     uint32_t chunk_patterns = 1u << 21;     // patterns per pipeline chunk of the host-buffer searches
     edsbwt_stats last{};
     int collect_counters = 0; uint32_t canonical_k = 12;
-    int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 20, fused_cap2 = FUSED_BIG_CAP;
+    int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 12, fused_cap2 = FUSED_BIG_CAP;
     uint64_t device_bytes() const;
     ~Index();
 };

@@ -223,6 +223,22 @@ __device__ __forceinline__ void rank2(const uint4* __restrict__ occL, uint32_t p
     rd = occ_rank_eof(occL, pos);
 }
 
+// the two rank pairs of an interval, (rank_c, rank_#) of L'[0, posA) and L'[0, posB), posA <= posB: the run heads b' and
+// e' + 1 nearly always share one 64-byte block of the L' structure, which is then fetched once (two 256-bit loads)
+__device__ __forceinline__ void rank2_pair(const uint4* __restrict__ occL, uint32_t posA, uint32_t posB, int c,
+                                           uint32_t& kb, uint32_t& l, uint32_t& ke1, uint32_t& u) {
+    const uint32_t x0 = (c & 1) ? 0u : 0xffffffffu, x1 = (c & 2) ? 0u : 0xffffffffu;
+    const uint32_t blkA = posA >> 7, blkB = posB >> 7;
+    Blk B;
+    load_blk(occL, blkA, B);
+    uint32_t ka, kk;
+    rank_in_blk(B, posA & 127u, c, x0, x1, kb, ka);
+    l = blkA * OCC_ROWS - letters_before(B) + ka;
+    if (blkB != blkA) load_blk(occL, blkB, B);
+    rank_in_blk(B, posB & 127u, c, x0, x1, ke1, kk);
+    u = blkB * OCC_ROWS - letters_before(B) + kk;
+}
+
 // One backward step of one interval by move-LF (updateSingleInterval, MOVE_EDSBWTSearch.cpp:424-510).
 // in: (b, e, b_, e_) and the ranks kb = rank_c(L', b_), ke1 = rank_c(L', e_ + 1).  false: no row of the interval holds c.
 __device__ __forceinline__ bool move_lf(const MoveView& mv, int c, uint32_t kb, uint32_t ke1, uint32_t& b, uint32_t& e, uint32_t& b_, uint32_t& e_) {
@@ -242,7 +258,8 @@ __device__ __forceinline__ bool move_lf(const MoveView& mv, int c, uint32_t kb, 
 
 }  // namespace
 
-__global__ void __launch_bounds__(MOVE_THREADS, 4)
+template <int MINB>
+__global__ void __launch_bounds__(MOVE_THREADS, MINB)
 move_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant__ MoveView mv, const __grid_constant__ SeedView sv, uint32_t k, const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ poff,
                    const uint32_t* __restrict__ ids, uint32_t npat, const uint8_t* __restrict__ lut, uint32_t cap, MoveOut out) {
     extern __shared__ uint4 m_list[];                 // [cap][MOVE_THREADS] of (b, e, b', e')
@@ -254,8 +271,8 @@ move_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant__
     const uint32_t tq = blockIdx.x * MOVE_THREADS + threadIdx.x;
     const bool live = tq < npat;
     const uint32_t q = live ? (ids ? ids[tq] : tq) : 0u;
-    uint32_t nF = 0, m = 0, L0 = 0;
-    uint64_t base = 0;
+    uint32_t nF = 0, m = 0, L0 = 0, win_lo = 0;
+    uint64_t base = 0, win = 0;                       // win: 2-bit codes of pattern characters [win_lo, win_lo + 32)
     bool ovf = false;
     if (live) {
         base = poff[q];
@@ -263,13 +280,15 @@ move_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant__
         m = len64 > 0xffffffffull ? 0u : (uint32_t)len64;
         L0 = m < k ? m : k;
         bool ok = m > 0;
-        uint32_t key = 0;
-        for (uint32_t i = 0; i < m; ++i) {
-            uint32_t c = s_lut[__ldg(bytes + base + i)];
-            if (c > 3) { ok = false; c = 0; }
-            if (i >= m - L0) key |= c << (2 * (i - (m - L0)));
+        for (uint32_t hi = m; hi > 0 && ok; ) {      // alphabet check of the whole pattern; the window keeps its last 32 characters
+            const uint32_t lo = hi > 32 ? hi - 32 : 0;
+            uint64_t cw;
+            ok = fetch_codes(bytes + base + lo, hi - lo, s_lut, cw);
+            if (hi == m) { win = cw; win_lo = lo; }
+            hi = lo;
         }
         if (ok) {
+            const uint32_t key = (uint32_t)(win >> (2 * (m - L0 - win_lo))) & (uint32_t)((1ull << (2 * L0)) - 1);
             // the first min(m,k) steps come from the seed table (rows); the companion input intervals are looked up
             uint32_t a = __ldg(sv.off[L0] + key), n0 = __ldg(sv.off[L0] + key + 1) - a;
             if (n0 > cap) ovf = true;
@@ -278,14 +297,19 @@ move_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant__
     }
     const uint32_t steps = m - L0;
     for (uint32_t s = 0; s < steps && nF && !ovf; ++s) {
-        const int c = (int)s_lut[__ldg(bytes + base + (m - L0 - s - 1))];
+        const uint32_t ci = m - L0 - s - 1;
+        if (ci < win_lo) {
+            const uint32_t lo = win_lo > 32 ? win_lo - 32 : 0;
+            fetch_codes(bytes + base + lo, win_lo - lo, s_lut, win);
+            win_lo = lo;
+        }
+        const int c = (int)((win >> (2 * (ci - win_lo))) & 3u);
         uint32_t nout = 0, ndol = 0;
         // ---- pass 1: link (the '#' runs among runs b'..e' of every interval) + F' = LF_c(F) in place
         for (uint32_t j = 0; j < nF && !ovf; ++j) {
             uint4 iv = LIST(j);
             uint32_t kb, l, ke1, u;
-            rank2(mv.occL, iv.z, c, kb, l);                        // dollars_in_interval: _RS_L_.rank('#', b') .. rank('#', e'+1), :609-610
-            rank2(mv.occL, iv.w + 1, c, ke1, u);
+            rank2_pair(mv.occL, iv.z, iv.w + 1, c, kb, l, ke1, u);  // dollars_in_interval: _RS_L_.rank('#', b') .. rank('#', e'+1), :609-610
             if (move_lf(mv, c, kb, ke1, iv.x, iv.y, iv.z, iv.w)) {
                 if (nout && LIST(nout - 1).y + 1 == iv.x) { uint4 t = LIST(nout - 1); t.y = iv.y; t.w = iv.w; LIST(nout - 1) = t; }
                 else { LIST(nout) = iv; ++nout; }
@@ -318,8 +342,7 @@ move_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant__
                 uint4 iv = DOL(i);
                 iv.z = __ldg(mv.row_run0 + iv.x); iv.w = __ldg(mv.row_run0 + iv.y);
                 uint32_t kb, l, ke1, u;
-                rank2(mv.occL, iv.z, c, kb, l);
-                rank2(mv.occL, iv.w + 1, c, ke1, u);
+                rank2_pair(mv.occL, iv.z, iv.w + 1, c, kb, l, ke1, u);
                 if (move_lf(mv, c, kb, ke1, iv.x, iv.y, iv.z, iv.w)) {
                     if (ndp && DOL(ndp - 1).y + 1 == iv.x) { uint4 t = DOL(ndp - 1); t.y = iv.y; t.w = iv.w; DOL(ndp - 1) = t; }
                     else { DOL(ndp) = iv; ++ndp; }
@@ -401,8 +424,13 @@ void launch_move_search(const IndexView& ix, const MoveView& mv, const SeedView&
                         const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const MoveOut& out, cudaStream_t s) {
     if (npat == 0) return;
     const size_t smem = (size_t)cap * MOVE_THREADS * sizeof(uint4);
-    CUDA_OK(cudaFuncSetAttribute(move_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    move_search_kernel<<<(npat + MOVE_THREADS - 1) / MOVE_THREADS, MOVE_THREADS, smem, s>>>(ix, mv, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out);
+    if (cap <= 14) {                   // first pass: 64 registers, 8 CTAs per SM (cfg3: 2.07 -> 1.56 ms against 4 CTAs at 72 registers)
+        CUDA_OK(cudaFuncSetAttribute(move_search_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        move_search_kernel<8><<<(npat + MOVE_THREADS - 1) / MOVE_THREADS, MOVE_THREADS, smem, s>>>(ix, mv, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out);
+    } else {
+        CUDA_OK(cudaFuncSetAttribute(move_search_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        move_search_kernel<4><<<(npat + MOVE_THREADS - 1) / MOVE_THREADS, MOVE_THREADS, smem, s>>>(ix, mv, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out);
+    }
     CUDA_OK(cudaGetLastError());
 }
 void launch_move_locate(const IndexView& ix, const MoveView& mv, const uint2* plist, const uint32_t* occ_ofs, const uint2* staging,

@@ -53,6 +53,8 @@ def main():
     ap.add_argument("--skip-cfg3", action="store_true")
     ap.add_argument("--skip-cfg5", action="store_true")
     ap.add_argument("--lens", default="8,16,32,64,128,256")
+    ap.add_argument("--fused-cap", type=int, default=0)
+    ap.add_argument("--cfg4-move", action="store_true", help="also time MOVE_EDSBWTSearch on the cfg4 index (m = 32)")
     args = ap.parse_args()
     import torch
     eb = importlib.import_module("eds-bwt_b200")
@@ -67,7 +69,7 @@ def main():
         pats = synth.sample_patterns(col, 1000000, 32, seed=33)
         data, off = synth.pack_fixed(pats)
         t0 = time.time()
-        with eb.Index(base, build_move=True) as idx:
+        with eb.Index(base, build_move=True, fused_cap=args.fused_cap) as idx:
             info = idx.info()
             log("cfg3 index: n=%d nText=%d nSeg=%d seed_k=%d move runs=%d intervals=%d (open %.2fs)" % (
                 info.n, info.n_text, info.n_seg, info.seed_k, info.move_runs, info.move_intervals, time.time() - t0))
@@ -81,6 +83,27 @@ def main():
             same = bool(np.array_equal(res["EDSBWTsearch"][0], res["MOVE_EDSBWTSearch"][0]) and res["EDSBWTsearch"][1] == res["MOVE_EDSBWTSearch"][1])
             print(json.dumps({"config": "cfg3", "variants_identical": same, "occurrences": len(res["EDSBWTsearch"][1])}), flush=True)
             del res
+
+    if args.cfg4_move:
+        base = os.path.join(work, "cfg4_%g" % args.mbp)
+        col = synth.chromosome_eds(args.mbp, seed=4)
+        if not os.path.exists(base + ".done"):
+            eb.build_from_collection(col.letters, col.str_off, col.seg_first, base, device=0)
+            open(base + ".done", "w").close()
+        pats = synth.sample_patterns(col, args.npat, 32, seed=44)
+        data, off = synth.pack_fixed(pats)
+        del pats, col
+        t0 = time.time()
+        with eb.Index(base, verify=False, build_move=True, fused_cap=args.fused_cap) as idx:
+            info = idx.info()
+            log("cfg4 index + move table: %.1fs, runs=%d intervals=%d rounds=%d device_bytes=%.2f GB" % (
+                time.time() - t0, info.move_runs, info.move_intervals, info.move_rounds, info.device_bytes / 1e9))
+            for name, lf in (("EDSBWTsearch", eb.LF_RANK), ("MOVE_EDSBWTSearch", eb.LF_MOVE)):
+                r, _, _ = run(idx, torch, data, off, 32, True, lf, args.steps)
+                print(json.dumps({"config": "cfg4 (%g Mbp, n=%d), %d length-32 patterns, locate" % (args.mbp, info.n, args.npat), "variant": name,
+                                  "seed_k": info.seed_k, "move_runs": info.move_runs, "move_intervals": info.move_intervals,
+                                  "device_bytes": info.device_bytes, **r}), flush=True)
+        del data, off
 
     if not args.skip_cfg5:
         base = os.path.join(work, "cfg4_%g" % args.mbp)
