@@ -189,6 +189,28 @@ def cpu_reference_run(base, pats, seconds, cores, note):
         shutil.rmtree(d, ignore_errors=True)
 
 
+_ORIG_AFFINITY = None
+
+
+def bind_to_gpu_numa_node(device):
+    """Pin this process to the CPUs next to its GPU (NVML's ideal affinity) before any pinned buffer is allocated, so that
+    the host side of the e2e copies lives on the GPU's own NUMA node / PCIe root (matters with 8 ranks on one box)."""
+    global _ORIG_AFFINITY
+    try:
+        import pynvml
+        _ORIG_AFFINITY = os.sched_getaffinity(0)
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(device)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = [64 * w + b for w in range(words) for b in range(64) if (mask[w] >> b) & 1]
+        if cpus:
+            os.sched_setaffinity(0, set(cpus) & os.sched_getaffinity(0) or set(cpus))
+            log("device %d: bound to %d CPUs (%d..%d)" % (device, len(cpus), cpus[0], cpus[-1]))
+    except Exception as e:      # noqa
+        log("no NUMA binding:", e)
+
+
 # ----------------------------------------------------------------------------------------------------
 _REAL_STDOUT = None
 
@@ -235,6 +257,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product has no CPU path (use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local_rank)
+    bind_to_gpu_numa_node(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     eb.lib()
@@ -431,6 +454,8 @@ def main():
     idx.close()
     if rank == 0 and world == 1 and not args.no_cpu:
         try:
+            if _ORIG_AFFINITY:
+                os.sched_setaffinity(0, _ORIG_AFFINITY)          # the CPU baseline gets every host core again
             cb = cpu_reference_run(base, pats, args.cpu_seconds, os.cpu_count() or 1, "locate (RECOVERBW=1)")
             ref_counts, nref = cb.pop("counts"), cb.pop("n")
             if len(ref_counts) == nref:         # full-size parity check on the sample: the reference's own counts
