@@ -121,11 +121,14 @@ __global__ void sa_walk_kernel(const __grid_constant__ IndexView ix, uint2* __re
     }
     slen[w] = d;
 }
-__global__ void sa_offset_kernel(uint32_t n_text, uint32_t n, uint2* __restrict__ sa, const uint32_t* __restrict__ slen) {
+// final table: one 16-byte record per row = everything a csv row needs, (string, offset in string, segment, index in segment)
+__global__ void sa_offset_kernel(uint32_t n_text, uint32_t n, const uint2* __restrict__ sa, const uint32_t* __restrict__ slen,
+                                 const uint2* __restrict__ str_info, uint4* __restrict__ sa4) {
     uint32_t row = n_text + blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n) return;
-    uint2 v = sa[row];
-    sa[row] = make_uint2(v.x, slen[v.x] - v.y);
+    const uint2 v = sa[row];
+    const uint2 si = __ldg(str_info + v.x);
+    sa4[row] = make_uint4(v.x, slen[v.x] - v.y, si.x, si.y);
 }
 // link_rec[r] for the r-th end-marker row of the eBWT (EOF_ID order): everything link() derives from it
 // (preceding_dollars_finder :1287-1307 + the empty-string closure :1255); str_info[w] = (segment, index in segment)
@@ -398,8 +401,17 @@ __global__ void locate_kernel(const __grid_constant__ IndexView ix, const uint2*
                               uint32_t npat, uint64_t nocc, uint32_t pat_base, edsbwt_occ* __restrict__ out, StatsDev* __restrict__ st) {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t steps = 0;
+    // the patterns of this CTA's occurrences form a narrow range: two searches over the whole offset array per CTA, then
+    // every thread searches inside that range (a few hundred entries, L1-resident) instead of 24 dependent L2 probes each
+    __shared__ uint32_t s_q[2];
+    if (threadIdx.x < 2) {
+        const uint64_t tt = threadIdx.x == 0 ? (uint64_t)blockIdx.x * blockDim.x : min((uint64_t)blockIdx.x * blockDim.x + blockDim.x - 1, nocc - 1);
+        s_q[threadIdx.x] = upper_bound_u32(occ_ofs, npat + 1, (uint32_t)tt) - 1;
+    }
+    __syncthreads();
     if (t < nocc) {
-        uint32_t q = upper_bound_u32(occ_ofs, npat + 1, (uint32_t)t) - 1;
+        const uint32_t q0 = s_q[0];
+        uint32_t q = q0 + upper_bound_u32(occ_ofs + q0, s_q[1] - q0 + 1, (uint32_t)t) - 1;
         uint32_t r = (uint32_t)t - __ldg(occ_ofs + q);
         uint2 pl = __ldg(plist + q);
         uint32_t row = 0;
@@ -419,8 +431,10 @@ __global__ void locate_kernel(const __grid_constant__ IndexView ix, const uint2*
                 ++off;
             }
             w = __ldg(ix.eof_flat + occ_rank_eof(ix.occ, row));
-        } else { uint2 v = __ldg(ix.sa + row); w = v.x; off = v.y; }
-        uint2 si = __ldg(ix.str_info + w);
+        }
+        uint2 si;
+        if (WALK) si = __ldg(ix.str_info + w);
+        else { const uint4 v = __ldg(ix.sa4 + row); w = v.x; off = v.y; si = make_uint2(v.z, v.w); }      // ONE 16-byte gather per occurrence
         edsbwt_occ o; o.pat = q + pat_base; o.str = w; o.seg = si.x; o.idx_in_seg = si.y; o.off = off;
         out[t] = o;
         steps = off + 1;
@@ -465,7 +479,7 @@ Index::~Index() {
     if (stream) cudaStreamDestroy(stream);
 }
 uint64_t Index::device_bytes() const {
-    uint64_t b = occ.bytes() + eof_flat.bytes() + eof_inv.bytes() + str_seg.bytes() + seg_first.bytes() + seg_low.bytes() + sa.bytes() + link_rec.bytes() + str_info.bytes();
+    uint64_t b = occ.bytes() + eof_flat.bytes() + eof_inv.bytes() + str_seg.bytes() + seg_first.bytes() + seg_low.bytes() + sa4.bytes() + link_rec.bytes() + str_info.bytes();
     for (SeedLevel* s : seed) if (s) b += s->off.bytes() + s->iv.bytes();
     if (move) b += move->bytes();
     return b;
@@ -717,13 +731,15 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     // ---- SA table
     ix.locate_mode = o.locate_mode == EDSBWT_LOCATE_WALK ? EDSBWT_LOCATE_WALK : EDSBWT_LOCATE_SA;
     if (ix.locate_mode == EDSBWT_LOCATE_SA) {
-        ix.sa.ensure((size_t)h.n + 1);
+        DevBuf<uint2> sa; sa.ensure((size_t)h.n + 1);                 // (string, distance to the end): build scratch
+        ix.sa4.ensure((size_t)h.n + 1);
         DevBuf<uint32_t> slen; slen.ensure(h.n_text + 1);
-        CUDA_OK(cudaMemsetAsync(ix.sa.p, 0xff, (size_t)h.n * 8, s));
-        sa_walk_kernel<<<grid_for(h.n_text, 128), 128, 0, s>>>(v, ix.sa.p, slen.p);
-        if (h.n > h.n_text) sa_offset_kernel<<<grid_for(h.n - h.n_text, 256), 256, 0, s>>>(h.n_text, h.n, ix.sa.p, slen.p);
+        CUDA_OK(cudaMemsetAsync(sa.p, 0xff, (size_t)h.n * 8, s));
+        CUDA_OK(cudaMemsetAsync(ix.sa4.p, 0xff, (size_t)h.n_text * 16, s));     // end-marker rows are never located
+        sa_walk_kernel<<<grid_for(h.n_text, 128), 128, 0, s>>>(v, sa.p, slen.p);
+        if (h.n > h.n_text) sa_offset_kernel<<<grid_for(h.n - h.n_text, 256), 256, 0, s>>>(h.n_text, h.n, sa.p, slen.p, ix.str_info.p, ix.sa4.p);
         CUDA_OK(cudaStreamSynchronize(s));
-        v.sa = ix.sa.p;
+        v.sa4 = ix.sa4.p;
     }
     CUDA_OK(cudaStreamSynchronize(s));
     // ---- seed table

@@ -69,7 +69,7 @@ struct IndexView {
     const uint32_t* str_seg;     // string -> 1-based segment        (rank on .bitvector)
     const uint32_t* seg_first;   // [1..n_seg+1] first string of segment (select), [n_seg+1] = n_text
     const uint32_t* seg_low;     // [1..n_seg] lowest segment reachable from s through segments holding ""
-    const uint2*    sa;          // row -> (string, offset in string); null in WALK mode
+    const uint4*    sa4;         // row -> (string, offset in string, segment, index in segment); null in WALK mode
     const uint2*    link_rec;    // per end-marker rank r (order of '#' rows in the eBWT): pile-0 row range [x,y] of all
                                  // strings of the segments reachable from string eof_flat[r] (x > y: none) -- the whole
                                  // preceding_dollars_finder + empty-string closure of link() in one 8-byte gather
@@ -326,7 +326,8 @@ struct Index {
     HostIndex host;       // ebwt bytes dropped after upload
     DevBuf<uint4> occ;
     DevBuf<uint32_t> eof_flat, str_seg, seg_first, seg_low;
-    DevBuf<uint2> sa, link_rec, str_info;
+    DevBuf<uint4> sa4;
+    DevBuf<uint2> link_rec, str_info;
     DevBuf<uint8_t> lut;             // 256-byte byte -> code table on the device (0..3 letters, 4 end-marker, 255 other)
     IndexView view{};
     uint32_t seed_k = 0;
