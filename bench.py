@@ -49,7 +49,7 @@ def log(*a):
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mbp", type=float, default=float(os.environ.get("EDSBWT_BENCH_MBP", "250")))
@@ -70,36 +70,64 @@ def parse_args():
 # clocks
 # ----------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    """Samples nvidia-smi SM clocks and throttle reasons while the timed region runs."""
+    """Samples SM clocks and throttle reasons while the timed region runs: NVML every 2 ms (the timed region of the default
+    run lasts tens of milliseconds), nvidia-smi as the fallback."""
 
     def __init__(self, device):
         super().__init__(daemon=True)
         self.device = device
         self.samples, self.reasons, self.max_mhz = [], set(), None
         self._halt = threading.Event()
+        self.how = "nvml"
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(device)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._nv = None
+            self.how = "nvidia-smi"
 
-    def run(self):
+    def _nvml_once(self):
+        nv = self._nv
+        self.samples.append(float(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+        try:
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+        except Exception:
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+        for nm, bit in (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4)):
+            if r & bit:
+                self.reasons.add(nm)
+
+    def _smi_once(self):
         q = "clocks.sm,clocks.max.sm,clocks_throttle_reasons.hw_slowdown,clocks_throttle_reasons.hw_thermal_slowdown," \
             "clocks_throttle_reasons.sw_thermal_slowdown,clocks_throttle_reasons.sw_power_cap"
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        out = subprocess.run(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                             capture_output=True, text=True, timeout=5).stdout.strip().split(",")
+        self.samples.append(float(out[0]))
+        self.max_mhz = float(out[1])
+        for nm, v in zip(names, out[2:]):
+            if v.strip().lower() == "active":
+                self.reasons.add(nm)
+
+    def run(self):
         while not self._halt.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip().split(",")
-                self.samples.append(float(out[0]))
-                self.max_mhz = float(out[1])
-                for nm, v in zip(names, out[2:]):
-                    if v.strip().lower() == "active":
-                        self.reasons.add(nm)
+                if self._nv is not None:
+                    self._nvml_once()
+                else:
+                    self._smi_once()
             except Exception:
                 pass
-            self._halt.wait(0.05)
+            self._halt.wait(0.002 if self._nv is not None else 0.05)
 
     def stop(self):
         self._halt.set()
         self.join(timeout=6)
         med = float(np.median(self.samples)) if self.samples else None
-        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples), "how": self.how}
 
 
 # ----------------------------------------------------------------------------------------------------
@@ -141,7 +169,7 @@ def build_index_files(eb, synth, args, base):
     return col
 
 
-def cpu_reference_run(base, pats, seconds, cores, note):
+def cpu_reference_run(base, pats, seconds, cores, note, per=None):
     """Times the reference's own CPU search on `cores` independent processes (it is single-threaded:
     mainEDS-BWT.cpp:66), each on its own shard of a bounded sample.  -> dict for cpu_baseline."""
     from oracle import run as R
@@ -177,14 +205,15 @@ def cpu_reference_run(base, pats, seconds, cores, note):
                     took.append(json.loads(out.strip().splitlines()[-1])["seconds"])
             return time.time() - t0, max(took), found
         # calibrate with one pattern per core, then size the sample for ~`seconds` of search time
-        wall1, took1, _ = run_shards(1)
-        per = int(max(1, min(len(pats) // cores, seconds / max(took1, 1e-3))))
+        if per is None:
+            wall1, took1, _ = run_shards(1)
+            per = int(max(1, min(len(pats) // cores, seconds / max(took1, 1e-3))))
         wall, took, found = run_shards(per)
         val = per * cores / max(took, 1e-9)
         return {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
                 "sample": "%d patterns (%d per process x %d processes) of the same batch, %s; max 'bs took' %.2fs (index load excluded, wall %.1fs)" % (
                     per * cores, per, cores, note, took, wall),
-                "search_seconds": took, "counts": found, "n": per * cores}
+                "search_seconds": took, "counts": found, "n": per * cores, "per": per}
     finally:
         shutil.rmtree(d, ignore_errors=True)
 
@@ -457,7 +486,7 @@ def main():
             if _ORIG_AFFINITY:
                 os.sched_setaffinity(0, _ORIG_AFFINITY)          # the CPU baseline gets every host core again
             cb = cpu_reference_run(base, pats, args.cpu_seconds, os.cpu_count() or 1, "locate (RECOVERBW=1)")
-            ref_counts, nref = cb.pop("counts"), cb.pop("n")
+            ref_counts, nref = cb.pop("counts"), cb.pop("n"); cb.pop("per", None)
             if len(ref_counts) == nref:         # full-size parity check on the sample: the reference's own counts
                 cb["parity_vs_gpu"] = "ok" if ref_counts == gpu_counts[:nref].tolist() else "MISMATCH"
             out["cpu_baseline"] = cb
@@ -489,8 +518,12 @@ def reference_arm(args, eb, synth, workdir, base, done_flag):
     cores = os.cpu_count() or 1
     vals, secs = [], []
     base_info = None
+    # bounded: the whole --steps K --warmup W run gets ~150 s of search time; one calibration, then the same sample size
+    budget = min(args.cpu_seconds, 150.0 / max(1, args.warmup + args.steps))
+    per = None
     for it in range(args.warmup + args.steps):
-        r = cpu_reference_run(base, pats[it * 4096:], args.cpu_seconds, cores, "locate (RECOVERBW=1), step %d" % it)
+        r = cpu_reference_run(base, pats[it * 4096:], budget, cores, "locate (RECOVERBW=1), step %d" % it, per=per)
+        per = r["per"]
         if it >= args.warmup:
             vals.append(r["value"]); secs.append(r["search_seconds"]); base_info = r
     v = float(np.mean(vals))

@@ -398,7 +398,7 @@ __global__ void ls_finalize_kernel(const uint32_t* __restrict__ pat, const uint3
 // (indices_of_dollars_in_interval, EDSBWTsearch.cpp:1310-1332).  Output grouped by ascending pattern.
 template <bool WALK>
 __global__ void locate_kernel(const __grid_constant__ IndexView ix, const uint2* __restrict__ plist, const uint32_t* __restrict__ occ_ofs, const uint2* __restrict__ staging,
-                              uint32_t npat, uint64_t nocc, uint32_t pat_base, edsbwt_occ* __restrict__ out, StatsDev* __restrict__ st) {
+                              const uint2* const* __restrict__ seed_ivp, uint32_t npat, uint64_t nocc, uint32_t pat_base, edsbwt_occ* __restrict__ out, StatsDev* __restrict__ st) {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t steps = 0;
     // the patterns of this CTA's occurrences form a narrow range: two searches over the whole offset array per CTA, then
@@ -414,9 +414,12 @@ __global__ void locate_kernel(const __grid_constant__ IndexView ix, const uint2*
         uint32_t q = q0 + upper_bound_u32(occ_ofs + q0, s_q[1] - q0 + 1, (uint32_t)t) - 1;
         uint32_t r = (uint32_t)t - __ldg(occ_ofs + q);
         uint2 pl = __ldg(plist + q);
+        // final intervals of the pattern: staged by the search kernels, or (pattern no longer than the seed depth) the seed entry itself
+        const uint2* ivs = staging + pl.x;
+        if (pl.y & PLIST_SEED) { ivs = seed_ivp[(pl.y >> 27) & 15u] + pl.x; pl.y &= PLIST_N_MASK; }
         uint32_t row = 0;
         for (uint32_t j = 0; j < pl.y; ++j) {
-            uint2 iv = __ldg(staging + pl.x + j);
+            uint2 iv = __ldg(ivs + j);
             uint32_t len = iv.y - iv.x + 1;
             if (r < len) { row = iv.x + r; break; }
             r -= len;
@@ -480,7 +483,7 @@ Index::~Index() {
 }
 uint64_t Index::device_bytes() const {
     uint64_t b = occ.bytes() + eof_flat.bytes() + eof_inv.bytes() + str_seg.bytes() + seg_first.bytes() + seg_low.bytes() + sa4.bytes() + link_rec.bytes() + str_info.bytes();
-    for (SeedLevel* s : seed) if (s) b += s->off.bytes() + s->iv.bytes();
+    for (SeedLevel* s : seed) if (s) b += s->off.bytes() + s->iv.bytes() + s->cnt.bytes();
     if (move) b += move->bytes();
     return b;
 }
@@ -587,6 +590,15 @@ static uint32_t engine_step(Index& ix, Workspace& ws, PatView pv, uint32_t step,
     return total;
 }
 
+// cnt[key] = number of rows in the frontier of key: patterns no longer than the seed depth are answered by one lookup
+__global__ void seed_counts_kernel(const uint32_t* __restrict__ off, const uint2* __restrict__ iv, uint32_t nkeys, uint32_t* __restrict__ cnt) {
+    uint32_t key = blockIdx.x * blockDim.x + threadIdx.x;
+    if (key >= nkeys) return;
+    uint32_t c = 0;
+    for (uint32_t i = off[key], e = off[key + 1]; i < e; ++i) { const uint2 v = __ldg(iv + i); c += v.y - v.x + 1; }
+    cnt[key] = c;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // index build on the device
 // ---------------------------------------------------------------------------------------------------
@@ -636,6 +648,19 @@ static void build_seed_table(Index& ix, uint32_t k) {
         CUDA_OK(cudaStreamSynchronize(s));
         ix.seed_intervals += newF;
     }
+    // per-key row counts of the levels below the deepest one (the deepest level's lists are short: summed on the fly)
+    std::vector<const uint2*> ivp(17, nullptr);
+    for (uint32_t L = 1; L <= k; ++L) {
+        SeedLevel* lv = ix.seed[L];
+        ivp[L] = lv->iv.p;
+        if (L == k && k > 8) continue;
+        const uint32_t nkeys = 1u << (2 * L);
+        lv->cnt.ensure(nkeys);
+        seed_counts_kernel<<<grid_for(nkeys, 256), 256, 0, s>>>(lv->off.p, lv->iv.p, nkeys, lv->cnt.p);
+    }
+    ix.seed_ivp.ensure(17);
+    CUDA_OK(cudaMemcpyAsync(ix.seed_ivp.p, ivp.data(), 17 * sizeof(const uint2*), cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaStreamSynchronize(s));
     CUDA_OK(cudaGetLastError());
 }
 void build_device_index(Index& ix, const edsbwt_open_opts& o) {
@@ -808,7 +833,7 @@ static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64
     encode_patterns_kernel<<<grid_for(nsub, 128), 128, 0, s>>>(d_bytes, d_off, ids, nsub, lut, words, ws.ppack.p, ws.plen.p);
     PatView pv{ws.ppack.p, ws.plen.p, words, nsub, k_eff};
     SeedView sv{};
-    for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; }
+    for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; sv.cnt[L] = ix.seed[L]->cnt.p; }
     ws.cnt.ensure(nsub + 1); ws.src.ensure(nsub); ws.base.ensure(nsub + 1);
     seed_count_kernel<<<grid_for(nsub, 256), 256, 0, s>>>(pv, sv, ws.cnt.p, ws.src.p);
     CUDA_OK(cudaMemsetAsync(ws.cnt.p + nsub, 0, 4, s));
@@ -866,7 +891,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             if (want > 0xfffffff0ull) want = 0xfffffff0ull;
             ws.staging.ensure(want); ws.ovf_ids.ensure(npat);
             SeedView sv{};
-            for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; }
+            for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; sv.cnt[L] = ix.seed[L]->cnt.p; }
             FusedOut fo{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 1, ws.ovf_ids.p, d_alive};
             CUDA_OK(cudaEventRecord(ws.evf0, s));
             // MOVE: 16-byte frontier entries (b, e, b', e'), so half the slots fit the same shared memory
@@ -943,9 +968,9 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
                 CUDA_OK(cudaEventRecord(ws.evl0, s));
                 if (move) launch_move_locate(ix.view, ix.move->view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, pat_base, out.occ.p, st, s);
                 else if (ix.locate_mode == EDSBWT_LOCATE_WALK)
-                    locate_kernel<true><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, pat_base, out.occ.p, st);
+                    locate_kernel<true><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, ix.seed_ivp.p, npat, nocc, pat_base, out.occ.p, st);
                 else
-                    locate_kernel<false><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, pat_base, out.occ.p, st);
+                    locate_kernel<false><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, ix.seed_ivp.p, npat, nocc, pat_base, out.occ.p, st);
                 CUDA_OK(cudaEventRecord(ws.evl1, s));
                 ws.launches += 1; locate_ran = true;
                 // csv row order of the reference; MOVE's order is the frontier order the kernel emits

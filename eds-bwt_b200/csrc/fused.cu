@@ -36,9 +36,10 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     // (ncu: 114 M local sectors per launch): keep them in shared memory instead
     __shared__ const uint32_t* s_off[17];
     __shared__ const uint2* s_iv[17];
+    __shared__ const uint32_t* s_cnt[17];
     __shared__ uint32_t s_Cl[5];
     for (int i = threadIdx.x; i < 256; i += FUSED_THREADS) s_lut[i] = lut[i];
-    if (threadIdx.x < 17) { s_off[threadIdx.x] = sv.off[threadIdx.x]; s_iv[threadIdx.x] = sv.iv[threadIdx.x]; }
+    if (threadIdx.x < 17) { s_off[threadIdx.x] = sv.off[threadIdx.x]; s_iv[threadIdx.x] = sv.iv[threadIdx.x]; s_cnt[threadIdx.x] = sv.cnt[threadIdx.x]; }
     if (threadIdx.x < 5) s_Cl[threadIdx.x] = ix.Cl[threadIdx.x];
     __syncthreads();
 #define LIST(j) s_list[(j) * FUSED_THREADS + threadIdx.x]
@@ -49,7 +50,7 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     const uint32_t q = live ? (ids ? ids[tq] : tq) : 0u;      // second pass (large cap): only the patterns listed in ids
     uint32_t nF = 0, m = 0, L0 = 0, key = 0, win_lo = 0;
     uint64_t base = 0, win = 0;                       // win: 2-bit codes of pattern characters [win_lo, win_lo + 32)
-    bool ovf = false;
+    bool ovf = false, direct = false;                 // direct: the answer is the seed entry itself (pattern no longer than the seed depth)
     unsigned long long sI = 0, sS = 0, sE = 0, sLF = 0, sBlk = 0;
     if (live) {
         base = poff[q];
@@ -69,7 +70,18 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         if (ok) {
             key = (uint32_t)(win >> (2 * (m - L0 - win_lo))) & (uint32_t)((1ull << (2 * L0)) - 1);
             uint32_t a = __ldg(s_off[L0] + key), n0 = __ldg(s_off[L0] + key + 1) - a;
-            if (n0 > cap) ovf = true;
+            if (n0 && m == L0 && n0 <= PLIST_N_MASK) {
+                // pattern no longer than the seed depth: nothing is left to search.  A short key's frontier can hold thousands
+                // of intervals, so it is neither copied nor staged: the count comes from the per-key table (or a sum at the deepest level) and the plist entry
+                // points into the seed table.  The lane's own (unused) slot column carries both to the epilogue.
+                direct = true;
+                uint32_t dc = 0;
+                if (s_cnt[L0]) dc = __ldg(s_cnt[L0] + key);
+                else for (uint32_t j = 0; j < n0; ++j) { const uint2 v = __ldg(s_iv[L0] + a + j); dc += v.y - v.x + 1; }
+                LIST(0) = make_uint2(a, PLIST_SEED | (L0 << 27) | n0);
+                LIST(1) = make_uint2(dc, n0);
+            }
+            else if (n0 > cap) ovf = true;
             else { for (uint32_t j = 0; j < n0; ++j) LIST(j) = __ldg(s_iv[L0] + a + j); nF = n0; }
         } else m = 0;
     }
@@ -144,12 +156,12 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         }
         nF = nout;
     }
-    if (STATS && !ovf && live && m && L0 + s == mk) sI += nF;            // frontier left at suffix length min(m, kc)
+    if (STATS && !ovf && live && m && L0 + s == mk) sI += direct ? LIST(1).y : nF;            // frontier left at suffix length min(m, kc)
     if (out.alive && live && !ovf) {
         // where the frontier died ("Pattern not found, interrupted in position", EDSBWTsearch.cpp:714-717)
         uint32_t la = 0;
         if (m == 0) la = 0;
-        else if (nF) la = m;
+        else if (nF || direct) la = m;
         else if (s > 0) la = L0 + s - 1;
         else for (uint32_t L = L0 - 1; L >= 1; --L) {                     // empty seed entry: longest shorter suffix that is not
             const uint32_t kl = key >> (2 * (L0 - L));
@@ -161,6 +173,7 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     uint32_t cnt = 0;
     if (ovf) nF = 0;
     for (uint32_t j = 0; j < nF; ++j) { const uint2 iv = LIST(j); cnt += iv.y - iv.x + 1; }
+    if (direct) cnt = LIST(1).x;
     const int lane = threadIdx.x & 31;
     uint32_t pre = nF;                                                  // inclusive warp scan
     for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= o) pre += t; }
@@ -173,7 +186,7 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     if (live) {
         const uint32_t my = wbase + pre - nF;
         for (uint32_t j = 0; j < nF; ++j) out.staging[my + j] = LIST(j);
-        out.plist[q] = make_uint2(my, nF);
+        out.plist[q] = direct ? LIST(0) : make_uint2(my, nF);
         out.counts[q] = cnt;
         if (ovf) out.ovf_ids[atomicAdd(out.ovf_count, 1u)] = q;
     }

@@ -40,6 +40,7 @@ struct DevBuf {
         size_t ncap = n + n / 4 + 64;
         T* q = nullptr;
         CUDA_OK(cudaMalloc(&q, ncap * sizeof(T)));
+        if (keep_n > cap) keep_n = cap;           // a cursor that ran past the end (staging overflow) keeps what exists
         if (keep && p && keep_n) { CUDA_OK(cudaMemcpyAsync(q, p, keep_n * sizeof(T), cudaMemcpyDeviceToDevice, s)); CUDA_OK(cudaStreamSynchronize(s)); }
         if (p) cudaFree(p);
         p = q; cap = ncap;
@@ -264,8 +265,10 @@ void parse_eds_text(const std::vector<uint8_t>& text, std::vector<uint8_t>& lett
 // ---------------------------------------------------------------------------------------------------
 // device index + search engine
 // ---------------------------------------------------------------------------------------------------
-struct SeedLevel { DevBuf<uint32_t> off; DevBuf<uint2> iv; size_t n_iv = 0; };     // iv[off[key] .. off[key+1]) = frontier (lo,hi) of key
-struct SeedView { const uint32_t* off[17]; const uint2* iv[17]; };
+struct SeedLevel { DevBuf<uint32_t> off, cnt; DevBuf<uint2> iv; size_t n_iv = 0; };     // iv[off[key] .. off[key+1]) = frontier (lo,hi) of key; cnt[key] = rows in it (levels < k)
+struct SeedView { const uint32_t* off[17]; const uint2* iv[17]; const uint32_t* cnt[17]; };
+// plist entries of patterns no longer than the seed depth reference the seed table itself (no copy): y = PLIST_SEED | level << 27 | n
+constexpr uint32_t PLIST_SEED = 0x80000000u, PLIST_N_MASK = 0x07ffffffu;
 
 struct StatsDev { unsigned long long I, S, E, L, O, lf_intervals, occ_blocks, overflow; };
 
@@ -328,6 +331,7 @@ struct Index {
     DevBuf<uint32_t> eof_flat, str_seg, seg_first, seg_low;
     DevBuf<uint4> sa4;
     DevBuf<uint2> link_rec, str_info;
+    DevBuf<const uint2*> seed_ivp;   // [17] device copy of the seed levels' interval arrays (locate of PLIST_SEED entries)
     DevBuf<uint8_t> lut;             // 256-byte byte -> code table on the device (0..3 letters, 4 end-marker, 255 other)
     IndexView view{};
     uint32_t seed_k = 0;

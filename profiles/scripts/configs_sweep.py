@@ -114,9 +114,9 @@ def main():
         with eb.Index(base, verify=False) as idx:
             info = idx.info()
             for m in [int(x) for x in args.lens.split(",")]:
-                # m < seed depth: the frontier of a short key holds thousands of intervals and every pattern has thousands of
-                # occurrences (4^8 keys over 2.8e8 rows): a 1/256 sample keeps frontier and tuple buffers bounded
-                npat = args.npat if m >= 16 else max(1, args.npat // 256)
+                # m < seed depth: count-only is one table lookup per pattern; every pattern has thousands of occurrences
+                # (4^8 keys over 2.8e8 rows), so locate runs on a 1/256 sample to keep the tuple buffer bounded
+                npat = args.npat
                 pats = synth.sample_patterns(col, npat, m, seed=55 + m)
                 data, off = synth.pack_fixed(pats)
                 del pats
@@ -124,7 +124,9 @@ def main():
                 r0["patterns"] = npat
                 rec = {"config": "cfg5: cfg4 index (%g Mbp, n=%d), %d length-%d patterns" % (args.mbp, info.n, npat, m), "pattern_len": m,
                        "seed_k": info.seed_k, "count_only": r0}
-                nloc = npat
+                nloc = npat if m >= 16 else max(1, npat // 256)
+                if nloc != npat:
+                    data, off = data[: nloc * m].copy(), off[: nloc + 1].copy()
                 try:
                     r1, _, _ = run(idx, torch, data, off, m, True, eb.LF_RANK, args.steps)
                     r1["patterns"] = nloc
