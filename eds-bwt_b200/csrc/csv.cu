@@ -62,6 +62,7 @@ __global__ void permute_rows_kernel(const edsbwt_occ* __restrict__ in, const uin
 uint64_t order_rows_reference(Index& ix, SearchOut& out, const uint32_t* d_occ_ofs, uint32_t npat, cudaStream_t s) {
     const uint64_t nocc = out.nocc;
     if (nocc < 2) return 0;
+    if (nocc > 0x7fffffffull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^31 rows to order in one batch; split the batch (edsbwt_set_chunk)");
     CsvScratch& c = scratch(ix);
     uint64_t launches = 0;
     if (!ix.eof_inv.p) {

@@ -676,6 +676,7 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     CUDA_OK(cudaEventCreate(&ws.evf0)); CUDA_OK(cudaEventCreate(&ws.evf1)); CUDA_OK(cudaEventCreate(&ws.evl0)); CUDA_OK(cudaEventCreate(&ws.evl1));
     ix.engine = o.engine == EDSBWT_ENGINE_LEVELSYNC ? EDSBWT_ENGINE_LEVELSYNC : EDSBWT_ENGINE_FUSED;
     ix.fused_cap = o.fused_cap > 0 ? (uint32_t)o.fused_cap : 12u;       // 12 slots: 12 CTAs/SM (40 registers) and >= 60 KB of L1 left (A/B: profiles/r01_ab_keep_sort_sizes.txt)
+    ix.fused_cap_auto = o.fused_cap <= 0;
     if (ix.fused_cap < 4) ix.fused_cap = 4;
     if (ix.fused_cap > FUSED_BIG_CAP) ix.fused_cap = FUSED_BIG_CAP;
     ix.fused_cap2 = o.fused_cap2 > 0 ? std::min<uint32_t>((uint32_t)o.fused_cap2, FUSED_BIG_CAP) : FUSED_BIG_CAP;
@@ -906,6 +907,9 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             CUDA_OK(cudaStreamSynchronize(s));
             nstage = ws.h_pin[0]; novf = ws.h_pin[1];
             novf1 = novf;
+            // variant-dense indexes (cfg3: a site every 6 bp) carry longer frontiers: a second pass costs a full pattern latency,
+            // so batches after one that overflowed noticeably run with 20 slots (10 CTAs/SM instantiation)
+            if (!move && ix.fused_cap_auto && ix.fused_cap < 20 && (uint64_t)novf * 1000 > npat) ix.fused_cap = 20;
             ids = ws.ovf_ids.p;
             if (novf && cap1 < cap2) {
                 // ---- second pass: the same kernel with the largest frontier that fits one CTA per SM, only over the
