@@ -909,7 +909,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             novf1 = novf;
             // variant-dense indexes (cfg3: a site every 6 bp) carry longer frontiers: a second pass costs a full pattern latency,
             // so batches after one that overflowed noticeably run with 20 slots (10 CTAs/SM instantiation)
-            if (!move && ix.fused_cap_auto && ix.fused_cap < 20 && (uint64_t)novf * 1000 > npat) ix.fused_cap = 20;
+            if (!move && !stats && ix.fused_cap_auto && ix.fused_cap < 20 && (uint64_t)novf * 1000 > npat) ix.fused_cap = 20;   // (a counting run starts from a shallower seed level: not representative)
             ids = ws.ovf_ids.p;
             if (novf && cap1 < cap2) {
                 // ---- second pass: the same kernel with the largest frontier that fits one CTA per SM, only over the
