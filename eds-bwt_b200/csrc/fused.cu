@@ -212,7 +212,7 @@ void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, co
     if (st) {
         CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<true, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
         fused_search_kernel<true, 10><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
-    } else if (cap <= 12) {              // 12 CTAs/SM: 40 registers (40 B of spill in a cold path), 12.8 KB of frontier each; 3.27 -> 3.09 ms
+    } else if (cap <= 14) {              // 12 CTAs/SM: 40 registers (40 B of spill in a cold path), at most 14 KB of frontier each; 3.27 -> 3.09 ms
         CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         fused_search_kernel<false, 12><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
     } else {

@@ -350,8 +350,8 @@ struct Index {
     uint32_t chunk_patterns = 1u << 21;     // patterns per pipeline chunk of the host-buffer searches
     edsbwt_stats last{};
     int collect_counters = 0; uint32_t canonical_k = 12;
-    int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 12, fused_cap2 = FUSED_BIG_CAP;
-    bool fused_cap_auto = true;         // no explicit fused_cap: a batch that overflows 12 slots in > 0.1 % of its patterns switches later batches to 20
+    int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 13, fused_cap2 = FUSED_BIG_CAP;
+    bool fused_cap_auto = true;         // no explicit fused_cap: a batch that overflows the default slots in > 0.1 % of its patterns switches later batches to 20
     uint64_t device_bytes() const;
     ~Index();
 };

@@ -72,7 +72,7 @@ typedef struct {
     int32_t  verify;            /* 1 = cross-check _bv_<p>.aux (rrr) and tableOcc against the pile bytes      */
     int32_t  build_move;        /* 1 = also build the move table (EDSBWT_LF_MOVE searches)                    */
     int32_t  engine;            /* EDSBWT_ENGINE_FUSED (default) / _LEVELSYNC                                 */
-    int32_t  fused_cap;         /* frontier slots per pattern of the fused kernel (0 = default 12: 12 CTAs per SM; above 12: 10 CTAs) */
+    int32_t  fused_cap;         /* frontier slots per pattern of the fused kernel (0 = default 13: 12 CTAs per SM; above 14: 10 CTAs) */
     int32_t  fused_cap2;        /* slots of the second pass over the patterns that outgrew the first (0 = 192) */
     int32_t  move_a;            /* balancing parameter a of the move table (build_MLF's <a>); 0 = default 8             */
 } edsbwt_open_opts;
