@@ -483,7 +483,7 @@ Index::~Index() {
 }
 uint64_t Index::device_bytes() const {
     uint64_t b = occ.bytes() + eof_flat.bytes() + eof_inv.bytes() + str_seg.bytes() + seg_first.bytes() + seg_low.bytes() + sa4.bytes() + link_rec.bytes() + str_info.bytes();
-    for (SeedLevel* s : seed) if (s) b += s->off.bytes() + s->iv.bytes() + s->cnt.bytes();
+    for (SeedLevel* s : seed) if (s) b += s->off.bytes() + s->iv.bytes() + s->cnt.bytes() + s->first.bytes();
     if (move) b += move->bytes();
     return b;
 }
@@ -599,6 +599,16 @@ __global__ void seed_counts_kernel(const uint32_t* __restrict__ off, const uint2
     cnt[key] = c;
 }
 
+// first[key] = {first interval, offset of the entry, number of intervals}: the seed lookup of the hot kernel in ONE 16-byte gather
+__global__ void seed_first_kernel(const uint32_t* __restrict__ off, const uint2* __restrict__ iv, uint32_t nkeys, uint4* __restrict__ first) {
+    uint32_t key = blockIdx.x * blockDim.x + threadIdx.x;
+    if (key >= nkeys) return;
+    const uint32_t a = off[key], n0 = off[key + 1] - a;
+    uint2 v = make_uint2(1u, 0u);
+    if (n0) v = __ldg(iv + a);
+    first[key] = make_uint4(v.x, v.y, a, n0);
+}
+
 // ---------------------------------------------------------------------------------------------------
 // index build on the device
 // ---------------------------------------------------------------------------------------------------
@@ -642,7 +652,7 @@ static void build_seed_table(Index& ix, uint32_t k) {
         }
         SeedLevel* nx = new SeedLevel; ix.seed[L + 1] = nx;
         uint32_t nk2 = nkeys * 4;
-        nx->off.ensure((size_t)nk2 + 1); nx->iv.ensure(newF + 1); nx->n_iv = newF;
+        nx->off.exact((size_t)nk2 + 1); nx->iv.exact((size_t)newF + 1); nx->n_iv = newF;
         if (newF) zip_kernel<<<grid_for(newF, 256), 256, 0, s>>>(ws.cur.lo.p, ws.cur.hi.p, newF, nx->iv.p);
         key_offsets_kernel<<<grid_for((size_t)nk2 + 1, 256), 256, 0, s>>>(ws.cur.pat.p, newF, nk2, nx->off.p);
         CUDA_OK(cudaStreamSynchronize(s));
@@ -655,8 +665,14 @@ static void build_seed_table(Index& ix, uint32_t k) {
         ivp[L] = lv->iv.p;
         if (L == k && k > 8) continue;
         const uint32_t nkeys = 1u << (2 * L);
-        lv->cnt.ensure(nkeys);
+        lv->cnt.exact(nkeys);
         seed_counts_kernel<<<grid_for(nkeys, 256), 256, 0, s>>>(lv->off.p, lv->iv.p, nkeys, lv->cnt.p);
+    }
+    if (k >= 10) {                      // worth 16 B per key only where the table is deep (large indexes)
+        SeedLevel* lv = ix.seed[k];
+        const uint32_t nkeys = 1u << (2 * k);
+        lv->first.exact(nkeys);
+        seed_first_kernel<<<grid_for(nkeys, 256), 256, 0, s>>>(lv->off.p, lv->iv.p, nkeys, lv->first.p);
     }
     ix.seed_ivp.ensure(17);
     CUDA_OK(cudaMemcpyAsync(ix.seed_ivp.p, ivp.data(), 17 * sizeof(const uint2*), cudaMemcpyHostToDevice, s));
@@ -758,7 +774,7 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     ix.locate_mode = o.locate_mode == EDSBWT_LOCATE_WALK ? EDSBWT_LOCATE_WALK : EDSBWT_LOCATE_SA;
     if (ix.locate_mode == EDSBWT_LOCATE_SA) {
         DevBuf<uint2> sa; sa.ensure((size_t)h.n + 1);                 // (string, distance to the end): build scratch
-        ix.sa4.ensure((size_t)h.n + 1);
+        ix.sa4.exact((size_t)h.n + 1);
         DevBuf<uint32_t> slen; slen.ensure(h.n_text + 1);
         CUDA_OK(cudaMemsetAsync(sa.p, 0xff, (size_t)h.n * 8, s));
         CUDA_OK(cudaMemsetAsync(ix.sa4.p, 0xff, (size_t)h.n_text * 16, s));     // end-marker rows are never located
@@ -835,6 +851,7 @@ static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64
     PatView pv{ws.ppack.p, ws.plen.p, words, nsub, k_eff};
     SeedView sv{};
     for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; sv.cnt[L] = ix.seed[L]->cnt.p; }
+            sv.first = ix.seed[ix.seed_k]->first.p; sv.first_level = ix.seed_k;
     ws.cnt.ensure(nsub + 1); ws.src.ensure(nsub); ws.base.ensure(nsub + 1);
     seed_count_kernel<<<grid_for(nsub, 256), 256, 0, s>>>(pv, sv, ws.cnt.p, ws.src.p);
     CUDA_OK(cudaMemsetAsync(ws.cnt.p + nsub, 0, 4, s));
@@ -893,6 +910,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             ws.staging.ensure(want); ws.ovf_ids.ensure(npat);
             SeedView sv{};
             for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; sv.cnt[L] = ix.seed[L]->cnt.p; }
+            sv.first = ix.seed[ix.seed_k]->first.p; sv.first_level = ix.seed_k;
             FusedOut fo{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 1, ws.ovf_ids.p, d_alive};
             CUDA_OK(cudaEventRecord(ws.evf0, s));
             // MOVE: 16-byte frontier entries (b, e, b', e'), so half the slots fit the same shared memory

@@ -69,7 +69,9 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         }
         if (ok) {
             key = (uint32_t)(win >> (2 * (m - L0 - win_lo))) & (uint32_t)((1ull << (2 * L0)) - 1);
-            uint32_t a = __ldg(s_off[L0] + key), n0 = __ldg(s_off[L0] + key + 1) - a;
+            uint32_t a, n0; uint2 iv0 = make_uint2(1u, 0u);
+            if (sv.first && L0 == sv.first_level) { const uint4 e = __ldg(sv.first + key); iv0 = make_uint2(e.x, e.y); a = e.z; n0 = e.w; }
+            else { a = __ldg(s_off[L0] + key); n0 = __ldg(s_off[L0] + key + 1) - a; if (n0) iv0 = __ldg(s_iv[L0] + a); }
             if (n0 && m == L0 && n0 <= PLIST_N_MASK) {
                 // pattern no longer than the seed depth: nothing is left to search.  A short key's frontier can hold thousands
                 // of intervals, so it is neither copied nor staged: the count comes from the per-key table (or a sum at the deepest level) and the plist entry
@@ -82,7 +84,7 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
                 LIST(1) = make_uint2(dc, n0);
             }
             else if (n0 > cap) ovf = true;
-            else { for (uint32_t j = 0; j < n0; ++j) LIST(j) = __ldg(s_iv[L0] + a + j); nF = n0; }
+            else { if (n0) LIST(0) = iv0; for (uint32_t j = 1; j < n0; ++j) LIST(j) = __ldg(s_iv[L0] + a + j); nF = n0; }
         } else m = 0;
     }
     const uint32_t steps = m - L0;

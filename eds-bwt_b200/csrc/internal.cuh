@@ -45,6 +45,14 @@ struct DevBuf {
         if (p) cudaFree(p);
         p = q; cap = ncap;
     }
+    // static index arrays: exactly n elements, no growth slack (the seed table and the locate table are gigabytes)
+    void exact(size_t n) {
+        if (n <= cap) return;
+        T* q = nullptr;
+        CUDA_OK(cudaMalloc(&q, n * sizeof(T)));
+        if (p) cudaFree(p);
+        p = q; cap = n;
+    }
     size_t bytes() const { return cap * sizeof(T); }
 };
 
@@ -265,8 +273,9 @@ void parse_eds_text(const std::vector<uint8_t>& text, std::vector<uint8_t>& lett
 // ---------------------------------------------------------------------------------------------------
 // device index + search engine
 // ---------------------------------------------------------------------------------------------------
-struct SeedLevel { DevBuf<uint32_t> off, cnt; DevBuf<uint2> iv; size_t n_iv = 0; };     // iv[off[key] .. off[key+1]) = frontier (lo,hi) of key; cnt[key] = rows in it (levels < k)
-struct SeedView { const uint32_t* off[17]; const uint2* iv[17]; const uint32_t* cnt[17]; };
+struct SeedLevel { DevBuf<uint32_t> off, cnt; DevBuf<uint2> iv; DevBuf<uint4> first; size_t n_iv = 0; };     // iv[off[key] .. off[key+1]) = frontier (lo,hi) of key; cnt[key] = rows in it (levels < k)
+struct SeedView { const uint32_t* off[17]; const uint2* iv[17]; const uint32_t* cnt[17];
+                  const uint4* first; uint32_t first_level; };   // deepest level: {lo, hi of the first interval, offset, count} per key -- one gather instead of two
 // plist entries of patterns no longer than the seed depth reference the seed table itself (no copy): y = PLIST_SEED | level << 27 | n
 constexpr uint32_t PLIST_SEED = 0x80000000u, PLIST_N_MASK = 0x07ffffffu;
 
