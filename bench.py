@@ -138,7 +138,7 @@ def workload_name(args):
         args.mbp, args.npat, args.plen)
 
 
-NCU_CAPTURE = "profiles/r01_fused_ncu_full_v6.txt"      # ncu --set full of fused_search_kernel at the default workload (cfg4, k = 14)
+NCU_CAPTURE = "profiles/r01_fused_ncu_full_v7.txt"      # ncu --set full of fused_search_kernel at the default workload (cfg4, k = 14)
 
 
 def ncu_traffic(args, seed_k):
