@@ -217,12 +217,6 @@ __device__ __forceinline__ void move_step(const MoveView& mv, uint32_t& row, uin
     run = e.z;
     while (row >= __ldg(&mv.T[run + 1].x)) ++run;
 }
-// rank of letter c and of '#' among the run heads L'[0, pos)
-__device__ __forceinline__ void rank2(const uint4* __restrict__ occL, uint32_t pos, int c, uint32_t& rc, uint32_t& rd) {
-    rc = occ_rank1(occL, pos, c);
-    rd = occ_rank_eof(occL, pos);
-}
-
 // the two rank pairs of an interval, (rank_c, rank_#) of L'[0, posA) and L'[0, posB), posA <= posB: the run heads b' and
 // e' + 1 nearly always share one 64-byte block of the L' structure, which is then fetched once (two 256-bit loads)
 __device__ __forceinline__ void rank2_pair(const uint4* __restrict__ occL, uint32_t posA, uint32_t posB, int c,
