@@ -116,6 +116,17 @@ void edsbwt_result_free(edsbwt_result* res) {
 // Pipelined host-buffer search: H2D of chunk i+1 | search of chunk i | D2H of chunk i-1 on three streams.
 // occ may be null (count-only or sizing pass).  *nocc receives the total number of occurrences even when it
 // exceeds occ_cap (then EDSBWT_E_NOSPACE is returned and only the first occ_cap tuples were copied).
+// streams / events / double buffers of the host-buffer searches, created on first use
+static Pipe& pipe_of(Index& ix) {
+    if (!ix.pipe) {
+        ix.pipe = new Pipe;
+        CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->in, cudaStreamNonBlocking));
+        CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->outs, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) { CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_in[i], cudaEventDisableTiming)); CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_out[i], cudaEventDisableTiming)); }
+    }
+    return *ix.pipe;
+}
+
 __global__ void fixed_offsets_kernel(uint64_t* __restrict__ off, uint32_t n, uint64_t first, uint64_t len) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i <= n) off[i] = first + (uint64_t)i * len;
@@ -128,13 +139,7 @@ static int search_into_impl(edsbwt_index* idx, const uint8_t* pat_bytes, const u
     auto off_of = [&](uint32_t i) -> uint64_t { return pat_off ? pat_off[i] : (uint64_t)i * fixed_len; };
     Index& ix = idx->ix;
     CUDA_OK(cudaSetDevice(ix.device));
-    if (!ix.pipe) {
-        ix.pipe = new Pipe;
-        CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->in, cudaStreamNonBlocking));
-        CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->outs, cudaStreamNonBlocking));
-        for (int i = 0; i < 2; ++i) { CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_in[i], cudaEventDisableTiming)); CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_out[i], cudaEventDisableTiming)); }
-    }
-    Pipe& P = *ix.pipe;
+    Pipe& P = pipe_of(ix);
     // chunk schedule: equal chunks, then a tapered tail (halves down to a quarter chunk) -- the input copies are the long
     // pole of the pipeline, so what the batch pays on top of them is the search + copy-out of the LAST chunk only
     const uint32_t chunk = ix.chunk_patterns ? ix.chunk_patterns : npat;
@@ -297,13 +302,7 @@ int edsbwt_search_to_csv(edsbwt_index* idx, const uint8_t* pat_bytes, const uint
     int rc = guarded([&] {
         Index& ix = idx->ix;
         CUDA_OK(cudaSetDevice(ix.device));
-        if (!ix.pipe) {
-            ix.pipe = new Pipe;
-            CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->in, cudaStreamNonBlocking));
-            CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->outs, cudaStreamNonBlocking));
-            for (int i = 0; i < 2; ++i) { CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_in[i], cudaEventDisableTiming)); CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_out[i], cudaEventDisableTiming)); }
-        }
-        Pipe& P = *ix.pipe;
+        Pipe& P = pipe_of(ix);
         const int saved_order = ix.row_order;
         ix.row_order = EDSBWT_ROWS_REFERENCE;
         struct Restore { Index& ix; int o; ~Restore() { ix.row_order = o; } } restore{ix, saved_order};
