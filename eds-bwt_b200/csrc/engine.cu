@@ -394,55 +394,89 @@ __global__ void ls_finalize_kernel(const uint32_t* __restrict__ pat, const uint3
         plist[g] = make_uint2(sbase + i, e - i);
     }
 }
-// one thread per occurrence row: (string, offset) by table lookup or by LF-walk, then segment / index in segment
-// (indices_of_dollars_in_interval, EDSBWTsearch.cpp:1310-1332).  Output grouped by ascending pattern.
+// Locate (indices_of_dollars_in_interval, EDSBWTsearch.cpp:1310-1332): row -> (string, offset) by table lookup or by LF-walk,
+// then segment / index in segment.  Output grouped by ascending pattern: pattern q owns out[occ_ofs[q] .. occ_ofs[q+1]).
 template <bool WALK>
-__global__ void locate_kernel(const __grid_constant__ IndexView ix, const uint2* __restrict__ plist, const uint32_t* __restrict__ occ_ofs, const uint2* __restrict__ staging,
-                              const uint2* const* __restrict__ seed_ivp, uint32_t npat, uint64_t nocc, uint32_t pat_base, edsbwt_occ* __restrict__ out, StatsDev* __restrict__ st) {
-    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t steps = 0;
-    // the patterns of this CTA's occurrences form a narrow range: two searches over the whole offset array per CTA, then
-    // every thread searches inside that range (a few hundred entries, L1-resident) instead of 24 dependent L2 probes each
-    __shared__ uint32_t s_q[2];
-    if (threadIdx.x < 2) {
-        const uint64_t tt = threadIdx.x == 0 ? (uint64_t)blockIdx.x * blockDim.x : min((uint64_t)blockIdx.x * blockDim.x + blockDim.x - 1, nocc - 1);
-        s_q[threadIdx.x] = upper_bound_u32(occ_ofs, npat + 1, (uint32_t)tt) - 1;
+__device__ __forceinline__ uint32_t locate_row(const IndexView& ix, uint32_t row, uint32_t pat, edsbwt_occ* __restrict__ dst) {
+    uint32_t w, off;
+    uint2 si;
+    if (WALK) {
+        off = 0;
+        for (;;) {
+            uint32_t sy = occ_symbol(ix.occ, row);
+            if (sy == 0) break;
+            row = ix.Cl[sy - 1] + occ_rank1(ix.occ, row, (int)sy - 1);
+            ++off;
+        }
+        w = __ldg(ix.eof_flat + occ_rank_eof(ix.occ, row));
+        si = __ldg(ix.str_info + w);
+    } else { const uint4 v = __ldg(ix.sa4 + row); w = v.x; off = v.y; si = make_uint2(v.z, v.w); }      // ONE 16-byte gather per occurrence
+    edsbwt_occ o; o.pat = pat; o.str = w; o.seg = si.x; o.idx_in_seg = si.y; o.off = off;
+    *dst = o;
+    return off + 1;
+}
+constexpr uint32_t LOCATE_LIGHT_MAX = 32;      // patterns with more occurrences go to the warp-per-pattern kernel
+// one thread per PATTERN (nearly every pattern has 0-2 occurrences): counts, plist and staged intervals are read
+// coalesced, no search for the owner of a row; heavy patterns are queued for locate_heavy_kernel
+template <bool WALK>
+__global__ void locate_light_kernel(const __grid_constant__ IndexView ix, const uint2* __restrict__ plist, const uint32_t* __restrict__ occ_ofs, const uint2* __restrict__ staging,
+                                    const uint2* const* __restrict__ seed_ivp, uint32_t npat, uint32_t pat_base, edsbwt_occ* __restrict__ out,
+                                    uint32_t* __restrict__ heavy, uint32_t* __restrict__ nheavy, StatsDev* __restrict__ st) {
+    const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t steps = 0, nrows = 0;
+    if (q < npat) {
+        const uint32_t o0 = __ldg(occ_ofs + q), cnt = __ldg(occ_ofs + q + 1) - o0;
+        if (cnt > LOCATE_LIGHT_MAX) heavy[atomicAdd(nheavy, 1u)] = q;
+        else if (cnt) {
+            uint2 pl = __ldg(plist + q);
+            const uint2* ivs = staging + pl.x;
+            if (pl.y & PLIST_SEED) { ivs = seed_ivp[(pl.y >> 27) & 15u] + pl.x; pl.y &= PLIST_N_MASK; }
+            uint32_t t = o0;
+            for (uint32_t j = 0; j < pl.y; ++j) {
+                const uint2 iv = __ldg(ivs + j);
+                for (uint32_t row = iv.x; row <= iv.y; ++row) steps += locate_row<WALK>(ix, row, q + pat_base, out + t++);
+            }
+            nrows = cnt;
+        }
     }
-    __syncthreads();
-    if (t < nocc) {
-        const uint32_t q0 = s_q[0];
-        uint32_t q = q0 + upper_bound_u32(occ_ofs + q0, s_q[1] - q0 + 1, (uint32_t)t) - 1;
-        uint32_t r = (uint32_t)t - __ldg(occ_ofs + q);
+    if (st) { warp_add(&st->L, steps); warp_add(&st->O, nrows); }
+}
+// one WARP per heavy pattern: the intervals are walked once, the lanes share the rows of each interval
+template <bool WALK>
+__global__ void locate_heavy_kernel(const __grid_constant__ IndexView ix, const uint2* __restrict__ plist, const uint32_t* __restrict__ occ_ofs, const uint2* __restrict__ staging,
+                                    const uint2* const* __restrict__ seed_ivp, uint32_t pat_base, edsbwt_occ* __restrict__ out,
+                                    const uint32_t* __restrict__ heavy, const uint32_t* __restrict__ nheavy, StatsDev* __restrict__ st) {
+    const uint32_t lane = threadIdx.x & 31, warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t nh = *nheavy;
+    uint32_t steps = 0, nrows = 0;
+    for (uint32_t i = warp; i < nh; i += nwarps) {
+        const uint32_t q = heavy[i];
         uint2 pl = __ldg(plist + q);
-        // final intervals of the pattern: staged by the search kernels, or (pattern no longer than the seed depth) the seed entry itself
         const uint2* ivs = staging + pl.x;
         if (pl.y & PLIST_SEED) { ivs = seed_ivp[(pl.y >> 27) & 15u] + pl.x; pl.y &= PLIST_N_MASK; }
-        uint32_t row = 0;
-        for (uint32_t j = 0; j < pl.y; ++j) {
-            uint2 iv = __ldg(ivs + j);
-            uint32_t len = iv.y - iv.x + 1;
-            if (r < len) { row = iv.x + r; break; }
-            r -= len;
-        }
-        uint32_t w, off;
-        if (WALK) {
-            off = 0;
-            for (;;) {
-                uint32_t sy = occ_symbol(ix.occ, row);
-                if (sy == 0) break;
-                row = ix.Cl[sy - 1] + occ_rank1(ix.occ, row, (int)sy - 1);
-                ++off;
+        uint32_t t = __ldg(occ_ofs + q);
+        // 32 intervals at a time: lane l holds interval j0 + l; an exclusive warp scan of the lengths places every row
+        for (uint32_t j0 = 0; j0 < pl.y; j0 += 32) {
+            uint2 iv = make_uint2(1u, 0u);
+            if (j0 + lane < pl.y) iv = __ldg(ivs + j0 + lane);
+            const uint32_t len = iv.y + 1 - iv.x;                      // 0 for the padding lanes
+            uint32_t pre = len;
+            for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= (uint32_t)o) pre += v; }
+            const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
+            pre -= len;                                                // exclusive
+            // rows k = 0 .. total-1 of this group: owner = last lane with pre <= k (binary search over the 32 prefix values by shuffles)
+            for (uint32_t k = lane; k < ((total + 31) & ~31u); k += 32) {
+                uint32_t lo = 0;
+                #pragma unroll
+                for (int b = 16; b; b >>= 1) { const uint32_t pv = __shfl_sync(0xffffffffu, pre, (lo + b) & 31); if (lo + b < 32 && pv <= k) lo += b; }
+                // skip empty (padding / zero-length) owners: pre is non-decreasing, the LAST lane with pre <= k has len > 0 when k < total
+                const uint32_t ivx = __shfl_sync(0xffffffffu, iv.x, lo), p0 = __shfl_sync(0xffffffffu, pre, lo);
+                if (k < total) { steps += locate_row<WALK>(ix, ivx + (k - p0), q + pat_base, out + t + k); ++nrows; }
             }
-            w = __ldg(ix.eof_flat + occ_rank_eof(ix.occ, row));
+            t += total;
         }
-        uint2 si;
-        if (WALK) si = __ldg(ix.str_info + w);
-        else { const uint4 v = __ldg(ix.sa4 + row); w = v.x; off = v.y; si = make_uint2(v.z, v.w); }      // ONE 16-byte gather per occurrence
-        edsbwt_occ o; o.pat = q + pat_base; o.str = w; o.seg = si.x; o.idx_in_seg = si.y; o.off = off;
-        out[t] = o;
-        steps = off + 1;
     }
-    if (st) { warp_add(&st->L, steps); warp_add(&st->O, steps ? 1u : 0u); }
+    if (st) { warp_add(&st->L, steps); warp_add(&st->O, nrows); }
 }
 
 // ===================================================================================================
@@ -462,7 +496,7 @@ struct Workspace {
     DevBuf<uint8_t> cubtmp;
     DevBuf<unsigned int> scalars;        // [0] nvalid
     DevBuf<uint2> plist, staging;        // per-pattern final lists (fused + level-synchronous results)
-    DevBuf<uint32_t> fcursor, ovf_ids, ovf_ids2, occ_ofs;
+    DevBuf<uint32_t> fcursor, ovf_ids, ovf_ids2, occ_ofs, heavy;
     StatsDev* d_stats = nullptr;
     uint32_t* h_pin = nullptr;           // pinned read-back area
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr, evf0 = nullptr, evf1 = nullptr, evl0 = nullptr, evl1 = nullptr;
@@ -989,10 +1023,20 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
                 out.occ.ensure(nocc);
                 CUDA_OK(cudaEventRecord(ws.evl0, s));
                 if (move) launch_move_locate(ix.view, ix.move->view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, pat_base, out.occ.p, st, s);
-                else if (ix.locate_mode == EDSBWT_LOCATE_WALK)
-                    locate_kernel<true><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, ix.seed_ivp.p, npat, nocc, pat_base, out.occ.p, st);
-                else
-                    locate_kernel<false><<<grid_for(nocc, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, ix.seed_ivp.p, npat, nocc, pat_base, out.occ.p, st);
+                else {
+                    // light patterns: one thread each; heavy ones (> 32 occurrences) are queued on the device and taken by warps
+                    ws.heavy.ensure(npat); uint32_t* nheavy = ws.fcursor.p + 3;
+                    CUDA_OK(cudaMemsetAsync(nheavy, 0, 4, s));
+                    const unsigned hgrid = 148 * 8;
+                    if (ix.locate_mode == EDSBWT_LOCATE_WALK) {
+                        locate_light_kernel<true><<<grid_for(npat, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, ix.seed_ivp.p, npat, pat_base, out.occ.p, ws.heavy.p, nheavy, st);
+                        locate_heavy_kernel<true><<<hgrid, 128, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, ix.seed_ivp.p, pat_base, out.occ.p, ws.heavy.p, nheavy, st);
+                    } else {
+                        locate_light_kernel<false><<<grid_for(npat, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, ix.seed_ivp.p, npat, pat_base, out.occ.p, ws.heavy.p, nheavy, st);
+                        locate_heavy_kernel<false><<<hgrid, 128, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, ix.seed_ivp.p, pat_base, out.occ.p, ws.heavy.p, nheavy, st);
+                    }
+                    ws.launches += 1;
+                }
                 CUDA_OK(cudaEventRecord(ws.evl1, s));
                 ws.launches += 1; locate_ran = true;
                 // csv row order of the reference; MOVE's order is the frontier order the kernel emits
