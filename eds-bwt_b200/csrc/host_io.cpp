@@ -3,6 +3,8 @@
 #include <cerrno>
 #include <cstdarg>
 #include <fstream>
+#include <new>
+#include <sys/stat.h>
 
 #include "internal.cuh"
 
@@ -17,7 +19,10 @@ const char* last_error_cstr() { return g_err; }
 std::vector<uint8_t> read_file(const std::string& path) {
     FILE* f = fopen(path.c_str(), "rb");
     if (!f) EDS_FAIL(EDSBWT_E_IO, "Error opening %s: %s", path.c_str(), strerror(errno));
+    struct stat sb;
+    if (fstat(fileno(f), &sb) != 0 || !S_ISREG(sb.st_mode)) { fclose(f); EDS_FAIL(EDSBWT_E_IO, "Error opening %s: not a regular file", path.c_str()); }
     fseek(f, 0, SEEK_END); long sz = ftell(f); fseek(f, 0, SEEK_SET);
+    if (sz < 0) { fclose(f); EDS_FAIL(EDSBWT_E_IO, "Error reading %s: %s", path.c_str(), strerror(errno)); }
     std::vector<uint8_t> b((size_t)sz);
     if (sz && fread(b.data(), 1, (size_t)sz, f) != (size_t)sz) { fclose(f); EDS_FAIL(EDSBWT_E_IO, "short read on %s", path.c_str()); }
     fclose(f);
@@ -27,7 +32,7 @@ void write_file(const std::string& path, const void* data, size_t len) {
     FILE* f = fopen(path.c_str(), "wb");
     if (!f) EDS_FAIL(EDSBWT_E_IO, "Error opening %s for writing: %s", path.c_str(), strerror(errno));
     if (len && fwrite(data, 1, len, f) != len) { fclose(f); EDS_FAIL(EDSBWT_E_IO, "short write on %s", path.c_str()); }
-    fclose(f);
+    if (fclose(f) != 0) EDS_FAIL(EDSBWT_E_IO, "Error writing %s: %s", path.c_str(), strerror(errno));
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -261,6 +266,16 @@ void load_host_index(const std::string& base, bool verify, HostIndex& h) {
 using namespace edsbwt;
 namespace edsbwt { const char* last_error_cstr(); }
 
+namespace {
+// no exception may cross the C ABI (same mapping as api.cu's guard)
+template <class F> int host_guard(F&& f) {
+    try { return f(); }
+    catch (const Failure& e) { return e.code; }
+    catch (const std::bad_alloc&) { set_error("host out of memory"); return EDSBWT_E_IO; }
+    catch (const std::exception& e) { set_error("exception: %s", e.what()); return EDSBWT_E_ARG; }
+}
+}  // namespace
+
 extern "C" {
 
 const char* edsbwt_last_error(void) { return edsbwt::last_error_cstr(); }
@@ -282,7 +297,7 @@ const char* edsbwt_strerror(int code) {
 
 int edsbwt_read_patterns(const char* path, uint8_t** bytes, uint64_t** off, uint32_t* npat) {
     if (!path || !bytes || !off || !npat) return EDSBWT_E_ARG;
-    try {
+    return host_guard([&]() -> int {
         std::vector<uint8_t> f = read_file(path);
         std::vector<uint64_t> o; std::vector<uint8_t> b; b.reserve(f.size());
         // std::getline semantics (EDSBWTsearch.cpp:207): '\n' separated, a final '\n' adds no line
@@ -292,13 +307,14 @@ int edsbwt_read_patterns(const char* path, uint8_t** bytes, uint64_t** off, uint
             i = j + 1;
         }
         o.push_back(b.size());
-        *npat = (uint32_t)(o.size() - 1);
-        *bytes = (uint8_t*)malloc(b.size() ? b.size() : 1); *off = (uint64_t*)malloc(o.size() * 8);
-        if (!*bytes || !*off) return EDSBWT_E_IO;
-        if (!b.empty()) memcpy(*bytes, b.data(), b.size());
-        memcpy(*off, o.data(), o.size() * 8);
+        if (o.size() - 1 > 0xffffffffull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "%s holds %zu patterns, at most 2^32-1 per batch", path, o.size() - 1);
+        uint8_t* pb = (uint8_t*)malloc(b.size() ? b.size() : 1); uint64_t* po = (uint64_t*)malloc(o.size() * 8);
+        if (!pb || !po) { free(pb); free(po); set_error("host out of memory"); return EDSBWT_E_IO; }
+        if (!b.empty()) memcpy(pb, b.data(), b.size());
+        memcpy(po, o.data(), o.size() * 8);
+        *bytes = pb; *off = po; *npat = (uint32_t)(o.size() - 1);
         return EDSBWT_OK;
-    } catch (const Failure& f) { return f.code; }
+    });
 }
 
 // stringCheck (stringCheck.cpp:11-84): brackets every non-degenerate stretch of an EDS text, drops <...> comments and
@@ -307,7 +323,7 @@ int edsbwt_read_patterns(const char* path, uint8_t** bytes, uint64_t** off, uint
 int edsbwt_string_check(const char* in_path, const char* out_path) {
     if (!in_path || !out_path) return EDSBWT_E_ARG;
     const uint8_t EMPTY = 'Z';
-    try {
+    return host_guard([&]() -> int {
         const std::vector<uint8_t> f = read_file(in_path);
         std::vector<uint8_t> o; o.reserve(f.size() + f.size() / 8 + 16);
         const size_t n = f.size();
@@ -337,24 +353,29 @@ int edsbwt_string_check(const char* in_path, const char* out_path) {
         }
         write_file(out_path, o.data(), o.size());
         return EDSBWT_OK;
-    } catch (const Failure& f) { return f.code; }
+    });
 }
 
 int edsbwt_write_csv(const char* path, const edsbwt_occ* occ, uint64_t nocc, uint32_t pat_base, int move, int append) {
     if (!path || (nocc && !occ)) return EDSBWT_E_ARG;
-    FILE* f = fopen(path, append ? "ab" : "wb");
-    if (!f) { set_error("ERROR opening file %s to write output", path); return EDSBWT_E_IO; }
-    if (!append) fputs(move ? "#Pat\t$_i\tD[i]\tS_j\tS_j[r] \n" : "#Pat\t$_i\tD[i]\tS_j\tS_j[r]\n", f);
-    std::vector<char> buf; buf.reserve(1 << 20);
-    char line[96];
-    for (uint64_t i = 0; i < nocc; ++i) {
-        int k = snprintf(line, sizeof line, "%u\t%u\t%u\t%u\t%u\n", occ[i].pat + pat_base + 1, occ[i].str, occ[i].seg, occ[i].idx_in_seg, occ[i].off);
-        buf.insert(buf.end(), line, line + k);
-        if (buf.size() > (1 << 20) - 128) { fwrite(buf.data(), 1, buf.size(), f); buf.clear(); }
-    }
-    if (!buf.empty()) fwrite(buf.data(), 1, buf.size(), f);
-    fclose(f);
-    return EDSBWT_OK;
+    return host_guard([&]() -> int {
+        std::vector<char> buf; buf.reserve(1 << 20);          // filled to at most 1 MiB: no allocation while the file is open
+        FILE* f = fopen(path, append ? "ab" : "wb");
+        if (!f) { set_error("ERROR opening file %s to write output", path); return EDSBWT_E_IO; }
+        bool ok = true;
+        if (!append) ok = fputs(move ? "#Pat\t$_i\tD[i]\tS_j\tS_j[r] \n" : "#Pat\t$_i\tD[i]\tS_j\tS_j[r]\n", f) >= 0;
+        char line[96];
+        for (uint64_t i = 0; i < nocc && ok; ++i) {
+            int k = snprintf(line, sizeof line, "%u\t%u\t%u\t%u\t%u\n", occ[i].pat + pat_base + 1, occ[i].str, occ[i].seg, occ[i].idx_in_seg, occ[i].off);
+            buf.insert(buf.end(), line, line + k);
+            if (buf.size() > (1 << 20) - 128) { ok = fwrite(buf.data(), 1, buf.size(), f) == buf.size(); buf.clear(); }
+        }
+        if (ok && !buf.empty()) ok = fwrite(buf.data(), 1, buf.size(), f) == buf.size();
+        const int werr = errno;
+        if (fclose(f) != 0 && ok) { ok = false; }
+        if (!ok) { set_error("ERROR writing %s: %s", path, strerror(werr ? werr : errno)); return EDSBWT_E_IO; }
+        return EDSBWT_OK;
+    });
 }
 
 }  // extern "C"

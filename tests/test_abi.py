@@ -57,3 +57,32 @@ def test_no_cpu_fallback(eb, tmp_path):
     assert ei.value.code == -4
     with pytest.raises(eb.EdsbwtError):
         eb.gather_bench(0, 1 << 20, 1 << 10, 1)
+
+
+def test_host_entry_points_report_io_errors(eb, tmp_path):
+    """Nothing may cross the C ABI as an exception: unreadable / unwritable paths come back as EDSBWT_E_IO (-1)
+    with a message, the reference's `exit(1)` paths (EDSBWTsearch.cpp:183-185, 200-203) turned into return codes."""
+    L = eb.lib()
+    d = str(tmp_path)                                   # a directory is not a pattern file
+    b, o, n = C.c_void_p(), C.c_void_p(), C.c_uint32(7)
+    for bad in (d, os.path.join(d, "missing.txt")):
+        rc = L.edsbwt_read_patterns(bad.encode(), C.byref(b), C.byref(o), C.byref(n))
+        assert rc == -1 and n.value == 7 and not b and not o
+        assert os.path.basename(bad) in L.edsbwt_last_error().decode()
+    src = str(tmp_path / "in.eds")
+    open(src, "wb").write(b"{AC}{G,T}{A}")
+    assert L.edsbwt_string_check(src.encode(), os.path.join(d, "no_such_dir", "out.eds").encode()) == -1
+    assert L.edsbwt_string_check(d.encode(), os.path.join(d, "out.eds").encode()) == -1
+    occ = np.zeros(1, dtype=eb.OCC_DTYPE)
+    rc = L.edsbwt_write_csv(os.path.join(d, "no_such_dir", "o.csv").encode(), occ.ctypes.data, 1, 0, 0, 0)
+    assert rc == -1 and "o.csv" in L.edsbwt_last_error().decode()
+    if os.path.exists("/dev/full"):                     # a write that fails after a successful open
+        rc = L.edsbwt_write_csv(b"/dev/full", occ.ctypes.data, 1, 0, 0, 0)
+        assert rc == -1
+
+
+def test_empty_pattern_file(eb, tmp_path):
+    pf = str(tmp_path / "empty.txt")
+    open(pf, "wb").close()
+    data, off = eb.read_patterns(pf)
+    assert off.tolist() == [0] and len(data) == 0
