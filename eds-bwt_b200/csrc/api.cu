@@ -29,13 +29,14 @@ int edsbwt_index_open_ex(const char* base, int device, const edsbwt_open_opts* o
     if (rc) return rc;
     edsbwt_open_opts o{}; o.seed_k = -1; o.locate_mode = EDSBWT_LOCATE_SA; o.verify = 1;
     if (opts) o = *opts;
-    edsbwt_index* h = new edsbwt_index;
+    edsbwt_index* h = nullptr;
     rc = guarded([&] {
+        h = new edsbwt_index;
         h->ix.device = device;
         load_host_index(base, o.verify != 0, h->ix.host);
         build_device_index(h->ix, o);
     });
-    if (rc) { delete h; return rc; }
+    if (rc) { cudaSetDevice(device); delete h; return rc; }
     *out = h;
     return EDSBWT_OK;
 }
@@ -79,10 +80,13 @@ int edsbwt_search_device_at(edsbwt_index* idx, const uint8_t* d_pat_bytes, const
                             uint64_t total_bytes, uint32_t max_len, int locate, int lf_variant, uint32_t pat_base, edsbwt_result** res) {
     if (!idx || !res || (npat && (!d_pat_off))) return EDSBWT_E_ARG;
     *res = nullptr;
-    edsbwt_result* r = new edsbwt_result; r->device = idx->ix.device; r->pool = idx->ix.pool; r->outp = r->pool->get();
-    r->outp->want_alive = false;
-    int rc = guarded([&] { run_search(idx->ix, d_pat_bytes, d_pat_off, npat, total_bytes, max_len, locate != 0, lf_variant, *r->outp, pat_base); });
-    if (rc) { cudaSetDevice(idx->ix.device); r->pool->put(r->outp); delete r; return rc; }
+    edsbwt_result* r = nullptr;
+    int rc = guarded([&] {
+        r = new edsbwt_result; r->device = idx->ix.device; r->pool = idx->ix.pool; r->outp = r->pool->get();
+        r->outp->want_alive = false;
+        run_search(idx->ix, d_pat_bytes, d_pat_off, npat, total_bytes, max_len, locate != 0, lf_variant, *r->outp, pat_base);
+    });
+    if (rc) { cudaSetDevice(idx->ix.device); if (r) { if (r->outp) r->pool->put(r->outp); delete r; } return rc; }
     *res = r;
     return EDSBWT_OK;
 }
@@ -138,6 +142,7 @@ static int search_into_impl(edsbwt_index* idx, const uint8_t* pat_bytes, const u
                             uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc) {
     auto off_of = [&](uint32_t i) -> uint64_t { return pat_off ? pat_off[i] : (uint64_t)i * fixed_len; };
     Index& ix = idx->ix;
+    std::lock_guard<std::mutex> call_lock(ix.call_mu);
     CUDA_OK(cudaSetDevice(ix.device));
     Pipe& P = pipe_of(ix);
     // chunk schedule: equal chunks, then a tapered tail (halves down to a quarter chunk) -- the input copies are the long
@@ -301,6 +306,7 @@ int edsbwt_search_to_csv(edsbwt_index* idx, const uint8_t* pat_bytes, const uint
     if (!f) { set_error("ERROR opening file %s to write output", csv_path); return EDSBWT_E_IO; }
     int rc = guarded([&] {
         Index& ix = idx->ix;
+        std::lock_guard<std::mutex> call_lock(ix.call_mu);
         CUDA_OK(cudaSetDevice(ix.device));
         Pipe& P = pipe_of(ix);
         const int saved_order = ix.row_order;

@@ -334,7 +334,8 @@ struct ResultPool {
 struct Index {
     int device = 0;
     cudaStream_t stream = nullptr;
-    std::mutex mu;
+    std::mutex mu;        // one search (run_search / csv emission / move-table build) at a time on the handle's stream and workspace
+    std::mutex call_mu;   // one host-buffer call at a time: the chunk pipeline (Pipe) is per handle; taken before mu, never after
     HostIndex host;       // ebwt bytes dropped after upload
     DevBuf<uint4> occ;
     DevBuf<uint32_t> eof_flat, str_seg, seg_first, seg_low;
@@ -409,4 +410,4 @@ double gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, int it
 }  // namespace edsbwt
 
 struct edsbwt_index { edsbwt::Index ix; };
-struct edsbwt_result { edsbwt::SearchOut* outp; std::shared_ptr<edsbwt::ResultPool> pool; int device; };
+struct edsbwt_result { edsbwt::SearchOut* outp = nullptr; std::shared_ptr<edsbwt::ResultPool> pool; int device = 0; };

@@ -7,6 +7,12 @@
  * EDSBWT_E_* code and never call exit() (the reference exits on every error: EDSBWTsearch.cpp:158-161,
  * 1562-1565).  There is NO CPU fallback: without a CUDA device every compute entry point fails with
  * EDSBWT_E_CUDA.
+ *
+ * Threads: the index data of a handle are immutable after open, but a handle owns ONE compute stream, one
+ * workspace and one chunk pipeline, so calls on the same handle are serialised inside the library (safe from
+ * any number of threads, not concurrent); edsbwt_set_* and edsbwt_last_stats refer to "the last call" and are
+ * the caller's to order.  For concurrency open one handle per GPU (the reference object is not re-entrant at
+ * all: per-pattern state lives in members, EDSBWTsearch.hpp:61-63).  edsbwt_last_error is thread-local.
  */
 #ifndef EDSBWT_H
 #define EDSBWT_H
