@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(HERE, "libedsbwt_cuda.so")
 
 LOCATE_SA, LOCATE_WALK = 0, 1
 LF_RANK, LF_MOVE = 0, 1
-ENGINE_FUSED, ENGINE_LEVELSYNC = 0, 1
+ENGINE_FUSED, ENGINE_LEVELSYNC, ENGINE_FUSED_FLAT = 0, 1, 2      # _FLAT: experimental (include/edsbwt.h)
 ROWS_GROUPED, ROWS_REFERENCE = 0, 1
 
 OCC_DTYPE = np.dtype([("pat", "<u4"), ("str", "<u4"), ("seg", "<u4"), ("idx_in_seg", "<u4"), ("off", "<u4")])

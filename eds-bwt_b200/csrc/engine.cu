@@ -725,6 +725,8 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     CUDA_OK(cudaEventCreate(&ws.ev0)); CUDA_OK(cudaEventCreate(&ws.ev1)); CUDA_OK(cudaEventCreate(&ws.evk0)); CUDA_OK(cudaEventCreate(&ws.evk1));
     CUDA_OK(cudaEventCreate(&ws.evf0)); CUDA_OK(cudaEventCreate(&ws.evf1)); CUDA_OK(cudaEventCreate(&ws.evl0)); CUDA_OK(cudaEventCreate(&ws.evl1));
     ix.engine = o.engine == EDSBWT_ENGINE_LEVELSYNC ? EDSBWT_ENGINE_LEVELSYNC : EDSBWT_ENGINE_FUSED;
+    { const char* e = getenv("EDSBWT_FUSED_FLAT");      // A/B switch of the experimental warp-flat first pass (fused.cu)
+      ix.fused_flat = o.engine == EDSBWT_ENGINE_FUSED_FLAT || (ix.engine == EDSBWT_ENGINE_FUSED && e && e[0] == '1'); }
     ix.fused_cap = o.fused_cap > 0 ? (uint32_t)o.fused_cap : 13u;       // 13 slots: 12 CTAs/SM (40 registers) and >= 60 KB of L1 left (A/B: profiles/r01_ab_keep_sort_sizes.txt)
     ix.fused_cap_auto = o.fused_cap <= 0;
     if (ix.fused_cap < 4) ix.fused_cap = 4;
@@ -952,7 +954,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             const uint32_t cap2 = move ? std::min<uint32_t>(ix.fused_cap2, FUSED_BIG_CAP / 2) : ix.fused_cap2;
             if (move) { MoveOut mo{fo.plist, fo.counts, fo.staging, fo.staging_cap, fo.cursor, fo.ovf_count, fo.ovf_ids};
                         launch_move_search(ix.view, ix.move->view, sv, k_eff, d_bytes, d_off, nullptr, npat, ix.lut.p, cap1, mo, s); }
-            else launch_fused_search(ix.view, sv, k_eff, d_bytes, d_off, nullptr, npat, ix.lut.p, cap1, fo, st, ix.canonical_k, s);
+            else launch_fused_search(ix.view, sv, k_eff, d_bytes, d_off, nullptr, npat, ix.lut.p, cap1, fo, st, ix.canonical_k, s, ix.fused_flat);
             CUDA_OK(cudaEventRecord(ws.evf1, s));
             ws.launches += 1; fused_ran = true;
             CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 8, cudaMemcpyDeviceToHost, s));

@@ -361,6 +361,7 @@ struct Index {
     edsbwt_stats last{};
     int collect_counters = 0; uint32_t canonical_k = 12;
     int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 13, fused_cap2 = FUSED_BIG_CAP;
+    bool fused_flat = false;            // experimental warp-flat first pass (EDSBWT_ENGINE_FUSED_FLAT)
     bool fused_cap_auto = true;         // no explicit fused_cap: a batch that overflows the default slots in > 0.1 % of its patterns switches later batches to 20
     uint64_t device_bytes() const;
     ~Index();
@@ -387,7 +388,8 @@ struct FusedOut {
     uint32_t* alive;        // optional [npat]: longest pattern suffix with a non-empty frontier (edsbwt_search_trace)
 };
 void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
-                         const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s);
+                         const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s,
+                         bool flat = false);
 
 // move.cu
 void build_move_table(Index& ix);

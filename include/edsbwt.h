@@ -65,6 +65,9 @@ typedef struct {
 #define EDSBWT_LOCATE_WALK  1   /* LF-walk each row to its string start (the reference's a9/a13 arithmetic)  */
 #define EDSBWT_ENGINE_FUSED     0   /* one thread per pattern, one launch; oversized frontiers fall through to: */
 #define EDSBWT_ENGINE_LEVELSYNC 1   /* level-synchronous interval-parallel engine (also builds the seed table)   */
+#define EDSBWT_ENGINE_FUSED_FLAT 2  /* EXPERIMENTAL, not yet timed: ENGINE_FUSED whose first pass fetches the Occ  */
+                                    /* blocks of a warp's 32 frontiers laid end to end; also */
+                                    /* selected for ENGINE_FUSED handles by the environment variable EDSBWT_FUSED_FLAT=1 */
 #define EDSBWT_LF_RANK      0   /* EDSBWTsearch:      LF by blocked rank                                      */
 #define EDSBWT_LF_MOVE      1   /* MOVE_EDSBWTSearch: LF by move table                                        */
 
@@ -77,7 +80,7 @@ typedef struct {
     int32_t  locate_mode;       /* EDSBWT_LOCATE_SA / _WALK                                                   */
     int32_t  verify;            /* 1 = cross-check _bv_<p>.aux (rrr) and tableOcc against the pile bytes      */
     int32_t  build_move;        /* 1 = also build the move table (EDSBWT_LF_MOVE searches)                    */
-    int32_t  engine;            /* EDSBWT_ENGINE_FUSED (default) / _LEVELSYNC                                 */
+    int32_t  engine;            /* EDSBWT_ENGINE_FUSED (default) / _LEVELSYNC / _FUSED_FLAT                   */
     int32_t  fused_cap;         /* frontier slots per pattern of the fused kernel (0 = default 13: 12 CTAs per SM; above 14: 10 CTAs) */
     int32_t  fused_cap2;        /* slots of the second pass over the patterns that outgrew the first (0 = 192) */
     int32_t  move_a;            /* balancing parameter a of the move table (build_MLF's <a>); 0 = default 8             */

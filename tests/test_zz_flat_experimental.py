@@ -1,0 +1,57 @@
+"""Parity of the EXPERIMENTAL warp-flat first pass of the fused kernel (EDSBWT_ENGINE_FUSED_FLAT)
+against the oracle.  The kernel was written at the end of round 1 without a GPU at hand: it is opt-in in the library and
+these tests are opt-in too (EDSBWT_TEST_FLAT=1), so that the default `pytest -m gpu` run judges only measured code."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+
+from conftest import golden_names, load_golden
+from oracle import eds_index as E
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("EDSBWT_TEST_FLAT") != "1", reason="experimental kernel: set EDSBWT_TEST_FLAT=1")]
+
+
+@pytest.fixture(scope="module")
+def eb():
+    return importlib.import_module("eds-bwt_b200")
+
+
+@pytest.mark.parametrize("name", golden_names())
+@pytest.mark.parametrize("seed_k,cap", [(-1, 0), (1, 0), (2, 5), (3, 14)])
+def test_flat_golden(eb, tmp_path, name, seed_k, cap):
+    g = load_golden(name)
+    base = str(tmp_path / "idx")
+    E.write_index(E.build_index(E.parse_eds(g["eds"])), base)
+    with eb.Index(base, seed_k=seed_k, engine=eb.ENGINE_FUSED_FLAT, fused_cap=cap) as idx:
+        counts, occ = idx.search(g["patterns"], locate=True)
+        assert counts.tolist() == g["counts"]
+        assert eb.occ_rows(occ) == sorted(g["rows_reference_order"])
+        _, pos = idx.search_trace(g["patterns"])
+        assert pos.tolist() == g["interrupted"]
+
+
+@pytest.mark.parametrize("seed,kw,seed_k,cap", [
+    (31, dict(n_seg=300, max_var=5, max_len=5, p_empty=0.3), 2, 0),
+    (32, dict(n_seg=2000, max_var=4, max_len=6, p_empty=0.15, nondeg_len=(1, 40)), 4, 0),
+    (33, dict(n_seg=1200, max_var=8, max_len=3, p_empty=0.45, nondeg_len=(1, 3)), 3, 0),     # '#' everywhere: queue overflows
+    (34, dict(n_seg=5000, max_var=3, max_len=8, p_empty=0.1, nondeg_len=(5, 120)), -1, 6),
+])
+def test_flat_random_vs_port(eb, oracle_built, tmp_path, seed, kw, seed_k, cap):
+    rng = np.random.default_rng(seed)
+    segs = E.random_eds(rng, **kw)
+    base = str(tmp_path / "idx")
+    E.write_index(E.build_index(segs), base)
+    pats = E.sample_patterns(rng, segs, 3000, [1, 2, 3, 5, 8, 13, 21, 32, 50, 64, 100]) + [b"ACGNT", b"#A", b"A" * 300]
+    pf = str(tmp_path / "p.txt")
+    E.write_patterns(pf, pats)
+    c_port, rows_port, _ = oracle_built.run_port(base, pf, locate=True)
+    with eb.Index(base, seed_k=seed_k, engine=eb.ENGINE_FUSED_FLAT, fused_cap=cap) as idx:
+        counts, occ = idx.search(pats, locate=True)
+        assert counts.tolist() == c_port
+        assert eb.occ_rows(occ) == sorted(rows_port)
+    with eb.Index(base, seed_k=seed_k, engine=eb.ENGINE_FUSED, fused_cap=cap) as idx:          # and the shipped kernel agrees
+        counts0, occ0 = idx.search(pats, locate=True)
+        assert np.array_equal(counts0, counts) and eb.occ_rows(occ0) == eb.occ_rows(occ)
