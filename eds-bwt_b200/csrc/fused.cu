@@ -98,9 +98,10 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         // owner-serial bookkeeping (compaction, merge, Dol set, prepend) as the loop below, but the expensive part of a step --
         // the Occ fetch and the popcounts of every interval -- is done over the warp's 32 frontiers laid end to end: lane l
         // maps item first + l whoever owns it, so lanes whose own pattern is dead or short keep fetching for the others.
-        static_assert(!STATS, "the warp-flat loop does not count");
         __shared__ uint4 s_queue[FUSED_THREADS / 32][FLAT_QCAP];          // (owner lane, '#' ranks before / after the interval)
         __shared__ uint32_t s_punt[FUSED_THREADS / 32];
+        __shared__ uint32_t s_E[STATS ? FUSED_THREADS : 1];               // counting runs: end-markers met by the owner's intervals in this step
+        if (STATS) s_E[threadIdx.x] = 0;
         constexpr uint32_t FULL = 0xffffffffu;
         const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5, wcol = threadIdx.x & ~31u;
         // insertion of the pile-0 range [l, h] into the owner's sorted, merged Dol set (top of its column); nkeep = entries of
@@ -148,6 +149,7 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
                     lf_range(ix.occ, iv.x, iv.y + 1, oc, x0, x1, rca, rcb, rda, rdb, nblk);
                     const uint32_t Cc = s_Cl[oc];
                     slot = rcb > rca ? make_uint2(Cc + rca, Cc + rcb - 1) : make_uint2(1u, 0u);
+                    if (STATS) { sBlk += nblk; if (rdb > rda) atomicAdd(&s_E[wcol + own], rdb - rda); }       // blocks: counted where they are fetched
                 }
                 if (queue) {
                     const bool hasd = rdb > rda;
@@ -176,12 +178,15 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
                 }
                 c = (int)((win >> (2 * (ci - win_lo))) & 3u);
             }
+            const bool beyond = STATS && act && (L0 + s >= kc);
+            if (STATS && act && L0 + s == mk) sI += nF;
             if (lane == 0) s_punt[wid] = 0;
             // ---- pass 1: F' = LF_c(F), fetched flat, then compacted / merged by its owner
             uint32_t nq = flat_sweep(act ? nF : 0u, c, false, true);
             if (nq > FLAT_QCAP) { if ((s_punt[wid] >> lane) & 1u) ovf = true; nq = FLAT_QCAP; }
             uint32_t nout = 0, ndol = 0;
             if (act && !ovf) {
+                if (STATS) { sLF += nF; if (beyond) sS += nF; }
                 for (uint32_t j = 0; j < nF; ++j) {
                     const uint2 r = LIST(j);
                     if (r.x > r.y) continue;
@@ -202,6 +207,7 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
             if (__any_sync(FULL, myD != 0)) {
                 flat_sweep(myD, c, true, false);
                 if (myD) {
+                    if (STATS) { sLF += ndol; if (beyond) sS += ndol; }
                     uint32_t ndp = 0;
                     for (uint32_t i = 0; i < ndol; ++i) {
                         const uint2 r = DOL(i);
@@ -219,6 +225,7 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
                     }
                 }
             }
+            if (STATS) { if (beyond) sE += s_E[threadIdx.x]; s_E[threadIdx.x] = 0; }
             if (act && !ovf) { nF = nout; ++s; }
             __syncwarp();                                  // s_punt / s_queue are rewritten by the next step
         }
@@ -326,6 +333,8 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         if (ovf) out.ovf_ids[atomicAdd(out.ovf_count, 1u)] = q;
     }
     if (STATS) {
+        if constexpr (FLAT) { if (ovf) sI = sS = sE = sLF = 0; }     // the blocks a lane fetched belong to other lanes' patterns: kept
+        else
         if (ovf) sI = sS = sE = sLF = sBlk = 0;          // the level-synchronous engine redoes (and recounts) this pattern
         const unsigned long long v[5] = {sI, sS, sE, sLF, sBlk};
         unsigned long long* dst[5] = {&st->I, &st->S, &st->E, &st->lf_intervals, &st->occ_blocks};
@@ -345,9 +354,14 @@ void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, co
     if (npat == 0) return;
     const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
     const unsigned grid = (npat + FUSED_THREADS - 1) / FUSED_THREADS;
-    if (flat && !st && cap <= 14) {      // experimental warp-flat step loop: first pass of non-counting runs only
-        CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false, FLAT_MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        fused_search_kernel<false, FLAT_MINB, true><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+    if (flat && cap <= 14) {             // experimental warp-flat step loop: first pass only
+        if (st) {
+            CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<true, FLAT_MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            fused_search_kernel<true, FLAT_MINB, true><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+        } else {
+            CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false, FLAT_MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            fused_search_kernel<false, FLAT_MINB, true><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+        }
     } else if (st) {
         CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<true, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
         fused_search_kernel<true, 10><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);

@@ -47,11 +47,18 @@ def test_flat_random_vs_port(eb, oracle_built, tmp_path, seed, kw, seed_k, cap):
     pats = E.sample_patterns(rng, segs, 3000, [1, 2, 3, 5, 8, 13, 21, 32, 50, 64, 100]) + [b"ACGNT", b"#A", b"A" * 300]
     pf = str(tmp_path / "p.txt")
     E.write_patterns(pf, pats)
-    c_port, rows_port, _ = oracle_built.run_port(base, pf, locate=True)
     with eb.Index(base, seed_k=seed_k, engine=eb.ENGINE_FUSED_FLAT, fused_cap=cap) as idx:
+        k = idx.info().seed_k
+        c_port, rows_port, st_port = oracle_built.run_port(base, pf, locate=True, k=k)
         counts, occ = idx.search(pats, locate=True)
         assert counts.tolist() == c_port
         assert eb.occ_rows(occ) == sorted(rows_port)
+        idx.set_stats(True, canonical_k=k)                     # counting instantiation of the flat loop: byte-model counters
+        counts1, occ1 = idx.search(pats, locate=True)
+        st = idx.last_stats()
+        assert counts1.tolist() == c_port and eb.occ_rows(occ1) == sorted(rows_port)
+        for key in "ISELO":
+            assert st[key] == st_port[key], (key, st[key], st_port[key])
     with eb.Index(base, seed_k=seed_k, engine=eb.ENGINE_FUSED, fused_cap=cap) as idx:          # and the shipped kernel agrees
         counts0, occ0 = idx.search(pats, locate=True)
         assert np.array_equal(counts0, counts) and eb.occ_rows(occ0) == eb.occ_rows(occ)
