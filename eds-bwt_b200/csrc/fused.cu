@@ -350,7 +350,7 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
 
 void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
                          const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s,
-                         bool flat) {
+                         int flat) {
     if (npat == 0) return;
     const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
     const unsigned grid = (npat + FUSED_THREADS - 1) / FUSED_THREADS;
@@ -358,6 +358,9 @@ void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, co
         if (st) {
             CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<true, FLAT_MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
             fused_search_kernel<true, FLAT_MINB, true><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+        } else if (flat == 2) {           // A/B: the 12 CTAs/SM register budget of the shipped instantiation
+            CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false, 12, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            fused_search_kernel<false, 12, true><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
         } else {
             CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false, FLAT_MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
             fused_search_kernel<false, FLAT_MINB, true><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
