@@ -455,7 +455,7 @@ def main():
             "dtype": "u32", "data": "synthetic",
             "config": {"workload": workload_name(args), "index_rows": info.n, "strings": info.n_text, "segments": info.n_seg,
                        "patterns_per_gpu": args.npat, "pattern_len": args.plen, "seed_k": info.seed_k, "locate": "sa-table",
-                       "fused_kernel": "warp-flat (experimental, EDSBWT_FUSED_FLAT=%s)" % os.environ["EDSBWT_FUSED_FLAT"] if os.environ.get("EDSBWT_FUSED_FLAT") in ("1", "2") else "step-loop",
+                       "fused_kernel": "warp-flat (experimental, EDSBWT_FUSED_FLAT=%s)" % os.environ["EDSBWT_FUSED_FLAT"] if os.environ.get("EDSBWT_FUSED_FLAT") in ("1", "2", "3") else "step-loop",
                        "parallelism": "patterns sharded x%d, index replicated" % world,
                        "l2": "inputs larger than L2 (patterns %.0f MB + index %.2f GB per step; no flush needed)" % (data.nbytes / 1e6, info.device_bytes / 1e9)},
             "wall_ms_per_step": wall_ms_max / args.steps,

@@ -726,7 +726,7 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     CUDA_OK(cudaEventCreate(&ws.evf0)); CUDA_OK(cudaEventCreate(&ws.evf1)); CUDA_OK(cudaEventCreate(&ws.evl0)); CUDA_OK(cudaEventCreate(&ws.evl1));
     ix.engine = o.engine == EDSBWT_ENGINE_LEVELSYNC ? EDSBWT_ENGINE_LEVELSYNC : EDSBWT_ENGINE_FUSED;
     { const char* e = getenv("EDSBWT_FUSED_FLAT");      // A/B switch of the experimental warp-flat first pass (fused.cu)
-      ix.fused_flat = (ix.engine == EDSBWT_ENGINE_FUSED && e && (e[0] == '1' || e[0] == '2')) ? e[0] - '0' : (o.engine == EDSBWT_ENGINE_FUSED_FLAT ? 1 : 0); }
+      ix.fused_flat = (ix.engine == EDSBWT_ENGINE_FUSED && e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : (o.engine == EDSBWT_ENGINE_FUSED_FLAT ? 1 : 0); }
     ix.fused_cap = o.fused_cap > 0 ? (uint32_t)o.fused_cap : 13u;       // 13 slots: 12 CTAs/SM (40 registers) and >= 60 KB of L1 left (A/B: profiles/r01_ab_keep_sort_sizes.txt)
     ix.fused_cap_auto = o.fused_cap <= 0;
     if (ix.fused_cap < 4) ix.fused_cap = 4;

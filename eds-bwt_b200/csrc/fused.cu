@@ -28,7 +28,8 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 constexpr int FLAT_MINB = 10;          // CTAs per SM the warp-flat instantiation is compiled for
 constexpr uint32_t FLAT_QCAP = 8;      // '#'-carrying intervals one warp may meet in one step before their patterns are handed on
 
-template <bool STATS, int MINB, bool FLAT = false>
+// FLAT: 0 = the shipped step loop; 1 = warp-flat Occ fetch; 2 = 1 + the link records of a step gathered by the warp in one go
+template <bool STATS, int MINB, int FLAT = 0>
 __global__ void __launch_bounds__(FUSED_THREADS, MINB)
 fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant__ SeedView sv, uint32_t k, const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ poff,
                     const uint32_t* __restrict__ ids, uint32_t npat, const uint8_t* __restrict__ lut, uint32_t cap, FusedOut out,
@@ -93,13 +94,14 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     const uint32_t steps = m - L0;
     const uint32_t mk = m < kc ? m : kc;
     uint32_t s = 0;
-    if constexpr (FLAT) {
+    if constexpr (FLAT != 0) {
         // ---- EXPERIMENTAL warp-flat step loop (EDSBWT_ENGINE_FUSED_FLAT).  Same frontier columns, same
         // owner-serial bookkeeping (compaction, merge, Dol set, prepend) as the loop below, but the expensive part of a step --
         // the Occ fetch and the popcounts of every interval -- is done over the warp's 32 frontiers laid end to end: lane l
         // maps item first + l whoever owns it, so lanes whose own pattern is dead or short keep fetching for the others.
         __shared__ uint4 s_queue[FUSED_THREADS / 32][FLAT_QCAP];          // (owner lane, '#' ranks before / after the interval)
         __shared__ uint32_t s_punt[FUSED_THREADS / 32];
+        __shared__ uint2 s_qrec[FLAT == 2 ? FUSED_THREADS / 32 : 1][FLAT_QCAP];   // FLAT 2: link record of the first '#' of each queued interval
         __shared__ uint32_t s_E[STATS ? FUSED_THREADS : 1];               // counting runs: end-markers met by the owner's intervals in this step
         if (STATS) s_E[threadIdx.x] = 0;
         constexpr uint32_t FULL = 0xffffffffu;
@@ -184,6 +186,13 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
             // ---- pass 1: F' = LF_c(F), fetched flat, then compacted / merged by its owner
             uint32_t nq = flat_sweep(act ? nF : 0u, c, false, true);
             if (nq > FLAT_QCAP) { if ((s_punt[wid] >> lane) & 1u) ovf = true; nq = FLAT_QCAP; }
+            if constexpr (FLAT == 2) {
+                // one gather for the whole warp instead of one dependent wait per owner (a range rarely holds a second '#')
+                if (nq) {
+                    if (lane < nq) s_qrec[wid][lane] = __ldg(ix.link_rec + s_queue[wid][lane].y);
+                    __syncwarp();
+                }
+            }
             uint32_t nout = 0, ndol = 0;
             if (act && !ovf) {
                 if (STATS) { sLF += nF; if (beyond) sS += nF; }
@@ -197,7 +206,7 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
                     const uint4 qe = s_queue[wid][t];
                     if (qe.x != lane) continue;
                     for (uint32_t e = qe.y; e < qe.z && !ovf; ++e) {
-                        const uint2 rec = __ldg(ix.link_rec + e);
+                        const uint2 rec = (FLAT == 2 && e == qe.y) ? s_qrec[wid][t] : __ldg(ix.link_rec + e);
                         if (rec.x <= rec.y) dol_insert(rec.x, rec.y, nout, ndol);          // x > y: string of the first segment
                     }
                 }
@@ -333,7 +342,7 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         if (ovf) out.ovf_ids[atomicAdd(out.ovf_count, 1u)] = q;
     }
     if (STATS) {
-        if constexpr (FLAT) { if (ovf) sI = sS = sE = sLF = 0; }     // the blocks a lane fetched belong to other lanes' patterns: kept
+        if constexpr (FLAT != 0) { if (ovf) sI = sS = sE = sLF = 0; }     // the blocks a lane fetched belong to other lanes' patterns: kept
         else
         if (ovf) sI = sS = sE = sLF = sBlk = 0;          // the level-synchronous engine redoes (and recounts) this pattern
         const unsigned long long v[5] = {sI, sS, sE, sLF, sBlk};
@@ -348,33 +357,34 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
 #undef DOL
 }
 
+namespace {
+template <bool STATS, int MINB, int FLAT>
+void launch_instance(unsigned grid, size_t smem, cudaStream_t s, const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
+                     const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc) {
+    CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<STATS, MINB, FLAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
+    fused_search_kernel<STATS, MINB, FLAT><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+}
+}  // namespace
+
+// flat (experimental first pass, A/B values of EDSBWT_FUSED_FLAT): 1 = warp-flat fetch at 10 CTAs/SM, 2 = the same compiled for
+// 12 CTAs/SM, 3 = warp-flat fetch + warp-wide link gather at 10 CTAs/SM.  Counting runs use the 10 CTAs/SM builds.
 void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
                          const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s,
                          int flat) {
     if (npat == 0) return;
     const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
     const unsigned grid = (npat + FUSED_THREADS - 1) / FUSED_THREADS;
-    if (flat && cap <= 14) {             // experimental warp-flat step loop: first pass only
-        if (st) {
-            CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<true, FLAT_MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            fused_search_kernel<true, FLAT_MINB, true><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
-        } else if (flat == 2) {           // A/B: the 12 CTAs/SM register budget of the shipped instantiation
-            CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false, 12, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            fused_search_kernel<false, 12, true><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
-        } else {
-            CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false, FLAT_MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            fused_search_kernel<false, FLAT_MINB, true><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
-        }
-    } else if (st) {
-        CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<true, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
-        fused_search_kernel<true, 10><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
-    } else if (cap <= 14) {              // 12 CTAs/SM: 40 registers (40 B of spill in a cold path), at most 14 KB of frontier each; 3.27 -> 3.09 ms
-        CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        fused_search_kernel<false, 12><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
-    } else {
-        CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<false, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        fused_search_kernel<false, 10><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+#define INSTANCE(STATS, MINB, FLAT) launch_instance<STATS, MINB, FLAT>(grid, smem, s, ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc)
+    if (flat && cap <= 14) {             // experimental: first pass only
+        if (st) { if (flat == 3) INSTANCE(true, FLAT_MINB, 2); else INSTANCE(true, FLAT_MINB, 1); }
+        else if (flat == 3) INSTANCE(false, FLAT_MINB, 2);
+        else if (flat == 2) INSTANCE(false, 12, 1);
+        else INSTANCE(false, FLAT_MINB, 1);
     }
+    else if (st) INSTANCE(true, 10, 0);
+    else if (cap <= 14) INSTANCE(false, 12, 0);      // 12 CTAs/SM: 40 registers (40 B of spill in a cold path), at most 14 KB of frontier each; 3.27 -> 3.09 ms
+    else INSTANCE(false, 10, 0);
+#undef INSTANCE
     CUDA_OK(cudaGetLastError());
 }
 

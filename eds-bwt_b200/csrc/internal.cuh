@@ -361,7 +361,7 @@ struct Index {
     edsbwt_stats last{};
     int collect_counters = 0; uint32_t canonical_k = 12;
     int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 13, fused_cap2 = FUSED_BIG_CAP;
-    int fused_flat = 0;                 // experimental warp-flat first pass (EDSBWT_ENGINE_FUSED_FLAT); 2 = its 12 CTAs/SM build
+    int fused_flat = 0;                 // experimental warp-flat first pass (EDSBWT_ENGINE_FUSED_FLAT); 2, 3 = its A/B variants
     bool fused_cap_auto = true;         // no explicit fused_cap: a batch that overflows the default slots in > 0.1 % of its patterns switches later batches to 20
     uint64_t device_bytes() const;
     ~Index();
@@ -389,7 +389,7 @@ struct FusedOut {
 };
 void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
                          const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s,
-                         int flat = 0);      // 1 / 2: experimental warp-flat first pass compiled for 10 / 12 CTAs per SM
+                         int flat = 0);      // 1..3: experimental warp-flat first pass (variants: fused.cu)
 
 // move.cu
 void build_move_table(Index& ix);

@@ -67,7 +67,7 @@ typedef struct {
 #define EDSBWT_ENGINE_LEVELSYNC 1   /* level-synchronous interval-parallel engine (also builds the seed table)   */
 #define EDSBWT_ENGINE_FUSED_FLAT 2  /* EXPERIMENTAL, not yet timed: ENGINE_FUSED whose first pass fetches the Occ  */
                                     /* blocks of a warp's 32 frontiers laid end to end; also */
-                                    /* selected for ENGINE_FUSED handles by the environment variable EDSBWT_FUSED_FLAT=1 (=2: 12 CTAs/SM build) */
+                                    /* selected for ENGINE_FUSED handles by the environment variable EDSBWT_FUSED_FLAT=1 (2, 3: A/B variants, fused.cu) */
 #define EDSBWT_LF_RANK      0   /* EDSBWTsearch:      LF by blocked rank                                      */
 #define EDSBWT_LF_MOVE      1   /* MOVE_EDSBWTSearch: LF by move table                                        */
 

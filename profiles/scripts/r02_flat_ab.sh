@@ -1,9 +1,9 @@
 # Round 2, first GPU call: the experimental warp-flat first pass (fused.cu, FLAT = true) against the shipped kernel.
 #   gpurun --timeout 900 -- 'bash profiles/scripts/r02_flat_ab.sh'
-# 1. parity incl. the counting instantiation (never run in round 1), 2. A/B of the bench at cfg4, 3. one ncu capture of the flat kernel.
+# 1. parity of the three variants incl. their counting instantiations (only variant 1, non-counting, ran in round 1), 2. A/B of the bench at cfg4, 3. one ncu capture of the flat kernel.
 mkdir -p gpurun_out
 EDSBWT_TEST_FLAT=1 python -m pytest tests/test_zz_flat_experimental.py -m gpu -x -q > gpurun_out/r02_flat_parity.log 2>&1; tail -3 gpurun_out/r02_flat_parity.log
-for v in 0 1 2; do      # 0 shipped step loop, 1 warp-flat at 10 CTAs/SM (48 registers), 2 warp-flat at 12 CTAs/SM (40 registers, 120 B of spills)
+for v in 0 1 2 3; do    # 0 shipped step loop, 1 warp-flat at 10 CTAs/SM (48 registers), 2 warp-flat at 12 CTAs/SM (40 registers, 120 B of spills), 3 = 1 + warp-wide link gather
   EDSBWT_FUSED_FLAT=$v python bench.py --no-cpu --steps 20 > gpurun_out/r02_bench_flat$v.json 2> gpurun_out/r02_bench_flat$v.err
   python - <<PY
 import json

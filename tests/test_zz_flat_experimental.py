@@ -14,9 +14,17 @@ pytestmark = [pytest.mark.gpu,
               pytest.mark.skipif(os.environ.get("EDSBWT_TEST_FLAT") != "1", reason="experimental kernel: set EDSBWT_TEST_FLAT=1")]
 
 
-@pytest.fixture(scope="module")
-def eb():
-    return importlib.import_module("eds-bwt_b200")
+@pytest.fixture(scope="module", params=["1", "2", "3"])
+def eb(request):
+    """EDSBWT_FUSED_FLAT variants (fused.cu): 1 = warp-flat fetch at 10 CTAs/SM (the one run green at the end of round 1),
+    2 = the same compiled for 12 CTAs/SM, 3 = + warp-wide link gather.  The variable is read when an index is opened."""
+    old = os.environ.get("EDSBWT_FUSED_FLAT")
+    os.environ["EDSBWT_FUSED_FLAT"] = request.param
+    yield importlib.import_module("eds-bwt_b200")
+    if old is None:
+        os.environ.pop("EDSBWT_FUSED_FLAT", None)
+    else:
+        os.environ["EDSBWT_FUSED_FLAT"] = old
 
 
 @pytest.mark.parametrize("name", golden_names())
@@ -25,7 +33,7 @@ def test_flat_golden(eb, tmp_path, name, seed_k, cap):
     g = load_golden(name)
     base = str(tmp_path / "idx")
     E.write_index(E.build_index(E.parse_eds(g["eds"])), base)
-    with eb.Index(base, seed_k=seed_k, engine=eb.ENGINE_FUSED_FLAT, fused_cap=cap) as idx:
+    with eb.Index(base, seed_k=seed_k, engine=eb.ENGINE_FUSED, fused_cap=cap) as idx:        # flat via the environment variable
         counts, occ = idx.search(g["patterns"], locate=True)
         assert counts.tolist() == g["counts"]
         assert eb.occ_rows(occ) == sorted(g["rows_reference_order"])
@@ -47,7 +55,7 @@ def test_flat_random_vs_port(eb, oracle_built, tmp_path, seed, kw, seed_k, cap):
     pats = E.sample_patterns(rng, segs, 3000, [1, 2, 3, 5, 8, 13, 21, 32, 50, 64, 100]) + [b"ACGNT", b"#A", b"A" * 300]
     pf = str(tmp_path / "p.txt")
     E.write_patterns(pf, pats)
-    with eb.Index(base, seed_k=seed_k, engine=eb.ENGINE_FUSED_FLAT, fused_cap=cap) as idx:
+    with eb.Index(base, seed_k=seed_k, engine=eb.ENGINE_FUSED, fused_cap=cap) as idx:        # flat via the environment variable
         k = idx.info().seed_k
         c_port, rows_port, st_port = oracle_built.run_port(base, pf, locate=True, k=k)
         counts, occ = idx.search(pats, locate=True)
@@ -59,6 +67,26 @@ def test_flat_random_vs_port(eb, oracle_built, tmp_path, seed, kw, seed_k, cap):
         assert counts1.tolist() == c_port and eb.occ_rows(occ1) == sorted(rows_port)
         for key in "ISELO":
             assert st[key] == st_port[key], (key, st[key], st_port[key])
-    with eb.Index(base, seed_k=seed_k, engine=eb.ENGINE_FUSED, fused_cap=cap) as idx:          # and the shipped kernel agrees
-        counts0, occ0 = idx.search(pats, locate=True)
-        assert np.array_equal(counts0, counts) and eb.occ_rows(occ0) == eb.occ_rows(occ)
+    variant = os.environ.pop("EDSBWT_FUSED_FLAT")
+    try:
+        with eb.Index(base, seed_k=seed_k, engine=eb.ENGINE_FUSED, fused_cap=cap) as idx:      # and the shipped kernel agrees
+            counts0, occ0 = idx.search(pats, locate=True)
+            assert np.array_equal(counts0, counts) and eb.occ_rows(occ0) == eb.occ_rows(occ)
+    finally:
+        os.environ["EDSBWT_FUSED_FLAT"] = variant
+
+
+def test_flat_engine_option(tmp_path):
+    """The open option selects variant 1 without the environment variable."""
+    eb = importlib.import_module("eds-bwt_b200")
+    variant = os.environ.pop("EDSBWT_FUSED_FLAT", None)
+    try:
+        g = load_golden("readme_test")
+        base = str(tmp_path / "idx")
+        E.write_index(E.build_index(E.parse_eds(g["eds"])), base)
+        with eb.Index(base, seed_k=1, engine=eb.ENGINE_FUSED_FLAT) as idx:
+            counts, occ = idx.search(g["patterns"], locate=True)
+            assert counts.tolist() == g["counts"] and eb.occ_rows(occ) == sorted(g["rows_reference_order"])
+    finally:
+        if variant is not None:
+            os.environ["EDSBWT_FUSED_FLAT"] = variant
