@@ -129,6 +129,7 @@ inline int run_cli(int argc, char** argv, bool move) {
     if (move) out.reserve((size_t)npat * 72 + 64);
     std::vector<char> chunk(move ? 0 : (1u << 22));      // EDSBWTsearch: "Found ..." lines leave in 4 MB pieces
     char* w = chunk.data();
+    std::string err;
     char line[160];
     for (uint32_t i = 0; i < npat; ++i) {
         if (move) {
@@ -141,12 +142,17 @@ inline int run_cli(int argc, char** argv, bool move) {
             std::cerr << (counts[i] ? " TROVATA" : " NON TROVATA") << std::endl;                // :124,129
             out.append(line);
         } else {
-            if (!recover && interrupted[i]) std::cerr << "Pattern not found, interrupted in position " << interrupted[i] << "\n";    // :714-717
+            if (!recover && interrupted[i]) {                                                   // :714-717; stderr is unbuffered: one write per 4 MB, not per line
+                char num[12]; char* e = put_u32(num, interrupted[i]); *e++ = '\n';
+                err.append("Pattern not found, interrupted in position ", 43); err.append(num, (size_t)(e - num));
+                if (err.size() > (1u << 22)) { fwrite(err.data(), 1, err.size(), stderr); err.clear(); }
+            }
             w = put_found(w, counts[i], i + 1);
             if ((size_t)(w - chunk.data()) + 96 > chunk.size()) { fwrite(chunk.data(), 1, (size_t)(w - chunk.data()), stdout); w = chunk.data(); }
         }
         if (counts[i] > 0) ++count_found; else ++count_not_found;
     }
+    if (!err.empty()) fwrite(err.data(), 1, err.size(), stderr);
     if (move) fwrite(out.data(), 1, out.size(), stdout);
     else if (w != chunk.data()) fwrite(chunk.data(), 1, (size_t)(w - chunk.data()), stdout);
     fflush(stdout);
