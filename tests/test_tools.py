@@ -110,3 +110,17 @@ def test_extract_patterns_from_msa(tmp_path):
     assert sorted(out.read_text().split("\n")) == sorted(windows)
     with pytest.raises(ValueError):
         X.main([str(msa), str(out), "-l", "4", "-n", "8"])
+
+
+def test_cli_report_formatter(tmp_path):
+    """The executables format "Found N starting positions ..." by hand (10 M lines per batch): same bytes as printf."""
+    sys.path.insert(0, ROOT)
+    import __graft_entry__ as G
+    G.build()
+    exe = str(tmp_path / "cli_format_check")
+    libdir = os.path.join(ROOT, "eds-bwt_b200")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-I", os.path.join(ROOT, "include"), "-o", exe,
+                    os.path.join(ROOT, "tests", "native", "cli_format_check.cpp"), "-L", libdir, "-ledsbwt_cuda",
+                    "-Wl,-rpath," + libdir], check=True)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.strip() == "format ok", r.stdout
