@@ -63,6 +63,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--keep", action="store_true")
     ap.add_argument("--chunk", type=int, default=0, help="patterns per pipeline chunk of the host-buffer search (0 = library default)")
+    ap.add_argument("--engine", default="items", choices=["items", "step"], help="hot kernel: items.cu (default) or the round-1 step-loop kernel (A/B)")
     return ap.parse_args()
 
 
@@ -138,13 +139,13 @@ def workload_name(args):
         args.mbp, args.npat, args.plen)
 
 
-NCU_CAPTURE = "profiles/r01_fused_ncu_full_v7.txt"      # ncu --set full of fused_search_kernel at the default workload (cfg4, k = 14)
+NCU_CAPTURE = "profiles/r02_items_ncu_full.txt"      # ncu --set full of search_items_kernel at the default workload (cfg4, k = 14)
 
 
 def ncu_traffic(args, seed_k):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed ncu capture of
     this same command (only valid for the default workload the capture was taken on)."""
-    if args.mbp != 250 or args.npat != 10000000 or args.plen != 32 or seed_k != 14:
+    if args.mbp != 250 or args.npat != 10000000 or args.plen != 32 or seed_k != 14 or args.engine != "items":
         return None, None
     try:
         tot = 0.0
@@ -300,7 +301,8 @@ def main():
     if world > 1:
         dist.barrier()
     t0 = time.time()
-    idx = eb.Index(base, device=local_rank, seed_k=args.seed_k, verify=False, fused_cap=args.fused_cap, fused_cap2=args.fused_cap2)
+    idx = eb.Index(base, device=local_rank, seed_k=args.seed_k, verify=False, fused_cap=args.fused_cap, fused_cap2=args.fused_cap2,
+                   engine=eb.ENGINE_FUSED if args.engine == "items" else eb.ENGINE_FUSED_STEP)
     info = idx.info()
     log("rank %d: index open in %.1fs: n=%d nText=%d nSeg=%d seed_k=%d seed_intervals=%d device_bytes=%.2f GB" % (
         rank, time.time() - t0, info.n, info.n_text, info.n_seg, info.seed_k, info.seed_intervals, info.device_bytes / 1e9))
@@ -435,10 +437,12 @@ def main():
             pass
         peak = float(peaks.get("hbm_gbs", 6553.6))
         peak_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6553.6 GB/s (B200_PROFILING.md)"
-        # dominant kernel: the LF rank kernel.  Algorithmic bytes = 64 B per distinct Occ block an interval end needs
-        # + the 12 B interval record read + 8 B written; canonical SURVEY model printed next to it.
+        # dominant kernel: the search kernel.  Algorithmic bytes = 64 B per Occ block fetched + 8 B per link
+        # record + 8 B per seed interval read + the pattern itself: 2-bit words and one 8-byte offset per pattern for the item
+        # kernel, the raw bytes and two offsets for the step-loop kernel.  Canonical SURVEY model printed next to it.
         occ_blocks = st_a["occ_blocks"]
-        alg_bytes = 64.0 * occ_blocks + 8.0 * st_a["E"] + (args.plen + 16.0) * args.npat + 8.0 * st_a["I"]
+        pat_bytes = (8.0 * ((args.plen + 31) // 32) + 8.0) if args.engine == "items" else (args.plen + 16.0)
+        alg_bytes = 64.0 * occ_blocks + 8.0 * st_a["E"] + pat_bytes * args.npat + 8.0 * st_a["I"]
         lf_ms_step = lf_ms / args.steps
         achieved = alg_bytes / (lf_ms_step * 1e-3) / 1e9 if lf_ms_step > 0 else 0.0
         traffic, traffic_src = ncu_traffic(args, int(info.seed_k))
@@ -455,7 +459,7 @@ def main():
             "dtype": "u32", "data": "synthetic",
             "config": {"workload": workload_name(args), "index_rows": info.n, "strings": info.n_text, "segments": info.n_seg,
                        "patterns_per_gpu": args.npat, "pattern_len": args.plen, "seed_k": info.seed_k, "locate": "sa-table",
-                       "fused_kernel": "warp-flat (experimental, EDSBWT_FUSED_FLAT=%s)" % os.environ["EDSBWT_FUSED_FLAT"] if os.environ.get("EDSBWT_FUSED_FLAT") in ("1", "2", "3") else "step-loop",
+                       "search_kernel": "search_items_kernel (persistent warps, lane refill)" if args.engine == "items" else "fused_search_kernel (round-1 step loop)",
                        "parallelism": "patterns sharded x%d, index replicated" % world,
                        "l2": "inputs larger than L2 (patterns %.0f MB + index %.2f GB per step; no flush needed)" % (data.nbytes / 1e6, info.device_bytes / 1e9)},
             "wall_ms_per_step": wall_ms_max / args.steps,
@@ -469,7 +473,7 @@ def main():
                        if world > 1 else None),
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "fused_search_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "search_items_kernel" if args.engine == "items" else "fused_search_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "alg_bytes_per_step": alg_bytes, "kernel_ms_per_step": lf_ms_step,
                          "kernel_share_of_step": lf_ms_step / (dev_ms / args.steps) if dev_ms else None,

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(HERE, "libedsbwt_cuda.so")
 
 LOCATE_SA, LOCATE_WALK = 0, 1
 LF_RANK, LF_MOVE = 0, 1
-ENGINE_FUSED, ENGINE_LEVELSYNC, ENGINE_FUSED_FLAT = 0, 1, 2      # _FLAT: experimental (include/edsbwt.h)
+ENGINE_FUSED, ENGINE_LEVELSYNC, ENGINE_FUSED_STEP = 0, 1, 2      # _FUSED: item kernel (default); _FUSED_STEP: the round-1 step-loop kernel as first pass
 ROWS_GROUPED, ROWS_REFERENCE = 0, 1
 
 OCC_DTYPE = np.dtype([("pat", "<u4"), ("str", "<u4"), ("seg", "<u4"), ("idx_in_seg", "<u4"), ("off", "<u4")])
@@ -27,6 +27,7 @@ EXPORTS = [
     "edsbwt_strerror", "edsbwt_last_error", "edsbwt_version", "edsbwt_search_into", "edsbwt_host_alloc", "edsbwt_host_free",
     "edsbwt_set_chunk", "edsbwt_search_trace", "edsbwt_move_table_build", "edsbwt_move_table_fetch", "edsbwt_search_device_at", "edsbwt_gather_bench_ex",
     "edsbwt_set_row_order", "edsbwt_result_write_csv", "edsbwt_search_to_csv", "edsbwt_string_check", "edsbwt_search_into_fixed",
+    "edsbwt_search_into_packed", "edsbwt_pack_patterns", "edsbwt_pack_patterns_alphabet",
 ]
 
 
@@ -87,6 +88,11 @@ def lib():
                                          C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.edsbwt_search_into_fixed.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
                                                C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.edsbwt_search_into_packed.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
+                                                C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.edsbwt_pack_patterns.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]
+        L.edsbwt_pack_patterns_alphabet.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p,
+                                                    C.POINTER(C.c_uint32)]
         L.edsbwt_search_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
         L.edsbwt_move_table_build.argtypes = [C.c_void_p]
         L.edsbwt_move_table_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
@@ -228,6 +234,26 @@ class Index:
                                               occ.ctypes.data if occ is not None else None, len(occ) if occ is not None else 0, C.byref(nocc)))
         return nocc.value
 
+    def pack_patterns(self, data, pat_len, nthreads=1, words=None, invalid=None):
+        """edsbwt_pack_patterns: equal-length pattern bytes -> (uint64 words, uint32 invalid bitmap, number flagged)."""
+        npat = len(data) // pat_len
+        stride = (pat_len + 31) // 32
+        if words is None:
+            words = np.zeros(max(1, npat * stride), np.uint64)
+        if invalid is None:
+            invalid = np.zeros(max(1, (npat + 31) // 32), np.uint32)
+        nbad = C.c_uint32(0)
+        _check(lib().edsbwt_pack_patterns(self._h, data.ctypes.data, pat_len, npat, nthreads, words.ctypes.data, invalid.ctypes.data, C.byref(nbad)))
+        return words, invalid, nbad.value
+
+    def search_into_packed(self, words, invalid, pat_len, npat, counts, occ=None, locate=True, lf_variant=LF_RANK):
+        """The caller's own 2-bit words (layout: include/edsbwt.h); invalid may be None."""
+        nocc = C.c_uint64(0)
+        _check(lib().edsbwt_search_into_packed(self._h, words.ctypes.data, invalid.ctypes.data if invalid is not None else None, pat_len, npat,
+                                               int(locate), lf_variant, counts.ctypes.data, occ.ctypes.data if occ is not None else None,
+                                               len(occ) if occ is not None else 0, C.byref(nocc)))
+        return nocc.value
+
     def set_row_order(self, reference=True):
         """ROWS_REFERENCE: tuples of a pattern in the reference's csv order."""
         _check(lib().edsbwt_set_row_order(self._h, ROWS_REFERENCE if reference else ROWS_GROUPED))
@@ -316,6 +342,19 @@ def pinned_empty(n, dtype):
     buf = (C.c_uint8 * nbytes).from_address(owner.p.value)
     buf._owner = owner          # the ctypes buffer is the base of the array and keeps the allocation alive
     return np.frombuffer(buf, dtype=dtype, count=int(n))
+
+
+def pack_patterns_alphabet(alphabet, data, pat_len, nthreads=1):
+    """edsbwt_pack_patterns_alphabet (host-only, no GPU): alphabet = end-marker byte followed by the letters."""
+    alphabet = np.frombuffer(bytes(alphabet), dtype=np.uint8)
+    data = np.ascontiguousarray(data, dtype=np.uint8)
+    npat = len(data) // pat_len
+    words = np.zeros(max(1, npat * ((pat_len + 31) // 32)), np.uint64)
+    invalid = np.zeros(max(1, (npat + 31) // 32), np.uint32)
+    nbad = C.c_uint32(0)
+    _check(lib().edsbwt_pack_patterns_alphabet(alphabet.ctypes.data, len(alphabet), data.ctypes.data, pat_len, npat, nthreads,
+                                               words.ctypes.data, invalid.ctypes.data, C.byref(nbad)))
+    return words, invalid, nbad.value
 
 
 def occ_rows(occ, pat_base=0):

@@ -10,7 +10,7 @@ LIB = os.path.join(HERE, "libedsbwt_cuda.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-Xptxas", "-v"]
-LIB_SRCS = ["engine.cu", "fused.cu", "move.cu", "api.cu", "gather_bench.cu", "builder.cu", "csv.cu", "host_io.cpp"]
+LIB_SRCS = ["engine.cu", "fused.cu", "items.cu", "move.cu", "api.cu", "gather_bench.cu", "builder.cu", "csv.cu", "host_io.cpp", "pack_host.cc"]
 CLIS = {"EDSBWTsearch": "cli_edsbwtsearch.cpp", "MOVE_EDSBWTSearch": "cli_move_edsbwtsearch.cpp", "stringCheck": "cli_stringcheck.cpp"}
 
 
@@ -35,7 +35,10 @@ def build(force=False, verbose=False):
 
     def compile_one(job):
         src, sp, obj = job
-        cmd = [NVCC] + ARCH + COMMON + ["-x", "cu", "-c", sp, "-o", obj]
+        if src.endswith(".cc"):       # host-only translation unit (AVX2 intrinsics): straight to g++
+            cmd = ["g++", "-O3", "-std=c++17", "-fPIC", "-Wall", "-pthread", "-c", sp, "-o", obj]
+        else:
+            cmd = [NVCC] + ARCH + COMMON + ["-x", "cu", "-c", sp, "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         log = r.stdout + r.stderr
         with open(obj + ".log", "w") as f:

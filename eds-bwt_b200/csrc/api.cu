@@ -1,5 +1,9 @@
 // C ABI of libedsbwt_cuda.so -- compute entry points (include/edsbwt.h).  No CPU fallback anywhere: every
 // function that computes needs a CUDA device and fails with EDSBWT_E_CUDA otherwise.
+#include <algorithm>
+#include <functional>
+#include <thread>
+
 #include "internal.cuh"
 
 using namespace edsbwt;
@@ -15,6 +19,7 @@ int require_device(int device) {
 template <class F> int guarded(F&& f) {
     try { f(); return EDSBWT_OK; }
     catch (const Failure& e) { return e.code; }
+    catch (const OccOverflow&) { set_error("more than 2^32 occurrences in one search call; split the batch"); return EDSBWT_E_UNSUPPORTED; }
     catch (const std::bad_alloc&) { set_error("host out of memory"); return EDSBWT_E_IO; }
     catch (const std::exception& e) { set_error("exception: %s", e.what()); return EDSBWT_E_ARG; }
 }
@@ -131,72 +136,124 @@ static Pipe& pipe_of(Index& ix) {
     return *ix.pipe;
 }
 
-__global__ void fixed_offsets_kernel(uint64_t* __restrict__ off, uint32_t n, uint64_t first, uint64_t len) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i <= n) off[i] = first + (uint64_t)i * len;
-}
+// One batch in the three forms the host-buffer entry points accept: bytes + offsets, equal-length bytes, 2-bit words.
+struct HostBatch {
+    const uint8_t* bytes = nullptr; const uint64_t* off = nullptr;      // off == nullptr: fixed_len characters per pattern
+    uint32_t fixed_len = 0;
+    const uint64_t* words = nullptr; const uint32_t* invalid = nullptr; // packed: stride = ceil(fixed_len / 32) words per pattern
+    uint32_t npat = 0;
+    uint32_t stride() const { return (fixed_len + 31) / 32; }
+    uint64_t off_of(uint32_t i) const { return off ? off[i] : (uint64_t)i * fixed_len; }
+};
 
-// pat_off == nullptr: npat patterns of fixed_len bytes back to back; their offsets are generated on the device instead of
-// travelling over PCIe (20 % of the input bytes of a length-32 batch)
-static int search_into_impl(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t fixed_len, uint32_t npat, int locate, int lf_variant,
-                            uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc) {
-    auto off_of = [&](uint32_t i) -> uint64_t { return pat_off ? pat_off[i] : (uint64_t)i * fixed_len; };
+// Drains the pipeline streams when a call leaves by an error path, so that no DMA is still reading or writing the caller's
+// buffers after the call has returned (and the next call finds the slots idle).
+struct PipeDrain {
+    Index& ix; Pipe& P; bool armed = true;
+    ~PipeDrain() { if (armed) { cudaStreamSynchronize(P.in); cudaStreamSynchronize(ix.stream); cudaStreamSynchronize(P.outs); } }
+};
+
+// pat_off == nullptr: npat patterns of fixed_len bytes back to back (no offset array crosses PCIe); words != nullptr: the
+// caller's own 2-bit words (a quarter of the bytes).  grow != nullptr: *grow is a malloc'ed occurrence buffer of occ_cap
+// tuples that is enlarged as needed (edsbwt_search) instead of failing with EDSBWT_E_NOSPACE.
+static int search_into_impl(edsbwt_index* idx, const HostBatch& hb, int locate, int lf_variant,
+                            uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc, edsbwt_occ** grow = nullptr) {
+    const uint32_t npat = hb.npat;
     Index& ix = idx->ix;
     std::lock_guard<std::mutex> call_lock(ix.call_mu);
     CUDA_OK(cudaSetDevice(ix.device));
     Pipe& P = pipe_of(ix);
+    PipeDrain drain{ix, P};
     // chunk schedule: equal chunks, then a tapered tail (halves down to a quarter chunk) -- the input copies are the long
-    // pole of the pipeline, so what the batch pays on top of them is the search + copy-out of the LAST chunk only
-    const uint32_t chunk = ix.chunk_patterns ? ix.chunk_patterns : npat;
+    // pole of the pipeline, so what the batch pays on top of them is the search + copy-out of the LAST chunk only.
+    // Packed batches are cut at multiples of 32 patterns (their invalid bitmap is addressed by 32-bit words).
+    const bool packed = hb.words != nullptr;
+    auto r32 = [&](uint32_t v) { return packed ? (uint32_t)std::min<uint64_t>(((uint64_t)v + 31) & ~31ull, 0xffffffe0ull) : v; };
+    const uint32_t chunk = ix.chunk_patterns ? std::max<uint32_t>(r32(ix.chunk_patterns), 1u) : npat;
     std::vector<uint32_t> cb{0};
     for (uint32_t rem = npat; rem;) {
         uint32_t take;
         if (rem > chunk + chunk / 2) take = chunk;
-        else if (npat > chunk && rem > chunk / 4 + 1) take = (rem + 1) / 2;
+        else if (npat > chunk && rem > chunk / 4 + 1) take = std::min(rem, std::max<uint32_t>(r32((rem + 1) / 2), 1u));
         else take = rem;
         cb.push_back(cb.back() + take); rem -= take;
     }
     const uint32_t nchunks = (uint32_t)cb.size() - 1;
     uint64_t total_occ = 0; bool nospace = false;
-    edsbwt_stats acc{}; 
+    edsbwt_stats acc{};
     auto issue_in = [&](uint32_t c) {
         const uint32_t b = cb[c], e = cb[c + 1];
-        const uint64_t nb = off_of(e) - off_of(b);
         const int sl = c & 1;
-        P.bytes[sl].ensure(nb + 16); P.off[sl].ensure((size_t)(e - b) + 1);
-        if (nb) CUDA_OK(cudaMemcpyAsync(P.bytes[sl].p, pat_bytes + off_of(b), nb, cudaMemcpyHostToDevice, P.in));
-        if (pat_off) CUDA_OK(cudaMemcpyAsync(P.off[sl].p, pat_off + b, ((size_t)(e - b) + 1) * 8, cudaMemcpyHostToDevice, P.in));
-        else fixed_offsets_kernel<<<(e - b + 256) / 256, 256, 0, P.in>>>(P.off[sl].p, e - b, off_of(b), fixed_len);
+        if (packed) {
+            const size_t nw = (size_t)(e - b) * hb.stride();
+            P.words[sl].ensure(nw + 1); P.invalid[sl].ensure((size_t)(e - b + 31) / 32 + 1);
+            if (nw) CUDA_OK(cudaMemcpyAsync(P.words[sl].p, hb.words + (size_t)b * hb.stride(), nw * 8, cudaMemcpyHostToDevice, P.in));
+            if (hb.invalid) CUDA_OK(cudaMemcpyAsync(P.invalid[sl].p, hb.invalid + b / 32, (size_t)((e - b + 31) / 32) * 4, cudaMemcpyHostToDevice, P.in));
+        } else {
+            const uint64_t nb = hb.off_of(e) - hb.off_of(b);
+            P.bytes[sl].ensure(nb + 16);
+            if (nb) CUDA_OK(cudaMemcpyAsync(P.bytes[sl].p, hb.bytes + hb.off_of(b), nb, cudaMemcpyHostToDevice, P.in));
+            if (hb.off) { P.off[sl].ensure((size_t)(e - b) + 1); CUDA_OK(cudaMemcpyAsync(P.off[sl].p, hb.off + b, ((size_t)(e - b) + 1) * 8, cudaMemcpyHostToDevice, P.in)); }
+        }
         CUDA_OK(cudaEventRecord(P.ev_in[sl], P.in));
     };
-    issue_in(0);
-    for (uint32_t c = 0; c < nchunks; ++c) {
-        const uint32_t b = cb[c], e = cb[c + 1];
-        const int sl = c & 1;
-        const uint32_t max_len = 0;                                  // found on the device if the level-synchronous tier is needed
-        if (c + 1 < nchunks) issue_in(c + 1);                       // overlaps the search below
-        if (c >= 2) CUDA_OK(cudaEventSynchronize(P.ev_out[sl]));     // result buffers of chunk c-2 are free again
-        CUDA_OK(cudaStreamWaitEvent(ix.stream, P.ev_in[sl], 0));
-        // offsets stay absolute: bias the byte pointer instead of rebasing npat offsets on the host
-        const uint8_t* d_bytes = (const uint8_t*)((uintptr_t)P.bytes[sl].p - (uintptr_t)off_of(b));
-        run_search(ix, d_bytes, P.off[sl].p, e - b, off_of(e) - off_of(b), max_len, locate != 0, lf_variant, P.res[sl], b);
+    // search of patterns [lo, hi) of chunk [b, ..) whose input sits in slot sl; on an occurrence overflow the range is halved
+    std::function<void(int, uint32_t, uint32_t, uint32_t)> search_range = [&](int sl, uint32_t b, uint32_t lo, uint32_t hi) {
+        PatHint hint{};
+        const uint8_t* d_bytes = nullptr; const uint64_t* d_off = nullptr; uint64_t nbytes = 0;
+        if (packed) { hint.fixed_len = hb.fixed_len; hint.d_words = P.words[sl].p + (size_t)(lo - b) * hb.stride(); hint.d_invalid = hb.invalid ? P.invalid[sl].p + (lo - b) / 32 : nullptr; }
+        else {
+            // offsets stay absolute: bias the byte pointer instead of rebasing npat offsets on the host
+            d_bytes = (const uint8_t*)((uintptr_t)P.bytes[sl].p - (uintptr_t)hb.off_of(b));
+            nbytes = hb.off_of(hi) - hb.off_of(lo);
+            if (hb.off) d_off = P.off[sl].p + (lo - b);
+            else { hint.fixed_len = hb.fixed_len; hint.fixed_base = hb.off_of(lo); }
+        }
+        try {
+            run_search(ix, d_bytes, d_off, hi - lo, nbytes, 0, locate != 0, lf_variant, P.res[sl], lo, &hint);
+        } catch (const OccOverflow&) {
+            uint32_t mid = lo + (hi - lo) / 2;
+            if (packed) mid = b + (((mid - b) + 31) & ~31u);
+            if (mid <= lo || mid >= hi) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "patterns %u..%u alone have more than %llu occurrences", lo, hi - 1, (unsigned long long)ix.occ_limit);
+            search_range(sl, b, lo, mid);
+            CUDA_OK(cudaStreamSynchronize(P.outs));              // the slot's result buffers are reused by the second half
+            search_range(sl, b, mid, hi);
+            return;
+        }
         const edsbwt_stats& st = ix.last;
         acc.I += st.I; acc.S += st.S; acc.E += st.E; acc.L += st.L; acc.O += st.O; acc.steps += st.steps; acc.kernel_launches += st.kernel_launches;
         acc.lf_intervals += st.lf_intervals; acc.lf_kernel_ms += st.lf_kernel_ms; acc.locate_kernel_ms += st.locate_kernel_ms; acc.total_ms += st.total_ms;
         acc.frontier_peak = std::max(acc.frontier_peak, st.frontier_peak); acc.occ_blocks += st.occ_blocks; acc.overflow_patterns += st.overflow_patterns;
         acc.levelsync_patterns += st.levelsync_patterns; acc.search_kernel_ms += st.search_kernel_ms;
         // run_search returned with the compute stream idle: copy out on the third stream
-        CUDA_OK(cudaMemcpyAsync(counts + b, P.res[sl].counts.p, (size_t)(e - b) * 4, cudaMemcpyDeviceToHost, P.outs));
+        CUDA_OK(cudaMemcpyAsync(counts + lo, P.res[sl].counts.p, (size_t)(hi - lo) * 4, cudaMemcpyDeviceToHost, P.outs));
         const uint64_t k = P.res[sl].nocc;
         if (locate && k) {
+            if (grow && total_occ + k > occ_cap) {               // edsbwt_search: enlarge the malloc'ed buffer (copies into the old one must land first)
+                CUDA_OK(cudaStreamSynchronize(P.outs));
+                const uint64_t ncap = std::max<uint64_t>(occ_cap * 2, total_occ + k);
+                edsbwt_occ* nb = (edsbwt_occ*)realloc(*grow, (size_t)ncap * sizeof(edsbwt_occ));
+                if (!nb) EDS_FAIL(EDSBWT_E_IO, "host out of memory for %llu occurrences", (unsigned long long)ncap);
+                *grow = occ = nb; occ_cap = ncap;
+            }
             if (occ && total_occ + k <= occ_cap) CUDA_OK(cudaMemcpyAsync(occ + total_occ, P.res[sl].occ.p, (size_t)k * sizeof(edsbwt_occ), cudaMemcpyDeviceToHost, P.outs));
             else if (occ && total_occ < occ_cap) { CUDA_OK(cudaMemcpyAsync(occ + total_occ, P.res[sl].occ.p, (size_t)(occ_cap - total_occ) * sizeof(edsbwt_occ), cudaMemcpyDeviceToHost, P.outs)); nospace = true; }
             else nospace = true;
             total_occ += k;
         }
+    };
+    issue_in(0);
+    for (uint32_t c = 0; c < nchunks; ++c) {
+        const uint32_t b = cb[c], e = cb[c + 1];
+        const int sl = c & 1;
+        if (c + 1 < nchunks) issue_in(c + 1);                       // overlaps the search below
+        if (c >= 2) CUDA_OK(cudaEventSynchronize(P.ev_out[sl]));     // result buffers of chunk c-2 are free again
+        CUDA_OK(cudaStreamWaitEvent(ix.stream, P.ev_in[sl], 0));
+        search_range(sl, b, b, e);
         CUDA_OK(cudaEventRecord(P.ev_out[sl], P.outs));
     }
     CUDA_OK(cudaStreamSynchronize(P.outs));
+    drain.armed = false;
     ix.last = acc;
     if (nocc) *nocc = total_occ;
     return (locate && nospace && (occ || occ_cap)) ? EDSBWT_E_NOSPACE : EDSBWT_OK;
@@ -208,7 +265,8 @@ int edsbwt_search_into(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64
     if (nocc) *nocc = 0;
     if (npat == 0) return EDSBWT_OK;
     int rc2 = EDSBWT_OK;
-    int rc = guarded([&] { rc2 = search_into_impl(idx, pat_bytes, pat_off, 0, npat, locate, lf_variant, counts, occ, occ_cap, nocc); });
+    HostBatch hb; hb.bytes = pat_bytes; hb.off = pat_off; hb.npat = npat;
+    int rc = guarded([&] { rc2 = search_into_impl(idx, hb, locate, lf_variant, counts, occ, occ_cap, nocc); });
     return rc ? rc : rc2;
 }
 
@@ -218,8 +276,26 @@ int edsbwt_search_into_fixed(edsbwt_index* idx, const uint8_t* pat_bytes, uint32
     if (nocc) *nocc = 0;
     if (npat == 0) return EDSBWT_OK;
     int rc2 = EDSBWT_OK;
-    int rc = guarded([&] { rc2 = search_into_impl(idx, pat_bytes, nullptr, pat_len, npat, locate, lf_variant, counts, occ, occ_cap, nocc); });
+    HostBatch hb; hb.bytes = pat_bytes; hb.fixed_len = pat_len; hb.npat = npat;
+    int rc = guarded([&] { rc2 = search_into_impl(idx, hb, locate, lf_variant, counts, occ, occ_cap, nocc); });
     return rc ? rc : rc2;
+}
+
+int edsbwt_search_into_packed(edsbwt_index* idx, const uint64_t* pat_words, const uint32_t* invalid, uint32_t pat_len, uint32_t npat,
+                              int locate, int lf_variant, uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc) {
+    if (!idx || (npat && (!pat_words || !counts || !pat_len))) return EDSBWT_E_ARG;
+    if (nocc) *nocc = 0;
+    if (npat == 0) return EDSBWT_OK;
+    int rc2 = EDSBWT_OK;
+    HostBatch hb; hb.words = pat_words; hb.invalid = invalid; hb.fixed_len = pat_len; hb.npat = npat;
+    int rc = guarded([&] { rc2 = search_into_impl(idx, hb, locate, lf_variant, counts, occ, occ_cap, nocc); });
+    return rc ? rc : rc2;
+}
+
+int edsbwt_pack_patterns(const edsbwt_index* idx, const uint8_t* pat_bytes, uint32_t pat_len, uint32_t npat, int nthreads,
+                         uint64_t* words, uint32_t* invalid, uint32_t* n_invalid) {
+    if (!idx) return EDSBWT_E_ARG;
+    return edsbwt_pack_patterns_alphabet(idx->ix.host.alphabet, idx->ix.host.sigma, pat_bytes, pat_len, npat, nthreads, words, invalid, n_invalid);
 }
 
 int edsbwt_search(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat, int locate, int lf_variant,
@@ -230,18 +306,18 @@ int edsbwt_search(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* p
     if (nocc) *nocc = 0;
     if (npat == 0) return EDSBWT_OK;
     if (!locate) return edsbwt_search_into(idx, pat_bytes, pat_off, npat, 0, lf_variant, counts, nullptr, 0, nullptr);
-    // occurrences are malloc'ed for the caller: size them from the counts of a first attempt with a guessed capacity
-    uint64_t cap = (uint64_t)npat * 2 + 1024, got = 0;
-    for (int attempt = 0; attempt < 2; ++attempt) {
-        edsbwt_occ* buf = (edsbwt_occ*)malloc((size_t)cap * sizeof(edsbwt_occ));
-        if (!buf) { set_error("host out of memory for %llu occurrences", (unsigned long long)cap); return EDSBWT_E_IO; }
-        int rc = edsbwt_search_into(idx, pat_bytes, pat_off, npat, 1, lf_variant, counts, buf, cap, &got);
-        if (rc == EDSBWT_OK) { if (got == 0) { free(buf); buf = nullptr; } *occ = buf; *nocc = got; return EDSBWT_OK; }
-        free(buf);
-        if (rc != EDSBWT_E_NOSPACE) return rc;
-        cap = got;
-    }
-    return EDSBWT_E_UNSUPPORTED;
+    // occurrences are malloc'ed for the caller: a guessed capacity that the chunk loop enlarges when a chunk does not fit
+    // (nothing is searched twice)
+    const uint64_t cap = (uint64_t)npat * 2 + 1024;
+    edsbwt_occ* buf = (edsbwt_occ*)malloc((size_t)cap * sizeof(edsbwt_occ));
+    if (!buf) { set_error("host out of memory for %llu occurrences", (unsigned long long)cap); return EDSBWT_E_IO; }
+    uint64_t got = 0; int rc2 = EDSBWT_OK;
+    HostBatch hb; hb.bytes = pat_bytes; hb.off = pat_off; hb.npat = npat;
+    int rc = guarded([&] { rc2 = search_into_impl(idx, hb, 1, lf_variant, counts, buf, cap, &got, &buf); });
+    if (rc || rc2) { free(buf); return rc ? rc : rc2; }
+    if (got == 0) { free(buf); buf = nullptr; }
+    *occ = buf; *nocc = got;
+    return EDSBWT_OK;
 }
 
 int edsbwt_search_trace(edsbwt_index* idx, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t npat, int lf_variant,
@@ -316,6 +392,7 @@ int edsbwt_search_to_csv(edsbwt_index* idx, const uint8_t* pat_bytes, const uint
         const uint32_t nchunks = (npat + chunk - 1) / chunk;
         uint64_t total = 0, launches = 0;
         edsbwt_stats acc{};
+        PipeDrain drain{ix, P};
         auto issue_in = [&](uint32_t c) {
             const uint32_t b = c * chunk, e = (uint32_t)std::min<uint64_t>((uint64_t)b + chunk, npat);
             const uint64_t nb = pat_off[e] - pat_off[b];
@@ -325,25 +402,39 @@ int edsbwt_search_to_csv(edsbwt_index* idx, const uint8_t* pat_bytes, const uint
             CUDA_OK(cudaMemcpyAsync(P.off[sl].p, pat_off + b, ((size_t)(e - b) + 1) * 8, cudaMemcpyHostToDevice, P.in));
             CUDA_OK(cudaEventRecord(P.ev_in[sl], P.in));
         };
-        issue_in(0);
-        for (uint32_t c = 0; c < nchunks; ++c) {
-            const uint32_t b = c * chunk, e = (uint32_t)std::min<uint64_t>((uint64_t)b + chunk, npat);
-            const int sl = c & 1;
-            if (c + 1 < nchunks) issue_in(c + 1);                   // the other slot is free (chunk c-1 fully written): overlaps the search below
-            CUDA_OK(cudaStreamWaitEvent(ix.stream, P.ev_in[sl], 0));
+        // patterns [lo, hi) of the chunk starting at b (input in slot sl); a range with more than 2^32 occurrences (short patterns
+        // on a large index) is halved until it fits -- the reference handles such files too, one pattern at a time
+        std::function<void(int, uint32_t, uint32_t, uint32_t)> search_range = [&](int sl, uint32_t b, uint32_t lo, uint32_t hi) {
             const uint8_t* d_bytes = (const uint8_t*)((uintptr_t)P.bytes[sl].p - (uintptr_t)pat_off[b]);
-            run_search(ix, d_bytes, P.off[sl].p, e - b, pat_off[e] - pat_off[b], 0, true, lf_variant, P.res[sl], b);
+            try {
+                run_search(ix, d_bytes, P.off[sl].p + (lo - b), hi - lo, pat_off[hi] - pat_off[lo], 0, true, lf_variant, P.res[sl], lo);
+            } catch (const OccOverflow&) {
+                const uint32_t mid = lo + (hi - lo) / 2;
+                if (mid <= lo) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "pattern %u alone has more than %llu occurrences", lo, (unsigned long long)ix.occ_limit);
+                search_range(sl, b, lo, mid);
+                search_range(sl, b, mid, hi);
+                return;
+            }
             const edsbwt_stats st = ix.last;
             acc.L += st.L; acc.O += st.O; acc.kernel_launches += st.kernel_launches; acc.total_ms += st.total_ms;
             acc.search_kernel_ms += st.search_kernel_ms; acc.locate_kernel_ms += st.locate_kernel_ms; acc.overflow_patterns += st.overflow_patterns;
-            CUDA_OK(cudaMemcpyAsync(counts + b, P.res[sl].counts.p, (size_t)(e - b) * 4, cudaMemcpyDeviceToHost, ix.stream));
+            CUDA_OK(cudaMemcpyAsync(counts + lo, P.res[sl].counts.p, (size_t)(hi - lo) * 4, cudaMemcpyDeviceToHost, ix.stream));
             {
                 std::lock_guard<std::mutex> lock(ix.mu);
                 write_csv_device(ix, P.res[sl].occ.p, P.res[sl].nocc, 1, f, ix.stream, &launches);
             }
             CUDA_OK(cudaStreamSynchronize(ix.stream));
             total += P.res[sl].nocc;
+        };
+        issue_in(0);
+        for (uint32_t c = 0; c < nchunks; ++c) {
+            const uint32_t b = c * chunk, e = (uint32_t)std::min<uint64_t>((uint64_t)b + chunk, npat);
+            const int sl = c & 1;
+            if (c + 1 < nchunks) issue_in(c + 1);                   // the other slot is free (chunk c-1 fully written): overlaps the search below
+            CUDA_OK(cudaStreamWaitEvent(ix.stream, P.ev_in[sl], 0));
+            search_range(sl, b, b, e);
         }
+        drain.armed = false;
         acc.kernel_launches += launches;
         ix.last = acc;
         if (nocc) *nocc = total;

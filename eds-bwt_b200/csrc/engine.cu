@@ -38,6 +38,7 @@ __device__ __forceinline__ void warp_add(unsigned long long* dst, uint32_t v) {
 }
 
 static inline unsigned grid_for(size_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
+struct WidenU32 { __host__ __device__ __forceinline__ unsigned long long operator()(const uint32_t& v) const { return v; } };
 
 // ===================================================================================================
 // K1: Occ structure from the raw eBWT bytes  (replaces computeVectorOcc, EDSBWTsearch.cpp:1338-1442,
@@ -429,12 +430,16 @@ __global__ void locate_light_kernel(const __grid_constant__ IndexView ix, const 
         if (cnt > LOCATE_LIGHT_MAX) heavy[atomicAdd(nheavy, 1u)] = q;
         else if (cnt) {
             uint2 pl = __ldg(plist + q);
-            const uint2* ivs = staging + pl.x;
-            if (pl.y & PLIST_SEED) { ivs = seed_ivp[(pl.y >> 27) & 15u] + pl.x; pl.y &= PLIST_N_MASK; }
             uint32_t t = o0;
-            for (uint32_t j = 0; j < pl.y; ++j) {
-                const uint2 iv = __ldg(ivs + j);
-                for (uint32_t row = iv.x; row <= iv.y; ++row) steps += locate_row<WALK>(ix, row, q + pat_base, out + t++);
+            if (pl.y == PLIST_INLINE) {                    // one interval, carried by the entry itself: rows pl.x .. pl.x + cnt - 1
+                for (uint32_t row = pl.x; row < pl.x + cnt; ++row) steps += locate_row<WALK>(ix, row, q + pat_base, out + t++);
+            } else {
+                const uint2* ivs = staging + pl.x;
+                if (pl.y & PLIST_SEED) { ivs = seed_ivp[(pl.y >> 27) & 15u] + pl.x; pl.y &= PLIST_N_MASK; }
+                for (uint32_t j = 0; j < pl.y; ++j) {
+                    const uint2 iv = __ldg(ivs + j);
+                    for (uint32_t row = iv.x; row <= iv.y; ++row) steps += locate_row<WALK>(ix, row, q + pat_base, out + t++);
+                }
             }
             nrows = cnt;
         }
@@ -453,12 +458,15 @@ __global__ void locate_heavy_kernel(const __grid_constant__ IndexView ix, const 
         const uint32_t q = heavy[i];
         uint2 pl = __ldg(plist + q);
         const uint2* ivs = staging + pl.x;
-        if (pl.y & PLIST_SEED) { ivs = seed_ivp[(pl.y >> 27) & 15u] + pl.x; pl.y &= PLIST_N_MASK; }
         uint32_t t = __ldg(occ_ofs + q);
+        const bool inl = pl.y == PLIST_INLINE;             // one interval carried by the entry itself
+        const uint32_t inl_hi = pl.x + (__ldg(occ_ofs + q + 1) - t) - 1;
+        if (inl) pl.y = 1;
+        else if (pl.y & PLIST_SEED) { ivs = seed_ivp[(pl.y >> 27) & 15u] + pl.x; pl.y &= PLIST_N_MASK; }
         // 32 intervals at a time: lane l holds interval j0 + l; an exclusive warp scan of the lengths places every row
         for (uint32_t j0 = 0; j0 < pl.y; j0 += 32) {
             uint2 iv = make_uint2(1u, 0u);
-            if (j0 + lane < pl.y) iv = __ldg(ivs + j0 + lane);
+            if (j0 + lane < pl.y) iv = inl ? make_uint2(pl.x, inl_hi) : __ldg(ivs + j0 + lane);
             const uint32_t len = iv.y + 1 - iv.x;                      // 0 for the padding lanes
             uint32_t pre = len;
             for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, pre, o); if (lane >= (uint32_t)o) pre += v; }
@@ -497,6 +505,9 @@ struct Workspace {
     DevBuf<unsigned int> scalars;        // [0] nvalid
     DevBuf<uint2> plist, staging;        // per-pattern final lists (fused + level-synchronous results)
     DevBuf<uint32_t> fcursor, ovf_ids, ovf_ids2, occ_ofs, heavy;
+    DevBuf<uint64_t> pwords, uoff;       // 2-bit pattern words of the batch (pack_patterns_kernel); offsets generated for fixed-length batches
+    DevBuf<uint32_t> pinvalid;
+    DevBuf<uint8_t> ubytes;              // characters of packed patterns, unpacked for the tiers that read characters
     StatsDev* d_stats = nullptr;
     uint32_t* h_pin = nullptr;           // pinned read-back area
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr, evf0 = nullptr, evf1 = nullptr, evl0 = nullptr, evl1 = nullptr;
@@ -702,7 +713,7 @@ static void build_seed_table(Index& ix, uint32_t k) {
         lv->cnt.exact(nkeys);
         seed_counts_kernel<<<grid_for(nkeys, 256), 256, 0, s>>>(lv->off.p, lv->iv.p, nkeys, lv->cnt.p);
     }
-    if (k >= 10) {                      // worth 16 B per key only where the table is deep (large indexes)
+    {                                   // deepest level: the seed lookup of the hot kernel in one 16-byte gather
         SeedLevel* lv = ix.seed[k];
         const uint32_t nkeys = 1u << (2 * k);
         lv->first.exact(nkeys);
@@ -720,13 +731,11 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     cudaStream_t s = ix.stream;
     ix.ws = new Workspace;
     Workspace& ws = *ix.ws;
-    CUDA_OK(cudaMalloc(&ws.d_stats, sizeof(StatsDev)));
+    CUDA_OK(cudaMalloc(&ws.d_stats, 2 * sizeof(StatsDev)));      // [1]: 64-bit scratch (occurrence total)
     CUDA_OK(cudaMallocHost(&ws.h_pin, 256));
     CUDA_OK(cudaEventCreate(&ws.ev0)); CUDA_OK(cudaEventCreate(&ws.ev1)); CUDA_OK(cudaEventCreate(&ws.evk0)); CUDA_OK(cudaEventCreate(&ws.evk1));
     CUDA_OK(cudaEventCreate(&ws.evf0)); CUDA_OK(cudaEventCreate(&ws.evf1)); CUDA_OK(cudaEventCreate(&ws.evl0)); CUDA_OK(cudaEventCreate(&ws.evl1));
-    ix.engine = o.engine == EDSBWT_ENGINE_LEVELSYNC ? EDSBWT_ENGINE_LEVELSYNC : EDSBWT_ENGINE_FUSED;
-    { const char* e = getenv("EDSBWT_FUSED_FLAT");      // A/B switch of the experimental warp-flat first pass (fused.cu)
-      ix.fused_flat = (ix.engine == EDSBWT_ENGINE_FUSED && e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : (o.engine == EDSBWT_ENGINE_FUSED_FLAT ? 1 : 0); }
+    ix.engine = (o.engine == EDSBWT_ENGINE_LEVELSYNC || o.engine == EDSBWT_ENGINE_FUSED_STEP) ? o.engine : EDSBWT_ENGINE_FUSED;
     ix.fused_cap = o.fused_cap > 0 ? (uint32_t)o.fused_cap : 13u;       // 13 slots: 12 CTAs/SM (40 registers) and >= 60 KB of L1 left (A/B: profiles/r01_ab_keep_sort_sizes.txt)
     ix.fused_cap_auto = o.fused_cap <= 0;
     if (ix.fused_cap < 4) ix.fused_cap = 4;
@@ -829,6 +838,7 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     build_seed_table(ix, ix.seed_k);
     CUDA_OK(cudaGetLastError());
     ix.move_a = o.move_a > 0 ? (uint32_t)o.move_a : 8u;
+    if (const char* e = getenv("EDSBWT_OCC_LIMIT")) { const unsigned long long v = strtoull(e, nullptr, 10); if (v && v < ix.occ_limit) ix.occ_limit = v; }
     if (o.build_move) build_move_table(ix);
     h.ebwt.clear(); h.ebwt.shrink_to_fit();
     h.seg_first_bit.clear(); h.seg_first_bit.shrink_to_fit();
@@ -909,12 +919,22 @@ static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64
     return nF;
 }
 
+__global__ void fixed_offsets_kernel(uint64_t* __restrict__ off, uint32_t n, uint64_t first, uint64_t len) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i <= n) off[i] = first + (uint64_t)i * len;
+}
+
 void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat, uint64_t total_bytes, uint32_t max_len,
-                bool locate, int lf_variant, SearchOut& out, uint32_t pat_base) {
+                bool locate, int lf_variant, SearchOut& out, uint32_t pat_base, const PatHint* hint) {
     if (lf_variant != EDSBWT_LF_RANK && lf_variant != EDSBWT_LF_MOVE) EDS_FAIL(EDSBWT_E_ARG, "unknown LF variant %d", lf_variant);
     const bool move = lf_variant == EDSBWT_LF_MOVE;
     if (move && out.want_alive) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "edsbwt_search_trace is an EDSBWTsearch (RECOVERBW=0) feature; MOVE_EDSBWTSearch always locates");
-    (void)total_bytes;
+    const uint32_t fixed_len = hint ? hint->fixed_len : 0u, stride = (fixed_len + 31) / 32;
+    const uint64_t* caller_words = hint ? hint->d_words : nullptr;
+    if (npat && !d_off && !fixed_len) EDS_FAIL(EDSBWT_E_ARG, "a batch needs pattern offsets or a fixed pattern length");
+    if (npat && !d_bytes && !caller_words) EDS_FAIL(EDSBWT_E_ARG, "a batch needs pattern bytes or packed words");
+    if (caller_words && !fixed_len) EDS_FAIL(EDSBWT_E_ARG, "packed patterns are fixed-length batches");
+    if (fixed_len && max_len == 0) max_len = fixed_len;
     CUDA_OK(cudaSetDevice(ix.device));
     std::lock_guard<std::mutex> lock(ix.mu);
     if (move) build_move_table(ix);            // no-op once built
@@ -934,13 +954,31 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     if (out.want_alive) { out.alive.ensure(npat ? npat : 1); d_alive = out.alive.p; }
     uint32_t steps = 0, novf = 0, novf1 = 0; uint64_t peak = 0;
     bool fused_ran = false, locate_ran = false;
+    // The step-loop kernel, the move kernel and the level-synchronous engine read CHARACTERS + offsets; the item kernel reads
+    // 2-bit words.  Whatever form the caller did not supply is produced on the device, and only when a tier needs it.
+    const uint8_t* cbytes = d_bytes; const uint64_t* coff = d_off;
+    auto need_chars = [&](const uint32_t* sub_ids, uint32_t nsub) {
+        if (!cbytes) {                                       // packed input: back to characters (only the listed patterns)
+            ws.ubytes.ensure((size_t)npat * fixed_len + 64);
+            uint64_t letters = ix.host.alphabet[0];          // bits 0..7: the end-marker (written for patterns flagged invalid), then the letters
+            for (uint32_t a = 1; a < ix.host.sigma && a <= 4; ++a) letters |= (uint64_t)ix.host.alphabet[a] << (8 * a);
+            launch_unpack_patterns(caller_words, fixed_len, stride, sub_ids, nsub, letters, hint->d_invalid, ws.ubytes.p, s);
+            cbytes = ws.ubytes.p; ws.launches += 1;
+            coff = nullptr;
+        }
+        if (!coff) {
+            ws.uoff.ensure((size_t)npat + 1);
+            fixed_offsets_kernel<<<grid_for((size_t)npat + 1, 256), 256, 0, s>>>(ws.uoff.p, npat, d_bytes ? hint->fixed_base : 0ull, fixed_len);
+            coff = ws.uoff.p; ws.launches += 1;
+        }
+    };
     if (npat) {
-        ws.plist.ensure(npat); ws.fcursor.ensure(4);
-        CUDA_OK(cudaMemsetAsync(ws.fcursor.p, 0, 16, s));
+        ws.plist.ensure(npat); ws.fcursor.ensure(8);
+        CUDA_OK(cudaMemsetAsync(ws.fcursor.p, 0, 32, s));
         uint32_t nstage = 0;
         const uint32_t* ids = nullptr;
-        if (ix.engine == EDSBWT_ENGINE_FUSED || move) {
-            // ---- the hot kernel: one thread per pattern
+        if (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move) {
+            const bool items = !move && ix.engine == EDSBWT_ENGINE_FUSED;
             size_t want = (size_t)npat * 2 + (1u << 16);
             if (want > 0xfffffff0ull) want = 0xfffffff0ull;
             ws.staging.ensure(want); ws.ovf_ids.ensure(npat);
@@ -948,34 +986,56 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; sv.cnt[L] = ix.seed[L]->cnt.p; }
             sv.first = ix.seed[ix.seed_k]->first.p; sv.first_level = ix.seed_k;
             FusedOut fo{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 1, ws.ovf_ids.p, d_alive};
-            CUDA_OK(cudaEventRecord(ws.evf0, s));
             // MOVE: 16-byte frontier entries (b, e, b', e'), so half the slots fit the same shared memory
             const uint32_t cap1 = move ? std::min<uint32_t>(ix.fused_cap, 12u) : ix.fused_cap;     // MOVE: 24 KB per CTA, 8 CTAs/SM
             const uint32_t cap2 = move ? std::min<uint32_t>(ix.fused_cap2, FUSED_BIG_CAP / 2) : ix.fused_cap2;
-            if (move) { MoveOut mo{fo.plist, fo.counts, fo.staging, fo.staging_cap, fo.cursor, fo.ovf_count, fo.ovf_ids};
-                        launch_move_search(ix.view, ix.move->view, sv, k_eff, d_bytes, d_off, nullptr, npat, ix.lut.p, cap1, mo, s); }
-            else launch_fused_search(ix.view, sv, k_eff, d_bytes, d_off, nullptr, npat, ix.lut.p, cap1, fo, st, ix.canonical_k, s, ix.fused_flat);
-            CUDA_OK(cudaEventRecord(ws.evf1, s));
+            if (items) {
+                // ---- the hot kernel (items.cu): patterns as 2-bit words, persistent warps, lanes refilled
+                PackedPats pp{};
+                if (caller_words) { pp.words = caller_words; pp.invalid = hint->d_invalid; pp.poff = nullptr; }
+                else {
+                    const uint64_t nwords = fixed_len ? (uint64_t)npat * stride : (total_bytes >> 5) + npat + 1;
+                    if (nwords > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 pattern words in one batch; split the batch");
+                    ws.pwords.ensure(nwords + 1); ws.pinvalid.ensure(((size_t)npat + 31) / 32 + 1);
+                    launch_pack_patterns(d_bytes, fixed_len ? nullptr : d_off, fixed_len, hint ? hint->fixed_base : 0ull, stride, npat, ix.lut.p,
+                                         ws.pwords.p, nwords, ws.pinvalid.p, ws.fcursor.p + 5, s);
+                    ws.launches += 1;
+                    pp.words = ws.pwords.p; pp.invalid = ws.pinvalid.p; pp.poff = fixed_len ? nullptr : d_off;
+                }
+                pp.fixed_len = fixed_len; pp.stride = stride;
+                CUDA_OK(cudaEventRecord(ws.evf0, s));
+                launch_items_search(ix.view, sv, k_eff, pp, npat, cap1, fo, ws.fcursor.p + 4, st, ix.canonical_k, s);
+                CUDA_OK(cudaEventRecord(ws.evf1, s));
+            } else {
+                need_chars(nullptr, npat);
+                CUDA_OK(cudaEventRecord(ws.evf0, s));
+                if (move) { MoveOut mo{fo.plist, fo.counts, fo.staging, fo.staging_cap, fo.cursor, fo.ovf_count, fo.ovf_ids};
+                            launch_move_search(ix.view, ix.move->view, sv, k_eff, cbytes, coff, nullptr, npat, ix.lut.p, cap1, mo, s); }
+                else launch_fused_search(ix.view, sv, k_eff, cbytes, coff, nullptr, npat, ix.lut.p, cap1, fo, st, ix.canonical_k, s);      // EDSBWT_ENGINE_FUSED_STEP
+                CUDA_OK(cudaEventRecord(ws.evf1, s));
+            }
             ws.launches += 1; fused_ran = true;
-            CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 8, cudaMemcpyDeviceToHost, s));
+            CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 32, cudaMemcpyDeviceToHost, s));
             CUDA_OK(cudaStreamSynchronize(s));
             nstage = ws.h_pin[0]; novf = ws.h_pin[1];
+            if (ws.h_pin[5]) EDS_FAIL(EDSBWT_E_ARG, "total_bytes (%llu) is smaller than the span of the pattern offsets", (unsigned long long)total_bytes);
             novf1 = novf;
             // variant-dense indexes (cfg3: a site every 6 bp) carry longer frontiers: a second pass costs a full pattern latency,
-            // so batches after one that overflowed noticeably run with 20 slots (10 CTAs/SM instantiation)
+            // so batches after one that overflowed noticeably run with 20 slots
             if (!move && !stats && ix.fused_cap_auto && ix.fused_cap < 20 && (uint64_t)novf * 1000 > npat) ix.fused_cap = 20;   // (a counting run starts from a shallower seed level: not representative)
             ids = ws.ovf_ids.p;
             if (novf && cap1 < cap2) {
-                // ---- second pass: the same kernel with the largest frontier that fits one CTA per SM, only over the
+                // ---- second pass: the step-loop kernel with the largest frontier that fits one CTA per SM, only over the
                 //      patterns that did not fit; what still does not fit goes to the level-synchronous engine
+                need_chars(ws.ovf_ids.p, novf);
                 ws.ovf_ids2.ensure(novf);
                 size_t want2 = (size_t)nstage + (size_t)novf * cap2;
                 if (want2 > 0xfffffff0ull) want2 = 0xfffffff0ull;
                 ws.staging.ensure(want2, s, true, nstage);
                 FusedOut fo2{ws.plist.p, out.counts.p, ws.staging.p, (uint32_t)std::min<size_t>(ws.staging.cap, 0xfffffff0ull), ws.fcursor.p, ws.fcursor.p + 2, ws.ovf_ids2.p, d_alive};
                 if (move) { MoveOut mo{fo2.plist, fo2.counts, fo2.staging, fo2.staging_cap, fo2.cursor, fo2.ovf_count, fo2.ovf_ids};
-                            launch_move_search(ix.view, ix.move->view, sv, k_eff, d_bytes, d_off, ws.ovf_ids.p, novf, ix.lut.p, cap2, mo, s); }
-                else launch_fused_search(ix.view, sv, k_eff, d_bytes, d_off, ws.ovf_ids.p, novf, ix.lut.p, cap2, fo2, st, ix.canonical_k, s);
+                            launch_move_search(ix.view, ix.move->view, sv, k_eff, cbytes, coff, ws.ovf_ids.p, novf, ix.lut.p, cap2, mo, s); }
+                else launch_fused_search(ix.view, sv, k_eff, cbytes, coff, ws.ovf_ids.p, novf, ix.lut.p, cap2, fo2, st, ix.canonical_k, s);
                 ws.launches += 1;
                 CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 12, cudaMemcpyDeviceToHost, s));
                 CUDA_OK(cudaStreamSynchronize(s));
@@ -989,13 +1049,14 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
         }
         if (novf) {
             // ---- level-synchronous engine: the whole batch (ENGINE_LEVELSYNC) or the patterns whose frontier outgrew the fused kernel
+            need_chars(ids, novf);
             if (max_len == 0) {
                 CUDA_OK(cudaMemsetAsync(ws.scalars.p + 2, 0, 4, s));
-                max_len_kernel<<<grid_for(novf, 256), 256, 0, s>>>(d_off, ids, novf, ws.scalars.p + 2);
+                max_len_kernel<<<grid_for(novf, 256), 256, 0, s>>>(coff, ids, novf, ws.scalars.p + 2);
                 max_len = read_u32(ws, ws.scalars.p + 2, s);
                 ws.launches += 1;
             }
-            uint32_t nF = levelsync_search(ix, d_bytes, d_off, ids, novf, max_len, st, steps, peak, d_alive, k_eff);
+            uint32_t nF = levelsync_search(ix, cbytes, coff, ids, novf, max_len, st, steps, peak, d_alive, k_eff);
             if (nF) {
                 if ((uint64_t)nstage + nF > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 result intervals in one batch; split the batch");
                 ws.staging.ensure((size_t)nstage + nF, s, true, nstage);
@@ -1005,20 +1066,22 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
         }
         if (locate) {
             ws.occ_ofs.ensure((size_t)npat + 2);
-            // exclusive scan of the counts (npat + 1 entries: the last one is the total)
-            size_t tmp = 0;
+            // total in 64 bits first (the 32-bit offsets below wrap silently when a batch of short patterns has more than 2^32
+            // occurrences), then the exclusive scan of the counts (npat + 1 entries: the last one is the total)
+            size_t tmp = 0, tmp2 = 0;
+            cub::TransformInputIterator<unsigned long long, WidenU32, const uint32_t*> wide(out.counts.p, WidenU32());
+            unsigned long long* d_total = reinterpret_cast<unsigned long long*>(ws.d_stats + 1);
+            CUDA_OK(cub::DeviceReduce::Sum(nullptr, tmp2, wide, d_total, (int)npat, s));
             CUDA_OK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, out.counts.p, ws.occ_ofs.p, (int)npat, s));
-            ws.cubtmp.ensure(tmp);
+            ws.cubtmp.ensure(std::max(tmp, tmp2));
+            CUDA_OK(cub::DeviceReduce::Sum(ws.cubtmp.p, tmp2, wide, d_total, (int)npat, s));
             CUDA_OK(cub::DeviceScan::ExclusiveSum(ws.cubtmp.p, tmp, out.counts.p, ws.occ_ofs.p, (int)npat, s));
-            ws.launches += 2;
-            // total = ofs[npat-1] + counts[npat-1]
-            CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.occ_ofs.p + (npat - 1), 4, cudaMemcpyDeviceToHost, s));
-            CUDA_OK(cudaMemcpyAsync(ws.h_pin + 1, out.counts.p + (npat - 1), 4, cudaMemcpyDeviceToHost, s));
+            ws.launches += 4;
+            CUDA_OK(cudaMemcpyAsync(ws.h_pin, d_total, 8, cudaMemcpyDeviceToHost, s));
             CUDA_OK(cudaStreamSynchronize(s));
-            uint64_t nocc = (uint64_t)ws.h_pin[0] + ws.h_pin[1];
-            if (nocc > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 occurrences in one batch; split the batch");
-            CUDA_OK(cudaMemcpyAsync(ws.occ_ofs.p + npat, ws.h_pin, 0, cudaMemcpyHostToDevice, s));
-            uint32_t tot32 = (uint32_t)nocc;
+            const uint64_t nocc = *reinterpret_cast<const unsigned long long*>(ws.h_pin);
+            if (nocc > ix.occ_limit) throw OccOverflow{};
+            const uint32_t tot32 = (uint32_t)nocc;
             CUDA_OK(cudaMemcpyAsync(ws.occ_ofs.p + npat, &tot32, 4, cudaMemcpyHostToDevice, s));
             out.nocc = nocc;
             if (nocc) {
@@ -1056,7 +1119,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     ls = edsbwt_stats{};
     ls.I = hs.I; ls.S = hs.S; ls.E = hs.E; ls.L = hs.L; ls.O = hs.O; ls.lf_intervals = hs.lf_intervals; ls.occ_blocks = hs.occ_blocks;
     ls.steps = steps; ls.kernel_launches = ws.launches; ls.lf_kernel_ms = ws.lf_ms; ls.total_ms = ms; ls.frontier_peak = peak;
-    ls.overflow_patterns = (ix.engine == EDSBWT_ENGINE_FUSED || move) ? novf1 : 0; ls.levelsync_patterns = novf;
+    ls.overflow_patterns = (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move) ? novf1 : 0; ls.levelsync_patterns = novf;
     if (fused_ran) { float fm = 0; CUDA_OK(cudaEventElapsedTime(&fm, ws.evf0, ws.evf1)); ls.search_kernel_ms = fm; }
     if (locate_ran) { float lm = 0; CUDA_OK(cudaEventElapsedTime(&lm, ws.evl0, ws.evl1)); ls.locate_kernel_ms = lm; }
 }

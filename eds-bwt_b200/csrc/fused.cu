@@ -25,11 +25,7 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 
 }  // namespace
 
-constexpr int FLAT_MINB = 10;          // CTAs per SM the warp-flat instantiation is compiled for
-constexpr uint32_t FLAT_QCAP = 8;      // '#'-carrying intervals one warp may meet in one step before their patterns are handed on
-
-// FLAT: 0 = the shipped step loop; 1 = warp-flat Occ fetch; 2 = 1 + the link records of a step gathered by the warp in one go
-template <bool STATS, int MINB, int FLAT = 0>
+template <bool STATS, int MINB>
 __global__ void __launch_bounds__(FUSED_THREADS, MINB)
 fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant__ SeedView sv, uint32_t k, const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ poff,
                     const uint32_t* __restrict__ ids, uint32_t npat, const uint8_t* __restrict__ lut, uint32_t cap, FusedOut out,
@@ -94,151 +90,6 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     const uint32_t steps = m - L0;
     const uint32_t mk = m < kc ? m : kc;
     uint32_t s = 0;
-    if constexpr (FLAT != 0) {
-        // ---- EXPERIMENTAL warp-flat step loop (EDSBWT_ENGINE_FUSED_FLAT).  Same frontier columns, same
-        // owner-serial bookkeeping (compaction, merge, Dol set, prepend) as the loop below, but the expensive part of a step --
-        // the Occ fetch and the popcounts of every interval -- is done over the warp's 32 frontiers laid end to end: lane l
-        // maps item first + l whoever owns it, so lanes whose own pattern is dead or short keep fetching for the others.
-        __shared__ uint4 s_queue[FUSED_THREADS / 32][FLAT_QCAP];          // (owner lane, '#' ranks before / after the interval)
-        __shared__ uint32_t s_punt[FUSED_THREADS / 32];
-        __shared__ uint2 s_qrec[FLAT == 2 ? FUSED_THREADS / 32 : 1][FLAT_QCAP];   // FLAT 2: link record of the first '#' of each queued interval
-        __shared__ uint32_t s_E[STATS ? FUSED_THREADS : 1];               // counting runs: end-markers met by the owner's intervals in this step
-        if (STATS) s_E[threadIdx.x] = 0;
-        constexpr uint32_t FULL = 0xffffffffu;
-        const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5, wcol = threadIdx.x & ~31u;
-        // insertion of the pile-0 range [l, h] into the owner's sorted, merged Dol set (top of its column); nkeep = entries of
-        // the F' list below it
-        auto dol_insert = [&](uint32_t l, uint32_t h, uint32_t nkeep, uint32_t& ndol) {
-            uint32_t i = 0;
-            while (i < ndol && DOL(i).y + 1 < l) ++i;
-            if (i < ndol && DOL(i).x <= h + 1) {
-                const uint2 d = DOL(i);
-                l = l < d.x ? l : d.x; h = h > d.y ? h : d.y;
-                uint32_t t = i + 1;
-                while (t < ndol && DOL(t).x <= h + 1) { const uint32_t y = DOL(t).y; h = h > y ? h : y; ++t; }
-                DOL(i) = make_uint2(l, h);
-                if (t > i + 1) { for (uint32_t u = t; u < ndol; ++u) DOL(i + 1 + (u - t)) = DOL(u); ndol -= t - (i + 1); }
-            } else {
-                if (nkeep + ndol + 1 > cap) { ovf = true; return; }
-                for (uint32_t u = ndol; u > i; --u) DOL(u) = DOL(u - 1);
-                DOL(i) = make_uint2(l, h);
-                ++ndol;
-            }
-        };
-        // one flat sweep: the n intervals of every lane (slot(j) of the owner's column, j < n), LF-mapped in place by the owner's
-        // letter; an interval that maps to nothing becomes (1, 0).  Returns the number of '#'-carrying intervals queued (pass 1).
-        auto flat_sweep = [&](uint32_t n, int c, bool top, bool queue) -> uint32_t {
-            uint32_t pre = n;
-            #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, pre, o); if ((int)lane >= o) pre += t; }
-            const uint32_t T = __shfl_sync(FULL, pre, 31);
-            uint32_t nq = 0;
-            __syncwarp();                                  // the columns were last written by their owners
-            for (uint32_t first = 0; first < T; first += 32) {
-                const uint32_t item = first + lane;
-                uint32_t own = 0;                          // the lane whose [pre - n, pre) holds item
-                #pragma unroll
-                for (int d = 16; d; d >>= 1) { const uint32_t t = __shfl_sync(FULL, pre, own + d - 1); if (t <= item) own += d; }
-                const uint32_t ostart = __shfl_sync(FULL, pre - n, own);
-                const int oc = __shfl_sync(FULL, c, own);
-                uint32_t rda = 0, rdb = 0;
-                if (item < T) {
-                    const uint32_t j = item - ostart;
-                    uint2& slot = s_list[(top ? cap - 1 - j : j) * FUSED_THREADS + wcol + own];
-                    const uint2 iv = slot;
-                    const uint32_t x0 = (oc & 1) ? 0u : 0xffffffffu, x1 = (oc & 2) ? 0u : 0xffffffffu;
-                    uint32_t rca, rcb, nblk;
-                    lf_range(ix.occ, iv.x, iv.y + 1, oc, x0, x1, rca, rcb, rda, rdb, nblk);
-                    const uint32_t Cc = s_Cl[oc];
-                    slot = rcb > rca ? make_uint2(Cc + rca, Cc + rcb - 1) : make_uint2(1u, 0u);
-                    if (STATS) { sBlk += nblk; if (rdb > rda) atomicAdd(&s_E[wcol + own], rdb - rda); }       // blocks: counted where they are fetched
-                }
-                if (queue) {
-                    const bool hasd = rdb > rda;
-                    const uint32_t bal = __ballot_sync(FULL, hasd);
-                    if (hasd) {
-                        const uint32_t pos = nq + __popc(bal & ((1u << lane) - 1u));
-                        if (pos < FLAT_QCAP) s_queue[wid][pos] = make_uint4(own, rda, rdb, 0u);
-                        else atomicOr(&s_punt[wid], 1u << own);
-                    }
-                    nq += __popc(bal);
-                }
-            }
-            __syncwarp();                                  // results and queue visible to the owners
-            return nq;
-        };
-        for (;;) {
-            const bool act = s < steps && nF && !ovf;
-            if (!__any_sync(FULL, act)) break;
-            int c = 0;
-            if (act) {
-                const uint32_t ci = m - L0 - s - 1;
-                if (ci < win_lo) {
-                    const uint32_t lo = win_lo > 32 ? win_lo - 32 : 0;
-                    fetch_codes(bytes + base + lo, win_lo - lo, s_lut, win);
-                    win_lo = lo;
-                }
-                c = (int)((win >> (2 * (ci - win_lo))) & 3u);
-            }
-            const bool beyond = STATS && act && (L0 + s >= kc);
-            if (STATS && act && L0 + s == mk) sI += nF;
-            if (lane == 0) s_punt[wid] = 0;
-            // ---- pass 1: F' = LF_c(F), fetched flat, then compacted / merged by its owner
-            uint32_t nq = flat_sweep(act ? nF : 0u, c, false, true);
-            if (nq > FLAT_QCAP) { if ((s_punt[wid] >> lane) & 1u) ovf = true; nq = FLAT_QCAP; }
-            if constexpr (FLAT == 2) {
-                // one gather for the whole warp instead of one dependent wait per owner (a range rarely holds a second '#')
-                if (nq) {
-                    if (lane < nq) s_qrec[wid][lane] = __ldg(ix.link_rec + s_queue[wid][lane].y);
-                    __syncwarp();
-                }
-            }
-            uint32_t nout = 0, ndol = 0;
-            if (act && !ovf) {
-                if (STATS) { sLF += nF; if (beyond) sS += nF; }
-                for (uint32_t j = 0; j < nF; ++j) {
-                    const uint2 r = LIST(j);
-                    if (r.x > r.y) continue;
-                    if (nout && LIST(nout - 1).y + 1 == r.x) LIST(nout - 1).y = r.y;
-                    else { LIST(nout) = r; ++nout; }
-                }
-                for (uint32_t t = 0; t < nq && !ovf; ++t) {
-                    const uint4 qe = s_queue[wid][t];
-                    if (qe.x != lane) continue;
-                    for (uint32_t e = qe.y; e < qe.z && !ovf; ++e) {
-                        const uint2 rec = (FLAT == 2 && e == qe.y) ? s_qrec[wid][t] : __ldg(ix.link_rec + e);
-                        if (rec.x <= rec.y) dol_insert(rec.x, rec.y, nout, ndol);          // x > y: string of the first segment
-                    }
-                }
-            }
-            // ---- pass 2: Dol' = LF_c(Dol), fetched flat, then F <- Dol' ++ F' by the owner
-            const uint32_t myD = (act && !ovf) ? ndol : 0u;
-            if (__any_sync(FULL, myD != 0)) {
-                flat_sweep(myD, c, true, false);
-                if (myD) {
-                    if (STATS) { sLF += ndol; if (beyond) sS += ndol; }
-                    uint32_t ndp = 0;
-                    for (uint32_t i = 0; i < ndol; ++i) {
-                        const uint2 r = DOL(i);
-                        if (r.x > r.y) continue;
-                        if (ndp && DOL(ndp - 1).y + 1 == r.x) DOL(ndp - 1).y = r.y;
-                        else { DOL(ndp) = r; ++ndp; }
-                    }
-                    if (ndp) {
-                        if (nout + 2 * ndp > cap) ovf = true;
-                        else {
-                            for (uint32_t j = nout; j > 0; --j) LIST(j - 1 + ndp) = LIST(j - 1);
-                            for (uint32_t i = 0; i < ndp; ++i) LIST(i) = DOL(i);
-                            nout += ndp;
-                        }
-                    }
-                }
-            }
-            if (STATS) { if (beyond) sE += s_E[threadIdx.x]; s_E[threadIdx.x] = 0; }
-            if (act && !ovf) { nF = nout; ++s; }
-            __syncwarp();                                  // s_punt / s_queue are rewritten by the next step
-        }
-    } else
     for (; s < steps && nF && !ovf; ++s) {
         const uint32_t ci = m - L0 - s - 1;
         if (ci < win_lo) {                                                // the next 32 characters to the left
@@ -342,8 +193,6 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         if (ovf) out.ovf_ids[atomicAdd(out.ovf_count, 1u)] = q;
     }
     if (STATS) {
-        if constexpr (FLAT != 0) { if (ovf) sI = sS = sE = sLF = 0; }     // the blocks a lane fetched belong to other lanes' patterns: kept
-        else
         if (ovf) sI = sS = sE = sLF = sBlk = 0;          // the level-synchronous engine redoes (and recounts) this pattern
         const unsigned long long v[5] = {sI, sS, sE, sLF, sBlk};
         unsigned long long* dst[5] = {&st->I, &st->S, &st->E, &st->lf_intervals, &st->occ_blocks};
@@ -358,32 +207,23 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
 }
 
 namespace {
-template <bool STATS, int MINB, int FLAT>
+template <bool STATS, int MINB>
 void launch_instance(unsigned grid, size_t smem, cudaStream_t s, const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
                      const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc) {
-    CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<STATS, MINB, FLAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
-    fused_search_kernel<STATS, MINB, FLAT><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+    CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<STATS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
+    fused_search_kernel<STATS, MINB><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
 }
 }  // namespace
 
-// flat (experimental first pass, A/B values of EDSBWT_FUSED_FLAT): 1 = warp-flat fetch at 10 CTAs/SM, 2 = the same compiled for
-// 12 CTAs/SM, 3 = warp-flat fetch + warp-wide link gather at 10 CTAs/SM.  Counting runs use the 10 CTAs/SM builds.
 void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
-                         const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s,
-                         int flat) {
+                         const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s) {
     if (npat == 0) return;
     const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
     const unsigned grid = (npat + FUSED_THREADS - 1) / FUSED_THREADS;
-#define INSTANCE(STATS, MINB, FLAT) launch_instance<STATS, MINB, FLAT>(grid, smem, s, ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc)
-    if (flat && cap <= 14) {             // experimental: first pass only
-        if (st) { if (flat == 3) INSTANCE(true, FLAT_MINB, 2); else INSTANCE(true, FLAT_MINB, 1); }
-        else if (flat == 3) INSTANCE(false, FLAT_MINB, 2);
-        else if (flat == 2) INSTANCE(false, 12, 1);
-        else INSTANCE(false, FLAT_MINB, 1);
-    }
-    else if (st) INSTANCE(true, 10, 0);
-    else if (cap <= 14) INSTANCE(false, 12, 0);      // 12 CTAs/SM: 40 registers (40 B of spill in a cold path), at most 14 KB of frontier each; 3.27 -> 3.09 ms
-    else INSTANCE(false, 10, 0);
+#define INSTANCE(STATS, MINB) launch_instance<STATS, MINB>(grid, smem, s, ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc)
+    if (st) INSTANCE(true, 10);
+    else if (cap <= 14) INSTANCE(false, 12);      // 12 CTAs/SM: 40 registers (40 B of spill in a cold path), at most 14 KB of frontier each; 3.27 -> 3.09 ms
+    else INSTANCE(false, 10);
 #undef INSTANCE
     CUDA_OK(cudaGetLastError());
 }

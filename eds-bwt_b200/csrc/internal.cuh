@@ -19,6 +19,7 @@ namespace edsbwt {
 // ---------------------------------------------------------------------------------------------------
 void set_error(const char* fmt, ...);
 struct Failure { int code; };
+struct OccOverflow {};      // a search found more occurrences than Index::occ_limit: the chunked callers halve the chunk and retry
 #define EDS_FAIL(code, ...) do { ::edsbwt::set_error(__VA_ARGS__); throw ::edsbwt::Failure{code}; } while (0)
 #define CUDA_OK(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { \
     ::edsbwt::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); \
@@ -207,11 +208,10 @@ __device__ __forceinline__ uint32_t low_mask(int below) {
 // when the range holds no '#' and lies inside one block).  After the seed lookup nearly every range is one or a few rows
 // inside ONE block: that case is a single sweep over the four 32-row words (letter mask computed once, '#' ranks only
 // when a '#' is present).  nblk = Occ blocks fetched (1 or 2).
-__device__ __forceinline__ void lf_range(const uint4* __restrict__ occ, uint32_t a, uint32_t b, int c, uint32_t x0, uint32_t x1,
-                                         uint32_t& rca, uint32_t& rcb, uint32_t& rda, uint32_t& rdb, uint32_t& nblk) {
+// B = block a >> 7, already in registers (the item kernel issues the fetch one stage before it consumes it)
+__device__ __forceinline__ void lf_range_loaded(Blk& B, const uint4* __restrict__ occ, uint32_t a, uint32_t b, int c, uint32_t x0, uint32_t x1,
+                                                uint32_t& rca, uint32_t& rcb, uint32_t& rda, uint32_t& rdb, uint32_t& nblk) {
     const uint32_t blkA = a >> 7, blkB = b >> 7;
-    Blk B;
-    load_blk(occ, blkA, B);
     if (blkA == blkB) {
         const int offA = (int)(a & 127u), offB = (int)(b & 127u);
         uint32_t r = c == 0 ? B.w[0] : c == 1 ? B.w[4] : c == 2 ? B.w[8] : B.w[12];
@@ -241,6 +241,12 @@ __device__ __forceinline__ void lf_range(const uint4* __restrict__ occ, uint32_t
         rdb = blkB * OCC_ROWS - letters_before(B) + kb;
         nblk = 2;
     }
+}
+__device__ __forceinline__ void lf_range(const uint4* __restrict__ occ, uint32_t a, uint32_t b, int c, uint32_t x0, uint32_t x1,
+                                         uint32_t& rca, uint32_t& rcb, uint32_t& rda, uint32_t& rdb, uint32_t& nblk) {
+    Blk B;
+    load_blk(occ, a >> 7, B);
+    lf_range_loaded(B, occ, a, b, c, x0, x1, rca, rcb, rda, rdb, nblk);
 }
 
 #endif
@@ -278,6 +284,22 @@ struct SeedView { const uint32_t* off[17]; const uint2* iv[17]; const uint32_t* 
                   const uint4* first; uint32_t first_level; };   // deepest level: {lo, hi of the first interval, offset, count} per key -- one gather instead of two
 // plist entries of patterns no longer than the seed depth reference the seed table itself (no copy): y = PLIST_SEED | level << 27 | n
 constexpr uint32_t PLIST_SEED = 0x80000000u, PLIST_N_MASK = 0x07ffffffu;
+// ... and a final frontier of ONE interval travels inside its plist entry: x = first row, y = PLIST_INLINE; the interval's
+// length is the pattern's count (items.cu; read by the locate kernels)
+constexpr uint32_t PLIST_INLINE = 0x40000000u;
+
+// Patterns as 2-bit codes (items.cu).  Pattern q of m characters occupies ceil(m/32) 64-bit words starting at word
+//   q * stride                            (poff == nullptr: every pattern has fixed_len characters, stride = ceil(fixed_len/32))
+//   ((poff[q] - poff[0]) >> 5) + q        (variable lengths: a closed form that never overlaps, no scan needed)
+// word w holds characters [max(0, m - 32(w+1)), m - 32w), the last of them in bits 62..63, code = rank of the letter in
+// the index alphabet.  invalid: bit q & 31 of word q >> 5 is set when pattern q holds a byte outside the alphabet (such a
+// pattern has 0 occurrences); nullptr = all valid.
+struct PackedPats {
+    const uint64_t* words;
+    const uint64_t* poff;
+    const uint32_t* invalid;
+    uint32_t fixed_len, stride;
+};
 
 struct StatsDev { unsigned long long I, S, E, L, O, lf_intervals, occ_blocks, overflow; };
 
@@ -294,6 +316,7 @@ struct Pipe {
     cudaStream_t in = nullptr, outs = nullptr;
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
     DevBuf<uint8_t> bytes[2]; DevBuf<uint64_t> off[2];
+    DevBuf<uint64_t> words[2]; DevBuf<uint32_t> invalid[2];      // packed batches (edsbwt_search_into_packed)
     SearchOut res[2];
     ~Pipe() { for (int i = 0; i < 2; ++i) { if (ev_in[i]) cudaEventDestroy(ev_in[i]); if (ev_out[i]) cudaEventDestroy(ev_out[i]); }
               if (in) cudaStreamDestroy(in); if (outs) cudaStreamDestroy(outs); }
@@ -358,10 +381,10 @@ struct Index {
     uint64_t l2_persist_bytes = 0;      // persisting-L2 carve-out granted for the Occ array
     std::shared_ptr<ResultPool> pool = std::make_shared<ResultPool>();
     uint32_t chunk_patterns = 1u << 21;     // patterns per pipeline chunk of the host-buffer searches
+    uint64_t occ_limit = 0xfffffff0ull;     // occurrences one search may produce (32-bit offsets); EDSBWT_OCC_LIMIT lowers it (tests of the chunk-halving path)
     edsbwt_stats last{};
     int collect_counters = 0; uint32_t canonical_k = 12;
     int engine = EDSBWT_ENGINE_FUSED; uint32_t fused_cap = 13, fused_cap2 = FUSED_BIG_CAP;
-    int fused_flat = 0;                 // experimental warp-flat first pass (EDSBWT_ENGINE_FUSED_FLAT); 2, 3 = its A/B variants
     bool fused_cap_auto = true;         // no explicit fused_cap: a batch that overflows the default slots in > 0.1 % of its patterns switches later batches to 20
     uint64_t device_bytes() const;
     ~Index();
@@ -373,10 +396,17 @@ Lut make_lut(const HostIndex& h);
 void build_occ_blocks(const uint8_t* d_bytes, uint32_t n, const Lut& lut, DevBuf<uint4>& occ, DevBuf<uint8_t>& cubtmp, cudaStream_t s,
                       uint32_t tot[4], unsigned int* bad_out);
 void build_device_index(Index& ix, const edsbwt_open_opts& o);
+// what a call knows about its batch besides bytes + offsets
+struct PatHint {
+    uint32_t fixed_len = 0;              // > 0: every pattern has this many characters; pattern q starts at byte fixed_base + q * fixed_len of d_bytes (d_off may be null)
+    uint64_t fixed_base = 0;
+    const uint64_t* d_words = nullptr;   // the caller's own 2-bit words (PackedPats layout, stride ceil(fixed_len / 32)); d_bytes may then be null
+    const uint32_t* d_invalid = nullptr; // with d_words: bitmap of patterns that hold a byte outside the alphabet (null: none)
+};
 void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat, uint64_t total_bytes,
-                uint32_t max_len, bool locate, int lf_variant, SearchOut& out, uint32_t pat_base = 0);
+                uint32_t max_len, bool locate, int lf_variant, SearchOut& out, uint32_t pat_base = 0, const PatHint* hint = nullptr);
 
-// fused.cu -- one thread per pattern, whole backward search in one launch
+// fused.cu -- the step-loop kernel: one thread per pattern (second pass over the patterns that outgrew the item kernel; A/B engine)
 struct FusedOut {
     uint2*    plist;        // [npat] (first slot in staging, number of final intervals)
     uint32_t* counts;       // [npat] number of occurrences ("Found N")
@@ -388,8 +418,15 @@ struct FusedOut {
     uint32_t* alive;        // optional [npat]: longest pattern suffix with a non-empty frontier (edsbwt_search_trace)
 };
 void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
-                         const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s,
-                         int flat = 0);      // 1..3: experimental warp-flat first pass (variants: fused.cu)
+                         const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc, cudaStream_t s);
+
+// items.cu -- the hot kernel: persistent warps, one item per lane per sweep, lanes refilled from a pool of patterns
+void launch_pack_patterns(const uint8_t* d_bytes, const uint64_t* d_off, uint32_t fixed_len, uint64_t fixed_base, uint32_t stride, uint32_t npat,
+                          const uint8_t* d_lut, uint64_t* words, uint64_t nwords, uint32_t* invalid, uint32_t* err, cudaStream_t s);
+void launch_unpack_patterns(const uint64_t* words, uint32_t fixed_len, uint32_t stride, const uint32_t* ids, uint32_t nsub, uint64_t letters,
+                            const uint32_t* invalid, uint8_t* bytes, cudaStream_t s);
+void launch_items_search(const IndexView& ix, const SeedView& sv, uint32_t k, const PackedPats& pp, uint32_t npat, uint32_t cap, const FusedOut& out,
+                         uint32_t* work, StatsDev* st, uint32_t kc, cudaStream_t s);
 
 // move.cu
 void build_move_table(Index& ix);

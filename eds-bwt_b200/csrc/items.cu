@@ -1,0 +1,401 @@
+// The hot kernel (round 2): persistent warps, one ITEM per lane per sweep, lanes refilled with new patterns.
+//
+//   reference per-pattern loop     EDSBWT::backwardSearch   EDSBWTsearch.cpp:619-772   (the loop :660-722 is what a lane runs)
+//   LF of every frontier interval  updateIntervals / updateSingleInterval / rankManySymbols / MergeAndRemove   :841-1209
+//   segment jump                   link / dollars_in_interval / preceding_dollars_finder   :1212-1307
+//
+// The step-loop kernel of round 1 (fused.cu) gave every pattern a thread and walked its frontier in a per-thread loop:
+// ncu counted 14.9 of 32 lanes active per instruction (patterns that died early, frontiers of different length, one lane
+// in twenty waiting alone for a link record).  Here a warp is a pool of 32 independent state machines.  In every sweep
+// each lane (1) ISSUES the one memory fetch its pattern needs next -- a 64-byte Occ block (two 256-bit loads), a seed
+// entry, a link record, a further seed interval or the next 32 pattern characters -- and only then (2) CONSUMES it and
+// moves its state on.  All 32 fetches of a sweep are in flight together whatever they are, so a link record or a seed
+// lookup costs its lane one sweep instead of stalling the warp, and a lane whose pattern is finished takes the next
+// pattern from the warp's pool (32 patterns fetched coalesced, refilled from a global cursor: the warp-cooperative part)
+// in the very next sweep.  Semantics are those of the step loop, statement for statement: same frontier lists
+// (Dol' ++ F'), same merge rule, same overflow conditions, same byte-model counters.
+//
+// Patterns arrive as 2-bit codes (PackedPats, internal.cuh): produced by pack_patterns_kernel below from the caller's
+// bytes, or by the caller itself (edsbwt_search_into_packed).
+#include "internal.cuh"
+
+namespace edsbwt {
+
+// ---------------------------------------------------------------------------------------------------
+// bytes -> 2-bit words.  Pattern q of m characters occupies ceil(m/32) words; word w holds characters
+// [max(0, m - 32(w+1)), m - 32w) with the LAST of them in bits 62..63 (a short head is padded with zero bits below):
+// the backward search consumes word 0 from the top down, the seed key is its top min(m, k) characters.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+pack_patterns_kernel(const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ poff, uint32_t fixed_len, uint64_t fixed_base, uint32_t stride,
+                     uint32_t npat, const uint8_t* __restrict__ lut, uint64_t* __restrict__ words, uint64_t nwords, uint32_t* __restrict__ invalid,
+                     uint32_t* __restrict__ err) {
+    __shared__ uint8_t s_lut[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) s_lut[i] = lut[i];
+    __syncthreads();
+    const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    bool bad = false;
+    if (q < npat) {
+        uint64_t base, wb; uint32_t m;
+        if (poff) {
+            base = __ldg(poff + q);
+            const uint64_t len64 = __ldg(poff + q + 1) - base;
+            m = len64 > 0xffffffffull ? 0u : (uint32_t)len64;
+            wb = ((base - __ldg(poff)) >> 5) + q;
+        } else { base = fixed_base + (uint64_t)q * fixed_len; m = fixed_len; wb = (uint64_t)q * stride; }
+        if (wb + (m + 31) / 32 > nwords) { *err = 1u; bad = true; m = 0; }      // the caller's total_bytes does not cover the offsets: nothing is written, the call fails
+        for (uint32_t hi = m, w = 0; hi > 0; ++w) {
+            const uint32_t lo = hi > 32 ? hi - 32 : 0, n = hi - lo;
+            uint64_t cw;
+            if (!fetch_codes(bytes + base + lo, n, s_lut, cw)) bad = true;
+            words[wb + w] = cw << (2 * (32 - n));
+            hi = lo;
+        }
+    }
+    const uint32_t bal = __ballot_sync(0xffffffffu, bad);       // q >> 5 is the same for the whole warp
+    if ((threadIdx.x & 31) == 0 && q < npat) invalid[q >> 5] = bal;
+}
+
+void launch_pack_patterns(const uint8_t* d_bytes, const uint64_t* d_off, uint32_t fixed_len, uint64_t fixed_base, uint32_t stride, uint32_t npat,
+                          const uint8_t* d_lut, uint64_t* words, uint64_t nwords, uint32_t* invalid, uint32_t* err, cudaStream_t s) {
+    if (npat == 0) return;
+    pack_patterns_kernel<<<(npat + 127) / 128, 128, 0, s>>>(d_bytes, d_off, fixed_len, fixed_base, stride, npat, d_lut, words, nwords, invalid, err);
+    CUDA_OK(cudaGetLastError());
+}
+
+// words -> characters of the patterns listed in ids (nullptr: all), pattern q at bytes[q * fixed_len ..): the rare patterns
+// that outgrow the item kernel's frontier go to the step-loop kernel / the level-synchronous engine, which read characters.
+// Only needed when the caller handed in packed patterns, i.e. no bytes exist on the device.  A pattern flagged invalid
+// gets the end-marker byte, which no tier accepts.  letters: the (up to) four alphabet bytes, letter c in bits 8c..8c+7.
+__global__ void unpack_patterns_kernel(const uint64_t* __restrict__ words, uint32_t fixed_len, uint32_t stride, const uint32_t* __restrict__ ids,
+                                       uint32_t nsub, uint32_t letters, uint32_t bad_byte, const uint32_t* __restrict__ invalid, uint8_t* __restrict__ bytes) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nsub) return;
+    const uint32_t q = ids ? ids[t] : t;
+    const bool inv = invalid && ((__ldg(invalid + (q >> 5)) >> (q & 31u)) & 1u);
+    for (uint32_t i = 0; i < fixed_len; ++i) {
+        const uint32_t back = fixed_len - 1 - i;             // characters from the end: word back / 32, position 31 - back % 32
+        const uint64_t w = __ldg(words + (uint64_t)q * stride + (back >> 5));
+        const uint32_t c = (uint32_t)(w >> (2 * (31 - (back & 31u)))) & 3u;
+        bytes[(uint64_t)q * fixed_len + i] = inv ? (uint8_t)bad_byte : (uint8_t)(letters >> (8 * c));
+    }
+}
+void launch_unpack_patterns(const uint64_t* words, uint32_t fixed_len, uint32_t stride, const uint32_t* ids, uint32_t nsub, uint64_t letters,
+                            const uint32_t* invalid, uint8_t* bytes, cudaStream_t s) {
+    if (nsub == 0) return;
+    unpack_patterns_kernel<<<(nsub + 127) / 128, 128, 0, s>>>(words, fixed_len, stride, ids, nsub, (uint32_t)(letters >> 8), (uint32_t)(letters & 255u), invalid, bytes);
+    CUDA_OK(cudaGetLastError());
+}
+
+namespace {
+
+enum : uint32_t {
+    K_IDLE = 0,      // no pattern: takes one from the warp's pool
+    K_OCCF,          // fetch: Occ block of F[j]           (pass 1: F' = LF_c(F), '#' rows -> link)
+    K_OCCD,          // fetch: Occ block of Dol[j]         (pass 2: Dol' = LF_c(Dol))
+    K_SEED,          // fetch: first[key] of the deepest seed level (16 B)
+    K_LD64,          // kinds >= K_LD64 fetch 8 bytes at ptr:
+    K_LINK = K_LD64, //   link record of the next '#' row inside F[j]
+    K_SEEDIV,        //   a further interval of the seed entry
+    K_WORD,          //   the next 32 pattern characters
+    // transitions, resolved inside the sweep that raises them (no fetch)
+    K_ENDP1, K_ENDP2, K_STEP, K_FIN
+};
+
+__device__ __forceinline__ void ld128(const void* p, uint32_t* r) {
+    asm volatile("ld.global.nc.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "l"(p));
+}
+__device__ __forceinline__ void ld64(const void* p, uint32_t* r) {
+    asm volatile("ld.global.nc.v2.b32 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "l"(p));
+}
+
+}  // namespace
+
+template <bool STATS, int MINB>
+__global__ void __launch_bounds__(FUSED_THREADS, MINB)
+search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant__ SeedView sv, uint32_t k, const __grid_constant__ PackedPats pp,
+                    uint32_t npat, uint32_t cap, FusedOut out, uint32_t* __restrict__ work, StatsDev* __restrict__ st, uint32_t kc) {
+    extern __shared__ uint2 s_list[];                 // [cap][FUSED_THREADS]: column of the lane = its frontier (F from the bottom, Dol from the top)
+    __shared__ const uint32_t* s_off[17];             // runtime-indexed kernel parameters would live in local memory
+    __shared__ const uint2* s_iv[17];
+    __shared__ const uint32_t* s_cnt[17];
+    __shared__ uint32_t s_Cl[5];
+    if (threadIdx.x < 17) { s_off[threadIdx.x] = sv.off[threadIdx.x]; s_iv[threadIdx.x] = sv.iv[threadIdx.x]; s_cnt[threadIdx.x] = sv.cnt[threadIdx.x]; }
+    if (threadIdx.x < 5) s_Cl[threadIdx.x] = ix.Cl[threadIdx.x];
+    __syncthreads();
+#define LIST(j) s_list[(j) * FUSED_THREADS + threadIdx.x]
+#define DOL(i) s_list[(cap - 1 - (i)) * FUSED_THREADS + threadIdx.x]
+    constexpr uint32_t FULL = 0xffffffffu;
+    const uint32_t lane = threadIdx.x & 31u;
+
+    // ---- the warp's pool: 32 consecutive patterns, entry i in the registers of lane i
+    uint32_t pool_q = 0, pool_m = 0, pool_wb = 0, pool_pos = 0, pool_n = 0;
+    uint64_t pool_w = 0;
+    bool exhausted = false;
+    auto grab_pool = [&]() {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(work, 32u);
+        base = __shfl_sync(FULL, base, 0);
+        pool_pos = 0;
+        if (base >= npat) { exhausted = true; pool_n = 0; return; }
+        pool_n = npat - base < 32u ? npat - base : 32u;
+        pool_q = base + lane; pool_m = 0; pool_w = 0;
+        if (lane < pool_n) {
+            uint32_t mm;
+            if (pp.poff) {
+                const uint64_t a = __ldg(pp.poff + pool_q), len64 = __ldg(pp.poff + pool_q + 1) - a;
+                mm = len64 > 0xffffffffull ? 0u : (uint32_t)len64;
+                pool_wb = (uint32_t)(((a - __ldg(pp.poff)) >> 5) + pool_q);
+            } else { mm = pp.fixed_len; pool_wb = pool_q * pp.stride; }
+            if (pp.invalid && ((__ldg(pp.invalid + (pool_q >> 5)) >> (pool_q & 31u)) & 1u)) mm = 0;
+            pool_m = mm;
+            if (mm) pool_w = __ldg(pp.words + pool_wb);
+        }
+    };
+
+    // ---- lane state
+    uint32_t kind = K_IDLE, q = 0, m = 0, spos = 0, wb = 0;     // spos = length of the pattern suffix matched so far
+    uint64_t win = 0;                                             // word spos >> 5 of the pattern
+    uint32_t nF = 0, j = 0, nout = 0, ndol = 0;
+    uint32_t aux = 0;                                             // pass 1: link records left of F[j] (rem); pass 2: length of Dol' (ndp)
+#define rem aux
+#define ndp aux
+    const uint2* ptr = nullptr;                                   // K_SEED: &first[key]; K_LD64 kinds: the 8 bytes wanted
+    bool ovf = false;
+    unsigned long long sI = 0, sS = 0, sE = 0, sLF = 0, sBlk = 0;     // counting runs: totals of the lane ...
+    uint32_t tI = 0, tS = 0, tE = 0, tLF = 0, tBlk = 0;               // ... and of its current pattern (dropped when it overflows)
+
+    grab_pool();
+    for (;;) {
+        // ---------------- refill: idle lanes take the next patterns of the pool
+        const uint32_t idle = __ballot_sync(FULL, kind == K_IDLE);
+        if (idle) {
+            const uint32_t avail = pool_n - pool_pos;
+            if (avail) {
+                const uint32_t r = __popc(idle & ((1u << lane) - 1u));
+                const uint32_t src = (pool_pos + r) & 31u;
+                const uint32_t tq = __shfl_sync(FULL, pool_q, src), tm = __shfl_sync(FULL, pool_m, src), twb = __shfl_sync(FULL, pool_wb, src);
+                const uint64_t tw = __shfl_sync(FULL, pool_w, src);
+                if (kind == K_IDLE && r < avail) {
+                    q = tq; m = tm; win = tw; wb = twb; ovf = false;
+                    if (STATS) tI = tS = tE = tLF = tBlk = 0;
+                    if (m == 0) {                                 // empty pattern or a byte outside the alphabet: 0 occurrences
+                        out.counts[q] = 0; out.plist[q] = make_uint2(0u, 0u);
+                        if (out.alive) out.alive[q] = 0;
+                    } else {
+                        spos = m < k ? m : k;
+                        const uint32_t key = (uint32_t)(win >> (64 - 2 * spos));
+                        ptr = (const uint2*)(sv.first + key);
+                        kind = K_SEED;
+                    }
+                }
+                const uint32_t taken = __popc(idle);
+                pool_pos += taken < avail ? taken : avail;
+                if (pool_pos >= pool_n && !exhausted) grab_pool();      // its loads are first used by the shuffles of the next sweep
+            } else if (exhausted) {
+                if (idle == FULL) break;
+            } else grab_pool();
+        }
+
+        // ---------------- issue: one fetch per lane, all in flight together
+        uint32_t B[16];
+        if (kind == K_OCCF || kind == K_OCCD) {
+            const uint32_t row = kind == K_OCCF ? LIST(j).x : DOL(j).x;
+            const uint4* p = ix.occ + (size_t)(row >> 7) * 4;
+            ld256(p, B); ld256(p + 2, B + 8);
+        } else if (kind == K_SEED) {
+            if (sv.first && spos == sv.first_level) ld128(ptr, B);
+        } else if (kind >= K_LD64) {
+            ld64(ptr, B);
+        }
+
+        // ---------------- consume
+        if (kind == K_OCCF || kind == K_OCCD) {
+            const int c = (int)((win >> (2 * (31 - (spos & 31u)))) & 3u);
+            const uint32_t x0 = (c & 1) ? 0u : 0xffffffffu, x1 = (c & 2) ? 0u : 0xffffffffu;
+            uint32_t rca, rcb, rda, rdb, nblk;
+            const uint2 iv = kind == K_OCCF ? LIST(j) : DOL(j);
+            lf_range_loaded(*reinterpret_cast<Blk*>(B), ix.occ, iv.x, iv.y + 1, c, x0, x1, rca, rcb, rda, rdb, nblk);
+            if (STATS) { tLF += 1; tBlk += nblk; if (spos >= kc) { tS += 1; tE += rdb - rda; } }
+            const uint32_t Cc = s_Cl[c];
+            if (kind == K_OCCF) {
+                if (rcb > rca) {
+                    const uint32_t nlo = Cc + rca, nhi = Cc + rcb - 1;
+                    if (nout && LIST(nout - 1).y + 1 == nlo) LIST(nout - 1).y = nhi;
+                    else { LIST(nout) = make_uint2(nlo, nhi); ++nout; }
+                }
+                if (rdb > rda) { kind = K_LINK; ptr = ix.link_rec + rda; rem = rdb - rda; }
+                else if (++j == nF) kind = K_ENDP1;
+            } else {
+                if (rcb > rca) {
+                    const uint32_t nlo = Cc + rca, nhi = Cc + rcb - 1;
+                    if (ndp && DOL(ndp - 1).y + 1 == nlo) DOL(ndp - 1).y = nhi;
+                    else { DOL(ndp) = make_uint2(nlo, nhi); ++ndp; }
+                }
+                if (++j == ndol) kind = K_ENDP2;
+            }
+        } else if (kind == K_LINK) {
+            // pile-0 range [l, h] of the preceding segment(s) -> sorted, merged Dol set at the top of the column
+            uint32_t l = B[0], h = B[1];
+            if (l <= h) {                                         // l > h: string of the first segment, no predecessor
+                uint32_t i = 0;
+                while (i < ndol && DOL(i).y + 1 < l) ++i;
+                if (i < ndol && DOL(i).x <= h + 1) {              // overlaps / touches D[i]: merge, then absorb followers
+                    const uint2 d = DOL(i);
+                    l = l < d.x ? l : d.x; h = h > d.y ? h : d.y;
+                    uint32_t t = i + 1;
+                    while (t < ndol && DOL(t).x <= h + 1) { const uint32_t y = DOL(t).y; h = h > y ? h : y; ++t; }
+                    DOL(i) = make_uint2(l, h);
+                    if (t > i + 1) { for (uint32_t u = t; u < ndol; ++u) DOL(i + 1 + (u - t)) = DOL(u); ndol -= t - (i + 1); }
+                } else if (nF + ndol + 1 >= cap) { ovf = true; kind = K_FIN; }
+                else {                                            // insert before i
+                    for (uint32_t u = ndol; u > i; --u) DOL(u) = DOL(u - 1);
+                    DOL(i) = make_uint2(l, h);
+                    ++ndol;
+                }
+            }
+            if (!ovf) {
+                ++ptr;
+                if (--rem == 0) kind = (++j == nF) ? K_ENDP1 : K_OCCF;
+            }
+        } else if (kind == K_SEED) {
+            // seed entry of the last spos characters: frontier after the first min(m, k) backward steps
+            const uint32_t L0 = spos, key = (uint32_t)(win >> (64 - 2 * L0));
+            uint32_t a, n0; uint2 iv0 = make_uint2(1u, 0u);
+            if (sv.first && L0 == sv.first_level) { iv0 = make_uint2(B[0], B[1]); a = B[2]; n0 = B[3]; }
+            else { a = __ldg(s_off[L0] + key); n0 = __ldg(s_off[L0] + key + 1) - a; if (n0) iv0 = __ldg(s_iv[L0] + a); }
+            if (n0 && m == L0 && n0 <= PLIST_N_MASK) {
+                // pattern no longer than the seed depth: the table IS the answer (count from the per-key table, the result list
+                // is a reference into the seed intervals; a short key's frontier can hold thousands of them)
+                uint32_t dc = 0;
+                if (s_cnt[L0]) dc = __ldg(s_cnt[L0] + key);
+                else for (uint32_t t = 0; t < n0; ++t) { const uint2 v = __ldg(s_iv[L0] + a + t); dc += v.y - v.x + 1; }
+                out.counts[q] = dc; out.plist[q] = make_uint2(a, PLIST_SEED | (L0 << 27) | n0);
+                if (out.alive) out.alive[q] = m;
+                if (STATS) { if (m <= kc) sI += n0; }
+                kind = K_IDLE;
+            } else if (n0 > cap) { ovf = true; kind = K_FIN; }
+            else {
+                nF = n0;
+                if (n0) LIST(0) = iv0;
+                if (n0 > 1) { kind = K_SEEDIV; j = 1; ptr = s_iv[L0] + a + 1; }
+                else kind = K_STEP;
+            }
+        } else if (kind == K_SEEDIV) {
+            LIST(j) = make_uint2(B[0], B[1]);
+            ++ptr;
+            if (++j == nF) kind = K_STEP;
+        } else if (kind == K_WORD) {
+            win = ((uint64_t)B[1] << 32) | B[0];
+            kind = K_OCCF; j = 0; nout = 0; ndol = 0;
+        }
+
+        // ---------------- transitions
+        if (kind == K_ENDP1) {
+            if (ndol) { kind = K_OCCD; j = 0; ndp = 0; }
+            else { nF = nout; ++spos; kind = K_STEP; }
+        }
+        if (kind == K_ENDP2) {                                    // F <- Dol' ++ F'
+            if (ndp) {
+                if (nout + 2 * ndp > cap) { ovf = true; kind = K_FIN; }
+                else {
+                    for (uint32_t t = nout; t > 0; --t) LIST(t - 1 + ndp) = LIST(t - 1);
+                    for (uint32_t i = 0; i < ndp; ++i) LIST(i) = DOL(i);
+                    nout += ndp;
+                }
+            }
+            if (!ovf) { nF = nout; ++spos; kind = K_STEP; }
+        }
+        if (kind == K_STEP) {                                     // the frontier of the suffix of length spos is complete
+            if (STATS && spos == (m < kc ? m : kc)) tI += nF;
+            if (spos == m || nF == 0) kind = K_FIN;
+            else if ((spos & 31u) == 0) { kind = K_WORD; ptr = (const uint2*)(pp.words + wb + (spos >> 5)); }
+            else { kind = K_OCCF; j = 0; nout = 0; ndol = 0; }
+        }
+        if (kind == K_FIN) {
+            // ---- results: count + the final interval list.  One interval (nearly every found pattern) travels inside the
+            //      plist entry itself -- its end follows from the count -- longer lists are staged contiguously
+            if (ovf) nF = 0;
+            uint32_t cnt = 0;
+            for (uint32_t t = 0; t < nF; ++t) { const uint2 v = LIST(t); cnt += v.y - v.x + 1; }
+            uint2 pl = make_uint2(0u, 0u);
+            if (nF == 1) pl = make_uint2(LIST(0).x, PLIST_INLINE);
+            else if (nF > 1) {
+                const uint32_t my = atomicAdd(out.cursor, nF);
+                if ((uint64_t)my + nF > out.staging_cap) { ovf = true; cnt = 0; }
+                else { for (uint32_t t = 0; t < nF; ++t) out.staging[my + t] = LIST(t); pl = make_uint2(my, nF); }
+            }
+            out.plist[q] = pl; out.counts[q] = cnt;
+            if (ovf) out.ovf_ids[atomicAdd(out.ovf_count, 1u)] = q;
+            else {
+                if (out.alive) {
+                    // where the frontier died ("Pattern not found, interrupted in position", EDSBWTsearch.cpp:714-717)
+                    const uint32_t L0 = m < k ? m : k;
+                    uint32_t la = 0;
+                    if (nF) la = m;
+                    else if (spos > L0) la = spos - 1;
+                    else {                                        // empty seed entry: longest shorter suffix that is not
+                        const uint32_t key = (uint32_t)(win >> (64 - 2 * L0));
+                        for (uint32_t L = L0 - 1; L >= 1; --L) {
+                            const uint32_t kl = key >> (2 * (L0 - L));
+                            if (__ldg(s_off[L] + kl + 1) > __ldg(s_off[L] + kl)) { la = L; break; }
+                        }
+                    }
+                    out.alive[q] = la;
+                }
+                if (STATS) { sI += tI; sS += tS; sE += tE; sLF += tLF; sBlk += tBlk; }
+            }
+            kind = K_IDLE;
+        }
+    }
+    if (STATS) {
+        const unsigned long long v[5] = {sI, sS, sE, sLF, sBlk};
+        unsigned long long* dst[5] = {&st->I, &st->S, &st->E, &st->lf_intervals, &st->occ_blocks};
+        #pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            unsigned long long x = v[i];
+            for (int o = 16; o; o >>= 1) x += __shfl_xor_sync(FULL, x, o);
+            if (lane == 0 && x) atomicAdd(dst[i], x);
+        }
+    }
+#undef LIST
+#undef DOL
+#undef rem
+#undef ndp
+}
+
+namespace {
+template <bool STATS, int MINB>
+void launch_items_instance(size_t smem, cudaStream_t s, const IndexView& ix, const SeedView& sv, uint32_t k, const PackedPats& pp, uint32_t npat,
+                           uint32_t cap, const FusedOut& out, uint32_t* work, StatsDev* st, uint32_t kc) {
+    auto kern = search_items_kernel<STATS, MINB>;
+    CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
+    int dev = 0, sms = 148, per_sm = 1;
+    CUDA_OK(cudaGetDevice(&dev));
+    CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FUSED_THREADS, smem));
+    if (per_sm < 1) per_sm = 1;
+    // persistent: one wave of CTAs, every warp pulls pools of 32 patterns until the batch is empty
+    const unsigned want = (npat + FUSED_THREADS - 1) / FUSED_THREADS, wave = (unsigned)(sms * per_sm);
+    const unsigned grid = want < wave ? want : wave;
+    kern<<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, pp, npat, cap, out, work, st, kc);
+}
+}  // namespace
+
+// work: device counter, zeroed by the caller (the next unclaimed pattern)
+void launch_items_search(const IndexView& ix, const SeedView& sv, uint32_t k, const PackedPats& pp, uint32_t npat, uint32_t cap, const FusedOut& out,
+                         uint32_t* work, StatsDev* st, uint32_t kc, cudaStream_t s) {
+    if (npat == 0) return;
+    if (npat > 0xff000000u) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 - 2^24 patterns in one search call; split the batch");
+    const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
+    const char* e = getenv("EDSBWT_ITEMS_MINB");      // A/B of the occupancy target (profiles/scripts/r02_items_ab.py)
+    const int minb = e ? atoi(e) : 0;
+    if (st) launch_items_instance<true, 8>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    else if (cap > 16 || minb == 8) launch_items_instance<false, 8>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    else if (minb == 9) launch_items_instance<false, 9>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    else if (minb == 12) launch_items_instance<false, 12>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    else launch_items_instance<false, 10>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    CUDA_OK(cudaGetLastError());
+}
+
+}  // namespace edsbwt

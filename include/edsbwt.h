@@ -63,11 +63,12 @@ typedef struct {
 
 #define EDSBWT_LOCATE_SA    0   /* row -> (string, offset) table in HBM: one gather per occurrence           */
 #define EDSBWT_LOCATE_WALK  1   /* LF-walk each row to its string start (the reference's a9/a13 arithmetic)  */
-#define EDSBWT_ENGINE_FUSED     0   /* one thread per pattern, one launch; oversized frontiers fall through to: */
-#define EDSBWT_ENGINE_LEVELSYNC 1   /* level-synchronous interval-parallel engine (also builds the seed table)   */
-#define EDSBWT_ENGINE_FUSED_FLAT 2  /* EXPERIMENTAL, not yet timed: ENGINE_FUSED whose first pass fetches the Occ  */
-                                    /* blocks of a warp's 32 frontiers laid end to end; also */
-                                    /* selected for ENGINE_FUSED handles by the environment variable EDSBWT_FUSED_FLAT=1 (2, 3: A/B variants, fused.cu) */
+#define EDSBWT_ENGINE_FUSED      0  /* whole backward search in one launch: persistent warps, one frontier item per lane */
+                                    /* per sweep, finished lanes refilled with new patterns (items.cu); frontiers that   */
+                                    /* outgrow it go to the step-loop kernel with 192 slots and then to:                 */
+#define EDSBWT_ENGINE_LEVELSYNC  1  /* level-synchronous interval-parallel engine (also builds the seed table)           */
+#define EDSBWT_ENGINE_FUSED_STEP 2  /* round-1 hot kernel as the first pass: one thread per pattern, per-thread step loop */
+                                    /* (fused.cu; kept as the second pass of ENGINE_FUSED and for A/B measurements)       */
 #define EDSBWT_LF_RANK      0   /* EDSBWTsearch:      LF by blocked rank                                      */
 #define EDSBWT_LF_MOVE      1   /* MOVE_EDSBWTSearch: LF by move table                                        */
 
@@ -76,12 +77,12 @@ typedef struct {
                                   /* eBWT position of the string-start row; MOVE: frontier order, ascending row)     */
 
 typedef struct {
-    int32_t  seed_k;            /* -1 = auto (min(12, floor(log4 n) - 1)), 0 = no seed table                  */
+    int32_t  seed_k;            /* -1 = auto: floor(log4 n), at most 14; values below 1 are raised to 1        */
     int32_t  locate_mode;       /* EDSBWT_LOCATE_SA / _WALK                                                   */
     int32_t  verify;            /* 1 = cross-check _bv_<p>.aux (rrr) and tableOcc against the pile bytes      */
     int32_t  build_move;        /* 1 = also build the move table (EDSBWT_LF_MOVE searches)                    */
-    int32_t  engine;            /* EDSBWT_ENGINE_FUSED (default) / _LEVELSYNC / _FUSED_FLAT                   */
-    int32_t  fused_cap;         /* frontier slots per pattern of the fused kernel (0 = default 13: 12 CTAs per SM; above 14: 10 CTAs) */
+    int32_t  engine;            /* EDSBWT_ENGINE_FUSED (default) / _LEVELSYNC / _FUSED_STEP                   */
+    int32_t  fused_cap;         /* frontier slots per pattern of the first pass (0 = default 13)                */
     int32_t  fused_cap2;        /* slots of the second pass over the patterns that outgrew the first (0 = 192) */
     int32_t  move_a;            /* balancing parameter a of the move table (build_MLF's <a>); 0 = default 8             */
 } edsbwt_open_opts;
@@ -133,6 +134,25 @@ int  edsbwt_search_into(edsbwt_index* idx, const uint8_t* pat_bytes, const uint6
  * its newlines): pattern i = pat_bytes[i*pat_len .. (i+1)*pat_len).  No offset array crosses PCIe. */
 int  edsbwt_search_into_fixed(edsbwt_index* idx, const uint8_t* pat_bytes, uint32_t pat_len, uint32_t npat,
                               int locate, int lf_variant, uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc);
+/* The same for patterns the caller already holds as 2-bit codes (a quarter of the bytes over PCIe: 8 B instead of 32 B
+ * per length-32 pattern).  Layout (the kernel's own, internal.cuh PackedPats): pattern i occupies W = ceil(pat_len / 32)
+ * consecutive uint64 words; word w holds characters [max(0, pat_len - 32(w+1)), pat_len - 32w) of the pattern, the LAST
+ * of them in bits 62..63 and each earlier one two bits lower (a short head is padded with zero bits below); code =
+ * rank of the letter in the index alphabet (edsbwt_index_info: alphabet[1 + code]).  For pat_len <= 32 that is one
+ * word per pattern with character j at bits 2(j + 32 - pat_len).  invalid (may be NULL): bit i & 31 of word i >> 5 set =
+ * pattern i holds a byte outside the alphabet and yields 0 occurrences.  edsbwt_pack_patterns produces both from bytes
+ * on the host (the std::getline loop of the reference's constructor, EDSBWTsearch.cpp:207-241, is where a caller would
+ * do it: once per pattern file, not once per search). */
+int  edsbwt_search_into_packed(edsbwt_index* idx, const uint64_t* pat_words, const uint32_t* invalid, uint32_t pat_len, uint32_t npat,
+                               int locate, int lf_variant, uint32_t* counts, edsbwt_occ* occ, uint64_t occ_cap, uint64_t* nocc);
+/* Host-side packer for the call above (AVX2 + BMI2 when the CPU has them, scalar otherwise; nthreads <= 1: the calling
+ * thread only).  words: npat * ceil(pat_len / 32) uint64; invalid: (npat + 31) / 32 uint32; *n_invalid (may be NULL)
+ * receives the number of patterns flagged.  Needs the index only for its alphabet; no device work. */
+int  edsbwt_pack_patterns(const edsbwt_index* idx, const uint8_t* pat_bytes, uint32_t pat_len, uint32_t npat, int nthreads,
+                          uint64_t* words, uint32_t* invalid, uint32_t* n_invalid);
+/* The same without a handle: alphabet[0] = end-marker, alphabet[1..sigma) = the letters (edsbwt_info.alphabet / sigma). */
+int  edsbwt_pack_patterns_alphabet(const uint8_t* alphabet, uint32_t sigma, const uint8_t* pat_bytes, uint32_t pat_len, uint32_t npat,
+                                   int nthreads, uint64_t* words, uint32_t* invalid, uint32_t* n_invalid);
 /* Count-only search that also reports where each not-found pattern died, for the RECOVERBW=0 stderr line
  * "Pattern not found, interrupted in position <posSymb>" (EDSBWTsearch.cpp:714-717): interrupted[i] = that posSymb
  * (the frontier became empty when character posSymb-1 of the pattern was prepended), 0 = no such line (pattern
@@ -143,9 +163,12 @@ int  edsbwt_host_alloc(void** p, uint64_t bytes);      /* page-locked host memor
 void edsbwt_host_free(void* p);
 int  edsbwt_set_chunk(edsbwt_index* idx, uint32_t patterns_per_chunk);   /* pipeline granularity, default 2^21; 0 = one chunk */
 
-/* Same search with the packed patterns already resident in HBM and the results left there (the `value`
- * leg of bench.py).  d_* are DEVICE pointers on the handle's device.  total_bytes = pat_off[npat]; max_len = length of
- * the longest pattern, or 0 when unknown (found on the device if needed). */
+/* Same search with the patterns (bytes + offsets) already resident in HBM and the results left there (the `value`
+ * leg of bench.py).  d_* are DEVICE pointers on the handle's device.  total_bytes >= pat_off[npat] - pat_off[0] (it sizes
+ * the 2-bit copy of the batch; a smaller value fails with EDSBWT_E_ARG); max_len = length of the longest pattern, or 0
+ * when unknown (found on the device if needed).  The kernels read pattern bytes in aligned 16-byte units: the 16-byte
+ * unit holding the last pattern byte must lie inside the allocation (true for any cudaMalloc'ed buffer, whose size is
+ * rounded up to 256 bytes; a sub-allocated buffer needs 15 bytes of slack at its end). */
 int  edsbwt_search_device(edsbwt_index* idx, const uint8_t* d_pat_bytes, const uint64_t* d_pat_off, uint32_t npat,
                           uint64_t total_bytes, uint32_t max_len, int locate, int lf_variant, edsbwt_result** res);
 /* The same for one shard of a larger batch (multi-GPU: patterns sharded, index replicated): tuples carry pat + pat_base. */

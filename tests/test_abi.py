@@ -45,6 +45,46 @@ def test_pattern_reader_and_csv(eb, tmp_path):
     assert open(out).read() == "#Pat\t$_i\tD[i]\tS_j\tS_j[r] \n11\t3\t2\t0\t0\n"
 
 
+def _pack_reference(pats, plen, letters=b"ACGT"):
+    """numpy-free restatement of the packed layout of include/edsbwt.h"""
+    stride = (plen + 31) // 32
+    words, bad = [], []
+    for i, p in enumerate(pats):
+        ok = all(ch in letters for ch in p)
+        for w in range(stride):
+            hi = plen - 32 * w
+            lo = max(0, hi - 32)
+            v = 0
+            for j in range(lo, hi):
+                c = letters.index(p[j]) if p[j] in letters else 0
+                v |= (c & 3) << (2 * (j - lo))
+            words.append((v << (2 * (32 - (hi - lo)))) & (2 ** 64 - 1) if ok else None)
+        if not ok:
+            bad.append(i)
+    return words, bad
+
+
+@pytest.mark.parametrize("plen", [1, 5, 31, 32, 33, 64, 100])
+@pytest.mark.parametrize("nthreads", [1, 4])
+def test_host_packer(eb, plen, nthreads):
+    """edsbwt_pack_patterns_alphabet (host-only): words and the invalid bitmap against the layout's definition"""
+    rng = np.random.default_rng(plen)
+    npat = 20000 if nthreads > 1 else 3000
+    data = rng.choice(np.frombuffer(b"ACGT", np.uint8), size=npat * plen)
+    for i in rng.integers(0, npat, 7):
+        data[i * plen + rng.integers(0, plen)] = ord("N")
+    pats = [bytes(data[i * plen:(i + 1) * plen]) for i in range(npat)]
+    words, invalid, nbad = eb.pack_patterns_alphabet(b"#ACGT", data, plen, nthreads)
+    exp, bad = _pack_reference(pats, plen)
+    assert nbad == len(bad)
+    assert [i for i in range(npat) if (invalid[i >> 5] >> (i & 31)) & 1] == bad
+    got = words.tolist()
+    assert all(e is None or e == g for e, g in zip(exp, got))
+    # a three-letter alphabet: T is not a letter
+    w3, inv3, nbad3 = eb.pack_patterns_alphabet(b"#ACG", data[:64 * plen], plen, 1)
+    assert nbad3 == sum(1 for p in pats[:64] if any(ch not in b"ACG" for ch in p))
+
+
 def test_no_cpu_fallback(eb, tmp_path):
     import torch
     if torch.cuda.is_available():

@@ -25,7 +25,8 @@ def _index_files(tmp_path, segs, name="idx"):
 
 
 @pytest.mark.parametrize("name", golden_names())
-@pytest.mark.parametrize("seed_k,locate_mode,engine,cap", [(-1, 0, 0, 0), (1, 0, 0, 0), (3, 1, 0, 4), (6, 0, 1, 0), (2, 0, 0, 5)])
+@pytest.mark.parametrize("seed_k,locate_mode,engine,cap", [(-1, 0, 0, 0), (1, 0, 0, 0), (3, 1, 0, 4), (6, 0, 1, 0), (2, 0, 0, 5),
+                                                           (-1, 0, 2, 0), (2, 1, 2, 5)])
 def test_golden(eb, tmp_path, name, seed_k, locate_mode, engine, cap):
     g = load_golden(name)
     _, base = _index_files(tmp_path, E.parse_eds(g["eds"]))
@@ -60,7 +61,8 @@ def test_random_vs_port(eb, oracle_built, tmp_path, seed, kw, seed_k):
     c_port = rows_port = None
     # the fused kernel (default), the fused kernel with a tiny frontier capacity (most patterns fall through to the
     # level-synchronous engine), and the level-synchronous engine alone: same counts, rows and byte-model counters
-    for engine, cap, cap2 in [(eb.ENGINE_FUSED, 0, 0), (eb.ENGINE_FUSED, 4, 0), (eb.ENGINE_FUSED, 4, 7), (eb.ENGINE_LEVELSYNC, 0, 0)]:
+    for engine, cap, cap2 in [(eb.ENGINE_FUSED, 0, 0), (eb.ENGINE_FUSED, 4, 0), (eb.ENGINE_FUSED, 4, 7), (eb.ENGINE_LEVELSYNC, 0, 0),
+                              (eb.ENGINE_FUSED_STEP, 0, 0), (eb.ENGINE_FUSED_STEP, 4, 7)]:
         with eb.Index(base, seed_k=seed_k, locate_mode=0, engine=engine, fused_cap=cap, fused_cap2=cap2) as idx:
             k = idx.info().seed_k
             idx.set_stats(True, canonical_k=k)
@@ -73,7 +75,7 @@ def test_random_vs_port(eb, oracle_built, tmp_path, seed, kw, seed_k):
             assert np.all(np.diff(occ["pat"].astype(np.int64)) >= 0)
             for key in "ISELO":
                 assert st[key] == st_port[key], (engine, cap, key, st[key], st_port[key])
-            if engine == eb.ENGINE_FUSED and cap == 4:
+            if engine != eb.ENGINE_LEVELSYNC and cap == 4:
                 assert st["overflow_patterns"] > 0
                 assert cap2 == 0 or st["levelsync_patterns"] > 0
             idx.set_stats(False)
@@ -259,9 +261,91 @@ def test_search_into_fixed_length_batches(eb, tmp_path, plen):
             assert eb.occ_rows(occ[:n]) == eb.occ_rows(o_ref)
 
 
+# ---- patterns handed in as 2-bit words (edsbwt_search_into_packed + the host packer edsbwt_pack_patterns) --------
+@pytest.mark.parametrize("plen", [1, 7, 16, 31, 32, 33, 64, 70])
+def test_search_into_packed(eb, tmp_path, plen):
+    """packed entry point == byte entry points, for every engine tier (the tiers that read characters get them unpacked on
+    the device), incl. patterns holding a byte outside the alphabet (flagged by the packer -> 0 occurrences)"""
+    rng = np.random.default_rng(500 + plen)
+    segs = E.random_eds(rng, n_seg=1200, max_var=4, max_len=6, p_empty=0.15, nondeg_len=(1, 60))
+    _, base = _index_files(tmp_path, segs)
+    pats = E.sample_patterns(rng, segs, 900, [plen])
+    for i in (3, 77, 500, 899):                                   # bytes outside {A,C,G,T}, incl. the end-marker itself
+        b = bytearray(pats[i]); b[rng.integers(0, plen)] = [ord("N"), ord("#"), 0, 255][i % 4]; pats[i] = bytes(b)
+    data, off = eb.pack_patterns(pats)
+    for engine, cap, lf in [(eb.ENGINE_FUSED, 0, eb.LF_RANK), (eb.ENGINE_FUSED, 4, eb.LF_RANK), (eb.ENGINE_LEVELSYNC, 0, eb.LF_RANK),
+                            (eb.ENGINE_FUSED_STEP, 0, eb.LF_RANK), (eb.ENGINE_FUSED, 0, eb.LF_MOVE)]:
+        with eb.Index(base, engine=engine, fused_cap=cap) as idx:
+            c_ref, o_ref = idx.search(pats, locate=True, lf_variant=lf)
+            assert all(c_ref[i] == 0 for i in (3, 77, 500, 899))
+            words, invalid, nbad = idx.pack_patterns(data, plen, nthreads=3)
+            assert nbad == 4 and [i for i in range(len(pats)) if (invalid[i >> 5] >> (i & 31)) & 1] == [3, 77, 500, 899]
+            p_words = eb.pinned_empty(words.size, np.uint64); p_words[:] = words
+            for chunk in [0, 256, 97, 1]:
+                idx.set_chunk(chunk)
+                counts = eb.pinned_empty(len(pats), np.uint32); counts[:] = 0xffffffff
+                occ = eb.pinned_empty(len(o_ref) + 3, eb.OCC_DTYPE)
+                n = idx.search_into_packed(p_words, invalid, plen, len(pats), counts, occ, locate=True, lf_variant=lf)
+                assert n == len(o_ref) and counts.tolist() == c_ref.tolist(), (engine, cap, lf, chunk)
+                assert eb.occ_rows(occ[:n]) == eb.occ_rows(o_ref)
+                if chunk == 97 and cap == 4:
+                    assert idx.last_stats()["overflow_patterns"] > 0
+            # without the bitmap the flagged patterns are searched as whatever their codes say: only the others must agree
+            idx.set_chunk(0)
+            counts = np.zeros(len(pats), np.uint32)
+            idx.search_into_packed(words, None, plen, len(pats), counts, None, locate=False, lf_variant=lf)
+            keep = np.ones(len(pats), bool); keep[[3, 77, 500, 899]] = False
+            assert counts[keep].tolist() == c_ref[keep].tolist()
+
+
+def test_occurrence_overflow_halves_the_chunk(eb, tmp_path, monkeypatch):
+    """More occurrences in one chunk than the 32-bit result offsets can address (here: than EDSBWT_OCC_LIMIT): the
+    host-buffer calls and the csv call halve the chunk and go on; the device-pointer call reports EDSBWT_E_UNSUPPORTED."""
+    rng = np.random.default_rng(77)
+    segs = E.random_eds(rng, n_seg=800, max_var=4, max_len=6, p_empty=0.15, nondeg_len=(1, 60))
+    _, base = _index_files(tmp_path, segs)
+    pats = E.sample_patterns(rng, segs, 400, [2, 3, 4, 8, 16])
+    data, off = eb.pack_patterns(pats)
+    with eb.Index(base) as idx:
+        c_ref, o_ref = idx.search(pats, locate=True)
+        csv_ref = str(tmp_path / "ref.csv")
+        idx.search_to_csv(pats, csv_ref)
+    biggest = int(c_ref.max())
+    assert len(o_ref) > 20 * biggest
+    monkeypatch.setenv("EDSBWT_OCC_LIMIT", str(3 * biggest))
+    with eb.Index(base) as idx:
+        c, o = idx.search(pats, locate=True)
+        assert c.tolist() == c_ref.tolist() and eb.occ_rows(o) == eb.occ_rows(o_ref)
+        assert np.all(np.diff(o["pat"].astype(np.int64)) >= 0)
+        fixed = [p for p in pats if len(p) == 3]
+        fd, _ = eb.pack_patterns(fixed)
+        cf = np.zeros(len(fixed), np.uint32); of = np.zeros(len(o_ref), eb.OCC_DTYPE)
+        nf = idx.search_into_fixed(fd, 3, cf, of, locate=True)
+        want = [c_ref[i] for i, p in enumerate(pats) if len(p) == 3]
+        assert cf.tolist() == want and nf == sum(want)
+        words, invalid, _ = idx.pack_patterns(fd, 3)
+        cp = np.zeros(len(fixed), np.uint32); op = np.zeros(len(o_ref), eb.OCC_DTYPE)
+        assert idx.search_into_packed(words, invalid, 3, len(fixed), cp, op, locate=True) == nf and cp.tolist() == want
+        assert eb.occ_rows(op[:nf]) == eb.occ_rows(of[:nf])
+        csv = str(tmp_path / "halved.csv")
+        idx.search_to_csv(pats, csv)
+        assert open(csv, "rb").read() == open(csv_ref, "rb").read()
+        import torch
+        d_data = torch.from_numpy(data).cuda(); d_off = torch.from_numpy(off.view(np.int64)).cuda()
+        with pytest.raises(eb.EdsbwtError) as ei:
+            idx.search_device(d_data.data_ptr(), d_off.data_ptr(), len(pats), int(data.size), 16, locate=True)
+        assert ei.value.code == -6
+        r = idx.search_device(d_data.data_ptr(), d_off.data_ptr(), len(pats), int(data.size), 16, locate=False)     # counting needs no offsets
+        assert r.fetch()[0].tolist() == c_ref.tolist()
+        r.free()
+        with pytest.raises(eb.EdsbwtError) as ei:                    # total_bytes must cover the offsets' span
+            idx.search_device(d_data.data_ptr(), d_off.data_ptr(), len(pats), 64, 16, locate=False)
+        assert ei.value.code == -5
+
+
 # ---- count-only trace (RECOVERBW=0 stderr line) and the two drop-in executables ---------------------------------
 @pytest.mark.parametrize("name", golden_names())
-@pytest.mark.parametrize("seed_k,engine,cap", [(-1, 0, 0), (1, 0, 0), (4, 0, 4), (3, 1, 0)])
+@pytest.mark.parametrize("seed_k,engine,cap", [(-1, 0, 0), (1, 0, 0), (4, 0, 4), (3, 1, 0), (-1, 2, 0), (4, 2, 4)])
 def test_trace_interrupted_positions(eb, tmp_path, name, seed_k, engine, cap):
     g = load_golden(name)
     _, base = _index_files(tmp_path, E.parse_eds(g["eds"]))
@@ -279,8 +363,8 @@ def test_trace_vs_port_random(eb, oracle_built, tmp_path):
     pf = str(tmp_path / "p.txt")
     E.write_patterns(pf, pats)
     c_port, _, st = oracle_built.run_port(base, pf, locate=False)
-    for seed_k, cap in [(-1, 0), (5, 4), (2, 0)]:
-        with eb.Index(base, seed_k=seed_k, fused_cap=cap) as idx:
+    for seed_k, cap, engine in [(-1, 0, 0), (5, 4, 0), (2, 0, 0), (5, 4, 2)]:
+        with eb.Index(base, seed_k=seed_k, fused_cap=cap, engine=engine) as idx:
             counts, pos = idx.search_trace(pats)
         assert counts.tolist() == c_port
         assert pos.tolist() == st["interrupted"]
