@@ -194,8 +194,8 @@ def cpu_reference_run(base, pats, seconds, cores, note, per=None):
             for pf in files:
                 cmd = [exe, base, pf] if kind == "reference" else [exe, base, pf, "--locate", "1", "--csv", pf + "output.csv"]
                 procs.append(subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True))
-            took, found = [], []
-            for p in procs:
+            took, found, rows = [], [], []
+            for c, p in enumerate(procs):
                 out = p.communicate()[0]
                 if kind == "reference":
                     import re
@@ -204,17 +204,26 @@ def cpu_reference_run(base, pats, seconds, cores, note, per=None):
                     found += [int(x) for x in re.findall(r"Found (\d+) starting", out)]
                 else:
                     took.append(json.loads(out.strip().splitlines()[-1])["seconds"])
-            return time.time() - t0, max(took), found
+                # the reference's own csv rows (<patterns>output.csv, EDSBWTsearch.cpp:1310-1332), pattern numbers made sample-global
+                csv = files[c] + "output.csv"
+                if os.path.exists(csv):
+                    with open(csv) as f:
+                        f.readline()
+                        for line in f:
+                            t = line.split()
+                            if len(t) == 5:
+                                rows.append((int(t[0]) - 1 + c * per, int(t[1]), int(t[2]), int(t[3]), int(t[4])))
+            return time.time() - t0, max(took), found, rows
         # calibrate with one pattern per core, then size the sample for ~`seconds` of search time
         if per is None:
-            wall1, took1, _ = run_shards(1)
+            wall1, took1, _, _ = run_shards(1)
             per = int(max(1, min(len(pats) // cores, seconds / max(took1, 1e-3))))
-        wall, took, found = run_shards(per)
+        wall, took, found, rows = run_shards(per)
         val = per * cores / max(took, 1e-9)
         return {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
                 "sample": "%d patterns (%d per process x %d processes) of the same batch, %s; max 'bs took' %.2fs (index load excluded, wall %.1fs)" % (
                     per * cores, per, cores, note, took, wall),
-                "search_seconds": took, "counts": found, "n": per * cores, "per": per}
+                "search_seconds": took, "counts": found, "rows": rows, "n": per * cores, "per": per}
     finally:
         shutil.rmtree(d, ignore_errors=True)
 
@@ -391,6 +400,7 @@ def main():
     assert np.array_equal(counts_generic, np.asarray(p_counts)), "fixed-length and offset-array entry points disagree"
     gpu_counts = np.array(p_counts, copy=True)
     gpu_occ_total = int(got)
+    gpu_occ_head = np.array(p_occ[:min(int(got), 1 << 18)], copy=True)      # tuples of the first patterns: row parity against the reference sample
     # ---- multi-GPU result gather (north star: "only an NCCL/NVLink gather of per-pattern counts and occurrence buffers"):
     #      shard search + all-gather of the counts + gather-v of the tuples to rank 0, timed on the device
     gather_ms, gather_bytes = 0.0, 0
@@ -491,9 +501,15 @@ def main():
             if _ORIG_AFFINITY:
                 os.sched_setaffinity(0, _ORIG_AFFINITY)          # the CPU baseline gets every host core again
             cb = cpu_reference_run(base, pats, args.cpu_seconds, os.cpu_count() or 1, "locate (RECOVERBW=1)")
-            ref_counts, nref = cb.pop("counts"), cb.pop("n"); cb.pop("per", None)
-            if len(ref_counts) == nref:         # full-size parity check on the sample: the reference's own counts
-                cb["parity_vs_gpu"] = "ok" if ref_counts == gpu_counts[:nref].tolist() else "MISMATCH"
+            ref_counts, ref_rows, nref = cb.pop("counts"), cb.pop("rows"), cb.pop("n"); cb.pop("per", None)
+            if len(ref_counts) == nref:         # full-size parity check on the sample: the reference's own counts AND csv rows
+                ngpu = int(gpu_counts[:nref].astype(np.int64).sum())
+                gpu_rows = sorted(zip(gpu_occ_head["pat"][:ngpu].tolist(), gpu_occ_head["str"][:ngpu].tolist(), gpu_occ_head["seg"][:ngpu].tolist(),
+                                      gpu_occ_head["idx_in_seg"][:ngpu].tolist(), gpu_occ_head["off"][:ngpu].tolist()))
+                ok_c = ref_counts == gpu_counts[:nref].tolist()
+                ok_r = ngpu <= len(gpu_occ_head) and sorted(ref_rows) == gpu_rows
+                cb["parity_vs_gpu"] = ("counts+rows ok (%d patterns, %d rows)" % (nref, len(ref_rows))) if (ok_c and ok_r) else (
+                    "MISMATCH (counts %s, rows %s)" % ("ok" if ok_c else "differ", "ok" if ok_r else "differ"))
             out["cpu_baseline"] = cb
         except Exception as e:
             out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": "failed: %r" % (e,)}
@@ -528,7 +544,7 @@ def reference_arm(args, eb, synth, workdir, base, done_flag):
     per = None
     for it in range(args.warmup + args.steps):
         r = cpu_reference_run(base, pats[it * 4096:], budget, cores, "locate (RECOVERBW=1), step %d" % it, per=per)
-        per = r["per"]
+        per = r["per"]; r.pop("rows", None)
         if it >= args.warmup:
             vals.append(r["value"]); secs.append(r["search_seconds"]); base_info = r
     v = float(np.mean(vals))

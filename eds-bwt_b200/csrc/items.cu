@@ -90,24 +90,21 @@ void launch_unpack_patterns(const uint64_t* words, uint32_t fixed_len, uint32_t 
 namespace {
 
 enum : uint32_t {
-    K_IDLE = 0,      // no pattern: takes one from the warp's pool
+    K_IDLE = 0,      // no pattern: takes one from the warp's pool at the top of the next sweep
+    K_FIN,           // pattern finished: its results are written, then the lane takes the next pattern (same place)
     K_OCCF,          // fetch: Occ block of F[j]           (pass 1: F' = LF_c(F), '#' rows -> link)
     K_OCCD,          // fetch: Occ block of Dol[j]         (pass 2: Dol' = LF_c(Dol))
-    K_SEED,          // fetch: first[key] of the deepest seed level (16 B)
-    K_LD64,          // kinds >= K_LD64 fetch 8 bytes at ptr:
-    K_LINK = K_LD64, //   link record of the next '#' row inside F[j]
-    K_SEEDIV,        //   a further interval of the seed entry
-    K_WORD,          //   the next 32 pattern characters
-    // transitions, resolved inside the sweep that raises them (no fetch)
-    K_ENDP1, K_ENDP2, K_STEP, K_FIN
+    K_LINK,          // fetch (8 B): link record of the next '#' row inside F[j]
+    K_SEEDIV,        // fetch (8 B): a further interval of the seed entry
+    K_WORD,          // fetch (8 B): the next 32 pattern characters
+    K_ENDP2          // transition, resolved inside the sweep that raises it: F <- Dol' ++ F'
 };
 
-__device__ __forceinline__ void ld128(const void* p, uint32_t* r) {
-    asm volatile("ld.global.nc.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "l"(p));
-}
 __device__ __forceinline__ void ld64(const void* p, uint32_t* r) {
     asm volatile("ld.global.nc.v2.b32 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "l"(p));
 }
+
+constexpr int ITEM_WARPS = FUSED_THREADS / 32;
 
 }  // namespace
 
@@ -120,119 +117,191 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     __shared__ const uint2* s_iv[17];
     __shared__ const uint32_t* s_cnt[17];
     __shared__ uint32_t s_Cl[5];
+    // the warp's pool: 32 consecutive patterns, fetched coalesced and with their seed entries already looked up by all 32
+    // lanes at once; a lane that needs a pattern reads entry pool_pos + (its rank among the needy lanes)
+    __shared__ uint64_t s_pw[ITEM_WARPS][32];         // word 0 of the pattern
+    __shared__ uint4 s_ps[ITEM_WARPS][32];            // seed entry {first interval lo, hi, offset of the entry, number of intervals}
+    __shared__ uint2 s_pm[ITEM_WARPS][32];            // {length (0: nothing to search), first word}
     if (threadIdx.x < 17) { s_off[threadIdx.x] = sv.off[threadIdx.x]; s_iv[threadIdx.x] = sv.iv[threadIdx.x]; s_cnt[threadIdx.x] = sv.cnt[threadIdx.x]; }
     if (threadIdx.x < 5) s_Cl[threadIdx.x] = ix.Cl[threadIdx.x];
     __syncthreads();
-#define LIST(j) s_list[(j) * FUSED_THREADS + threadIdx.x]
-#define DOL(i) s_list[(cap - 1 - (i)) * FUSED_THREADS + threadIdx.x]
+#define SLOT(i) s_list[(i) * FUSED_THREADS + threadIdx.x]
+#define LIST(j) SLOT(j)
+#define DOL(i) SLOT(cap - 1 - (i))
     constexpr uint32_t FULL = 0xffffffffu;
-    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
 
-    // ---- the warp's pool: 32 consecutive patterns, entry i in the registers of lane i
-    uint32_t pool_q = 0, pool_m = 0, pool_wb = 0, pool_pos = 0, pool_n = 0;
-    uint64_t pool_w = 0;
+    uint32_t pool_base = 0, pool_pos = 0, pool_n = 0;
     bool exhausted = false;
     auto grab_pool = [&]() {
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(work, 32u);
         base = __shfl_sync(FULL, base, 0);
-        pool_pos = 0;
+        pool_pos = 0; pool_base = base;
         if (base >= npat) { exhausted = true; pool_n = 0; return; }
         pool_n = npat - base < 32u ? npat - base : 32u;
-        pool_q = base + lane; pool_m = 0; pool_w = 0;
         if (lane < pool_n) {
-            uint32_t mm;
+            const uint32_t pq = base + lane;
+            uint32_t mm, pwb;
             if (pp.poff) {
-                const uint64_t a = __ldg(pp.poff + pool_q), len64 = __ldg(pp.poff + pool_q + 1) - a;
+                const uint64_t a = __ldg(pp.poff + pq), len64 = __ldg(pp.poff + pq + 1) - a;
                 mm = len64 > 0xffffffffull ? 0u : (uint32_t)len64;
-                pool_wb = (uint32_t)(((a - __ldg(pp.poff)) >> 5) + pool_q);
-            } else { mm = pp.fixed_len; pool_wb = pool_q * pp.stride; }
-            if (pp.invalid && ((__ldg(pp.invalid + (pool_q >> 5)) >> (pool_q & 31u)) & 1u)) mm = 0;
-            pool_m = mm;
-            if (mm) pool_w = __ldg(pp.words + pool_wb);
+                pwb = (uint32_t)(((a - __ldg(pp.poff)) >> 5) + pq);
+            } else { mm = pp.fixed_len; pwb = pq * pp.stride; }
+            if (pp.invalid && ((__ldg(pp.invalid + (pq >> 5)) >> (pq & 31u)) & 1u)) mm = 0;
+            uint64_t w = 0; uint4 se = make_uint4(1u, 0u, 0u, 0u);
+            if (mm) {
+                w = __ldg(pp.words + pwb);
+                // seed entry of the last min(m, k) characters: the frontier after that many backward steps
+                const uint32_t L0 = mm < k ? mm : k, key = (uint32_t)(w >> (64 - 2 * L0));
+                if (sv.first && L0 == sv.first_level) se = __ldg(sv.first + key);
+                else {
+                    se.z = __ldg(s_off[L0] + key); se.w = __ldg(s_off[L0] + key + 1) - se.z;
+                    if (se.w) { const uint2 v = __ldg(s_iv[L0] + se.z); se.x = v.x; se.y = v.y; }
+                }
+            }
+            s_pw[wid][lane] = w; s_ps[wid][lane] = se; s_pm[wid][lane] = make_uint2(mm, pwb);
         }
+        __syncwarp();
     };
 
     // ---- lane state
     uint32_t kind = K_IDLE, q = 0, m = 0, spos = 0, wb = 0;     // spos = length of the pattern suffix matched so far
     uint64_t win = 0;                                             // word spos >> 5 of the pattern
     uint32_t nF = 0, j = 0, nout = 0, ndol = 0;
-    uint32_t aux = 0;                                             // pass 1: link records left of F[j] (rem); pass 2: length of Dol' (ndp)
-#define rem aux
-#define ndp aux
-    const uint2* ptr = nullptr;                                   // K_SEED: &first[key]; K_LD64 kinds: the 8 bytes wanted
+    uint32_t aux = 0;                                             // pass 1: link records left of F[j]; pass 2: length of Dol'
+    uint32_t cur = 0;                                             // K_LINK: link record; K_SEEDIV: seed interval
     bool ovf = false;
     unsigned long long sI = 0, sS = 0, sE = 0, sLF = 0, sBlk = 0;     // counting runs: totals of the lane ...
     uint32_t tI = 0, tS = 0, tE = 0, tLF = 0, tBlk = 0;               // ... and of its current pattern (dropped when it overflows)
 
+    // the frontier of the suffix of length spos is complete: what the lane fetches next
+    auto next_step = [&]() {
+        if (STATS && spos == (m < kc ? m : kc)) tI += nF;
+        if (spos == m || nF == 0) kind = K_FIN;
+        else if ((spos & 31u) == 0) kind = K_WORD;
+        else { kind = K_OCCF; j = 0; nout = 0; ndol = 0; }
+    };
+
     grab_pool();
     for (;;) {
-        // ---------------- refill: idle lanes take the next patterns of the pool
-        const uint32_t idle = __ballot_sync(FULL, kind == K_IDLE);
-        if (idle) {
+        // ---------------- finished lanes write their results; they and the idle lanes take the next patterns of the pool
+        const uint32_t needy = __ballot_sync(FULL, kind <= K_FIN);
+        if (needy) {
+            if (kind == K_FIN) {
+                // count + the final interval list.  One interval (nearly every found pattern) travels inside the plist entry
+                // itself -- its end follows from the count -- longer lists are staged contiguously
+                uint32_t cnt = 0; uint2 pl = make_uint2(0u, 0u);
+                if (ovf) nF = 0;
+                if (nF == 1) { const uint2 v = LIST(0); cnt = v.y - v.x + 1; pl = make_uint2(v.x, PLIST_INLINE); }
+                else if (nF > 1) {
+                    for (uint32_t t = 0; t < nF; ++t) { const uint2 v = LIST(t); cnt += v.y - v.x + 1; }
+                    const uint32_t my = atomicAdd(out.cursor, nF);
+                    if ((uint64_t)my + nF > out.staging_cap) { ovf = true; cnt = 0; }
+                    else { for (uint32_t t = 0; t < nF; ++t) out.staging[my + t] = LIST(t); pl = make_uint2(my, nF); }
+                }
+                out.plist[q] = pl; out.counts[q] = cnt;
+                if (ovf) out.ovf_ids[atomicAdd(out.ovf_count, 1u)] = q;
+                else {
+                    if (out.alive) {
+                        // where the frontier died ("Pattern not found, interrupted in position", EDSBWTsearch.cpp:714-717)
+                        const uint32_t L0 = m < k ? m : k;
+                        uint32_t la = 0;
+                        if (nF) la = m;
+                        else if (spos > L0) la = spos - 1;
+                        else {                                    // empty seed entry: longest shorter suffix that is not (win is still word 0)
+                            const uint32_t key = (uint32_t)(win >> (64 - 2 * L0));
+                            for (uint32_t L = L0 - 1; L >= 1; --L) {
+                                const uint32_t kl = key >> (2 * (L0 - L));
+                                if (__ldg(s_off[L] + kl + 1) > __ldg(s_off[L] + kl)) { la = L; break; }
+                            }
+                        }
+                        out.alive[q] = la;
+                    }
+                    if (STATS) { sI += tI; sS += tS; sE += tE; sLF += tLF; sBlk += tBlk; }
+                }
+                kind = K_IDLE;
+            }
             const uint32_t avail = pool_n - pool_pos;
             if (avail) {
-                const uint32_t r = __popc(idle & ((1u << lane) - 1u));
-                const uint32_t src = (pool_pos + r) & 31u;
-                const uint32_t tq = __shfl_sync(FULL, pool_q, src), tm = __shfl_sync(FULL, pool_m, src), twb = __shfl_sync(FULL, pool_wb, src);
-                const uint64_t tw = __shfl_sync(FULL, pool_w, src);
-                if (kind == K_IDLE && r < avail) {
-                    q = tq; m = tm; win = tw; wb = twb; ovf = false;
+                const uint32_t r = __popc(needy & ((1u << lane) - 1u));
+                if (r < avail) {                                  // every needy lane is idle by now
+                    const uint32_t e = pool_pos + r;
+                    const uint2 pm = s_pm[wid][e];
+                    q = pool_base + e; m = pm.x; wb = pm.y; ovf = false;
                     if (STATS) tI = tS = tE = tLF = tBlk = 0;
                     if (m == 0) {                                 // empty pattern or a byte outside the alphabet: 0 occurrences
                         out.counts[q] = 0; out.plist[q] = make_uint2(0u, 0u);
                         if (out.alive) out.alive[q] = 0;
                     } else {
-                        spos = m < k ? m : k;
-                        const uint32_t key = (uint32_t)(win >> (64 - 2 * spos));
-                        ptr = (const uint2*)(sv.first + key);
-                        kind = K_SEED;
+                        win = s_pw[wid][e];
+                        const uint4 se = s_ps[wid][e];
+                        const uint32_t L0 = m < k ? m : k, n0 = se.w;
+                        spos = L0;
+                        if (n0 && m == L0 && n0 <= PLIST_N_MASK) {
+                            // pattern no longer than the seed depth: the table IS the answer (count from the per-key table, the
+                            // result list is a reference into the seed intervals; a short key's frontier can hold thousands)
+                            const uint32_t key = (uint32_t)(win >> (64 - 2 * L0));
+                            uint32_t dc = 0;
+                            if (s_cnt[L0]) dc = __ldg(s_cnt[L0] + key);
+                            else for (uint32_t t = 0; t < n0; ++t) { const uint2 v = __ldg(s_iv[L0] + se.z + t); dc += v.y - v.x + 1; }
+                            out.counts[q] = dc; out.plist[q] = make_uint2(se.z, PLIST_SEED | (L0 << 27) | n0);
+                            if (out.alive) out.alive[q] = m;
+                            if (STATS) { if (m <= kc) sI += n0; }
+                        } else if (n0 > cap) { ovf = true; kind = K_FIN; }
+                        else {
+                            nF = n0;
+                            if (n0) LIST(0) = make_uint2(se.x, se.y);
+                            if (n0 > 1) { kind = K_SEEDIV; j = 1; cur = se.z + 1; }
+                            else next_step();
+                        }
                     }
                 }
-                const uint32_t taken = __popc(idle);
+                const uint32_t taken = __popc(needy);
                 pool_pos += taken < avail ? taken : avail;
-                if (pool_pos >= pool_n && !exhausted) grab_pool();      // its loads are first used by the shuffles of the next sweep
+                if (pool_pos >= pool_n && !exhausted) { __syncwarp(); grab_pool(); }      // its loads land while the warp sweeps on
             } else if (exhausted) {
-                if (idle == FULL) break;
+                if (__all_sync(FULL, kind == K_IDLE)) break;
             } else grab_pool();
         }
 
         // ---------------- issue: one fetch per lane, all in flight together
         uint32_t B[16];
-        if (kind == K_OCCF || kind == K_OCCD) {
-            const uint32_t row = kind == K_OCCF ? LIST(j).x : DOL(j).x;
-            const uint4* p = ix.occ + (size_t)(row >> 7) * 4;
+        const bool occ_item = kind == K_OCCF || kind == K_OCCD;
+        const uint32_t slot = kind == K_OCCD ? cap - 1 - j : j;  // pass 2 walks the Dol set at the top of the column
+        if (occ_item) {
+            const uint4* p = ix.occ + (size_t)(SLOT(slot).x >> 7) * 4;
             ld256(p, B); ld256(p + 2, B + 8);
-        } else if (kind == K_SEED) {
-            if (sv.first && spos == sv.first_level) ld128(ptr, B);
-        } else if (kind >= K_LD64) {
-            ld64(ptr, B);
-        }
+        } else if (kind == K_LINK) ld64(ix.link_rec + cur, B);
+        else if (kind == K_SEEDIV) ld64(s_iv[m < k ? m : k] + cur, B);
+        else if (kind == K_WORD) ld64(pp.words + wb + (spos >> 5), B);
 
         // ---------------- consume
-        if (kind == K_OCCF || kind == K_OCCD) {
+        if (occ_item) {
             const int c = (int)((win >> (2 * (31 - (spos & 31u)))) & 3u);
             const uint32_t x0 = (c & 1) ? 0u : 0xffffffffu, x1 = (c & 2) ? 0u : 0xffffffffu;
             uint32_t rca, rcb, rda, rdb, nblk;
-            const uint2 iv = kind == K_OCCF ? LIST(j) : DOL(j);
+            const uint2 iv = SLOT(slot);
             lf_range_loaded(*reinterpret_cast<Blk*>(B), ix.occ, iv.x, iv.y + 1, c, x0, x1, rca, rcb, rda, rdb, nblk);
             if (STATS) { tLF += 1; tBlk += nblk; if (spos >= kc) { tS += 1; tE += rdb - rda; } }
-            const uint32_t Cc = s_Cl[c];
-            if (kind == K_OCCF) {
-                if (rcb > rca) {
-                    const uint32_t nlo = Cc + rca, nhi = Cc + rcb - 1;
-                    if (nout && LIST(nout - 1).y + 1 == nlo) LIST(nout - 1).y = nhi;
-                    else { LIST(nout) = make_uint2(nlo, nhi); ++nout; }
+            // one code path for both passes: the output list grows from the bottom (F', length nout) or from the top (Dol', length aux)
+            const bool pass2 = kind == K_OCCD;
+            uint32_t no = pass2 ? aux : nout;
+            if (rcb > rca) {
+                const uint32_t Cc = s_Cl[c], nlo = Cc + rca, nhi = Cc + rcb - 1;
+                const uint32_t prev = pass2 ? cap - no : no - 1;      // slot of the last output (valid when no > 0)
+                if (no && SLOT(prev).y + 1 == nlo) SLOT(prev).y = nhi;
+                else { SLOT(pass2 ? cap - 1 - no : no) = make_uint2(nlo, nhi); ++no; }
+            }
+            ++j;
+            if (pass2) { aux = no; if (j == ndol) kind = K_ENDP2; }
+            else {
+                nout = no;
+                if (rdb > rda) { kind = K_LINK; cur = rda; aux = rdb - rda; }
+                else if (j == nF) {
+                    if (ndol) { kind = K_OCCD; j = 0; aux = 0; }
+                    else { nF = nout; ++spos; next_step(); }
                 }
-                if (rdb > rda) { kind = K_LINK; ptr = ix.link_rec + rda; rem = rdb - rda; }
-                else if (++j == nF) kind = K_ENDP1;
-            } else {
-                if (rcb > rca) {
-                    const uint32_t nlo = Cc + rca, nhi = Cc + rcb - 1;
-                    if (ndp && DOL(ndp - 1).y + 1 == nlo) DOL(ndp - 1).y = nhi;
-                    else { DOL(ndp) = make_uint2(nlo, nhi); ++ndp; }
-                }
-                if (++j == ndol) kind = K_ENDP2;
             }
         } else if (kind == K_LINK) {
             // pile-0 range [l, h] of the preceding segment(s) -> sorted, merged Dol set at the top of the column
@@ -255,97 +324,31 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
                 }
             }
             if (!ovf) {
-                ++ptr;
-                if (--rem == 0) kind = (++j == nF) ? K_ENDP1 : K_OCCF;
-            }
-        } else if (kind == K_SEED) {
-            // seed entry of the last spos characters: frontier after the first min(m, k) backward steps
-            const uint32_t L0 = spos, key = (uint32_t)(win >> (64 - 2 * L0));
-            uint32_t a, n0; uint2 iv0 = make_uint2(1u, 0u);
-            if (sv.first && L0 == sv.first_level) { iv0 = make_uint2(B[0], B[1]); a = B[2]; n0 = B[3]; }
-            else { a = __ldg(s_off[L0] + key); n0 = __ldg(s_off[L0] + key + 1) - a; if (n0) iv0 = __ldg(s_iv[L0] + a); }
-            if (n0 && m == L0 && n0 <= PLIST_N_MASK) {
-                // pattern no longer than the seed depth: the table IS the answer (count from the per-key table, the result list
-                // is a reference into the seed intervals; a short key's frontier can hold thousands of them)
-                uint32_t dc = 0;
-                if (s_cnt[L0]) dc = __ldg(s_cnt[L0] + key);
-                else for (uint32_t t = 0; t < n0; ++t) { const uint2 v = __ldg(s_iv[L0] + a + t); dc += v.y - v.x + 1; }
-                out.counts[q] = dc; out.plist[q] = make_uint2(a, PLIST_SEED | (L0 << 27) | n0);
-                if (out.alive) out.alive[q] = m;
-                if (STATS) { if (m <= kc) sI += n0; }
-                kind = K_IDLE;
-            } else if (n0 > cap) { ovf = true; kind = K_FIN; }
-            else {
-                nF = n0;
-                if (n0) LIST(0) = iv0;
-                if (n0 > 1) { kind = K_SEEDIV; j = 1; ptr = s_iv[L0] + a + 1; }
-                else kind = K_STEP;
+                ++cur;
+                if (--aux == 0) {                                 // (j already counts F[j] as done)
+                    if (j < nF) kind = K_OCCF;
+                    else if (ndol) { kind = K_OCCD; j = 0; aux = 0; }
+                    else { nF = nout; ++spos; next_step(); }
+                }
             }
         } else if (kind == K_SEEDIV) {
             LIST(j) = make_uint2(B[0], B[1]);
-            ++ptr;
-            if (++j == nF) kind = K_STEP;
+            ++cur;
+            if (++j == nF) next_step();
         } else if (kind == K_WORD) {
             win = ((uint64_t)B[1] << 32) | B[0];
             kind = K_OCCF; j = 0; nout = 0; ndol = 0;
         }
-
-        // ---------------- transitions
-        if (kind == K_ENDP1) {
-            if (ndol) { kind = K_OCCD; j = 0; ndp = 0; }
-            else { nF = nout; ++spos; kind = K_STEP; }
-        }
-        if (kind == K_ENDP2) {                                    // F <- Dol' ++ F'
-            if (ndp) {
-                if (nout + 2 * ndp > cap) { ovf = true; kind = K_FIN; }
+        if (kind == K_ENDP2) {                                    // F <- Dol' ++ F'   (aux = length of Dol')
+            if (aux) {
+                if (nout + 2 * aux > cap) { ovf = true; kind = K_FIN; }
                 else {
-                    for (uint32_t t = nout; t > 0; --t) LIST(t - 1 + ndp) = LIST(t - 1);
-                    for (uint32_t i = 0; i < ndp; ++i) LIST(i) = DOL(i);
-                    nout += ndp;
+                    for (uint32_t t = nout; t > 0; --t) LIST(t - 1 + aux) = LIST(t - 1);
+                    for (uint32_t i = 0; i < aux; ++i) LIST(i) = DOL(i);
+                    nout += aux;
                 }
             }
-            if (!ovf) { nF = nout; ++spos; kind = K_STEP; }
-        }
-        if (kind == K_STEP) {                                     // the frontier of the suffix of length spos is complete
-            if (STATS && spos == (m < kc ? m : kc)) tI += nF;
-            if (spos == m || nF == 0) kind = K_FIN;
-            else if ((spos & 31u) == 0) { kind = K_WORD; ptr = (const uint2*)(pp.words + wb + (spos >> 5)); }
-            else { kind = K_OCCF; j = 0; nout = 0; ndol = 0; }
-        }
-        if (kind == K_FIN) {
-            // ---- results: count + the final interval list.  One interval (nearly every found pattern) travels inside the
-            //      plist entry itself -- its end follows from the count -- longer lists are staged contiguously
-            if (ovf) nF = 0;
-            uint32_t cnt = 0;
-            for (uint32_t t = 0; t < nF; ++t) { const uint2 v = LIST(t); cnt += v.y - v.x + 1; }
-            uint2 pl = make_uint2(0u, 0u);
-            if (nF == 1) pl = make_uint2(LIST(0).x, PLIST_INLINE);
-            else if (nF > 1) {
-                const uint32_t my = atomicAdd(out.cursor, nF);
-                if ((uint64_t)my + nF > out.staging_cap) { ovf = true; cnt = 0; }
-                else { for (uint32_t t = 0; t < nF; ++t) out.staging[my + t] = LIST(t); pl = make_uint2(my, nF); }
-            }
-            out.plist[q] = pl; out.counts[q] = cnt;
-            if (ovf) out.ovf_ids[atomicAdd(out.ovf_count, 1u)] = q;
-            else {
-                if (out.alive) {
-                    // where the frontier died ("Pattern not found, interrupted in position", EDSBWTsearch.cpp:714-717)
-                    const uint32_t L0 = m < k ? m : k;
-                    uint32_t la = 0;
-                    if (nF) la = m;
-                    else if (spos > L0) la = spos - 1;
-                    else {                                        // empty seed entry: longest shorter suffix that is not
-                        const uint32_t key = (uint32_t)(win >> (64 - 2 * L0));
-                        for (uint32_t L = L0 - 1; L >= 1; --L) {
-                            const uint32_t kl = key >> (2 * (L0 - L));
-                            if (__ldg(s_off[L] + kl + 1) > __ldg(s_off[L] + kl)) { la = L; break; }
-                        }
-                    }
-                    out.alive[q] = la;
-                }
-                if (STATS) { sI += tI; sS += tS; sE += tE; sLF += tLF; sBlk += tBlk; }
-            }
-            kind = K_IDLE;
+            if (!ovf) { nF = nout; ++spos; next_step(); }
         }
     }
     if (STATS) {
@@ -358,10 +361,9 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
             if (lane == 0 && x) atomicAdd(dst[i], x);
         }
     }
+#undef SLOT
 #undef LIST
 #undef DOL
-#undef rem
-#undef ndp
 }
 
 namespace {
@@ -393,7 +395,6 @@ void launch_items_search(const IndexView& ix, const SeedView& sv, uint32_t k, co
     if (st) launch_items_instance<true, 8>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
     else if (cap > 16 || minb == 8) launch_items_instance<false, 8>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
     else if (minb == 9) launch_items_instance<false, 9>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
-    else if (minb == 12) launch_items_instance<false, 12>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
     else launch_items_instance<false, 10>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
     CUDA_OK(cudaGetLastError());
 }
