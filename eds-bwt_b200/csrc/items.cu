@@ -225,7 +225,7 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
             const uint32_t avail = pool_n - pool_pos;
             if (avail) {
                 const uint32_t r = __popc(needy & ((1u << lane) - 1u));
-                if (r < avail) {                                  // every needy lane is idle by now
+                if (((needy >> lane) & 1u) && r < avail) {        // (every needy lane is idle by now)
                     const uint32_t e = pool_pos + r;
                     const uint2 pm = s_pm[wid][e];
                     q = pool_base + e; m = pm.x; wb = pm.y; ovf = false;

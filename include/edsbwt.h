@@ -179,6 +179,33 @@ int  edsbwt_result_device_ptrs(const edsbwt_result* res, const uint32_t** d_coun
 int  edsbwt_result_fetch(const edsbwt_result* res, uint32_t* counts, edsbwt_occ* occ); /* D2H into host buffers */
 void edsbwt_result_free(edsbwt_result* res);
 
+/* --- multi-GPU, one process (replaces the single EDSBWT object on a single thread of mainEDS-BWT.cpp:66-70):
+ *     the index is replicated on every listed device (devices == NULL / ndev == 0: all visible devices), patterns are sharded
+ *     in contiguous blocks, every shard is searched in chunks_per_gpu chunks (<= 0: 4) and the per-pattern counts and the
+ *     occurrence tuples of chunk c are gathered on devices[0] while chunk c + 1 is searched: ncclSend / ncclRecv inside one
+ *     ncclGroupStart/End per chunk (NCCL is bound at run time; without libnccl, or with EDSBWT_MULTI_P2P=1, peer copies over
+ *     NVLink are used instead).  pat_off == NULL: npat patterns of fixed_len bytes back to back.  HOST pointers.
+ *     The result lives in the HBM of devices[0]: counts[npat] and one tuple segment per (shard, chunk), in ascending pattern
+ *     order; tuples carry batch-global pattern numbers. */
+typedef struct edsbwt_multi edsbwt_multi;
+typedef struct edsbwt_multi_result edsbwt_multi_result;
+int  edsbwt_multi_open(const char* base, const int* devices, int ndev, const edsbwt_open_opts* opts, edsbwt_multi** out);
+int  edsbwt_multi_info(const edsbwt_multi* m, int* ndev, int* devices, int devices_cap, int* nccl /* 1: NCCL in use */);
+edsbwt_index* edsbwt_multi_handle(edsbwt_multi* m, int i);      /* the i-th device's handle (edsbwt_set_row_order, edsbwt_set_stats ...) */
+void edsbwt_multi_close(edsbwt_multi* m);
+int  edsbwt_search_multi(edsbwt_multi* m, const uint8_t* pat_bytes, const uint64_t* pat_off, uint32_t fixed_len, uint32_t npat,
+                         int locate, int lf_variant, int chunks_per_gpu, edsbwt_multi_result** res);
+/* search_ms: largest per-device sum of search times (CUDA events); gather_ms: first gather issued -> last gather landed
+ * on devices[0] (CUDA events on its communication stream; overlaps the searches); wall_ms: the whole call;
+ * gather_bytes: bytes that crossed NVLink. */
+int  edsbwt_multi_result_info(const edsbwt_multi_result* r, uint32_t* npat, uint64_t* nocc, uint32_t* nseg, double* search_ms,
+                              double* gather_ms, double* wall_ms, uint64_t* gather_bytes);
+int  edsbwt_multi_result_device_ptrs(const edsbwt_multi_result* r, const uint32_t** d_counts, const edsbwt_occ** seg_occ,
+                                     uint64_t* seg_nocc, uint32_t* seg_pat_lo, uint32_t seg_cap);
+int  edsbwt_multi_result_fetch(const edsbwt_multi_result* r, uint32_t* counts, edsbwt_occ* occ);   /* D2H, ascending pattern order */
+int  edsbwt_multi_result_write_csv(edsbwt_multi* m, const edsbwt_multi_result* r, const char* path, int move, int append, uint64_t* bytes);
+void edsbwt_multi_result_free(edsbwt_multi_result* r);
+
 int  edsbwt_last_stats(const edsbwt_index* idx, edsbwt_stats* st);
 int  edsbwt_set_stats(edsbwt_index* idx, int collect_counters, uint32_t canonical_k);
 
