@@ -28,6 +28,9 @@ EXPORTS = [
     "edsbwt_set_chunk", "edsbwt_search_trace", "edsbwt_move_table_build", "edsbwt_move_table_fetch", "edsbwt_search_device_at", "edsbwt_gather_bench_ex",
     "edsbwt_set_row_order", "edsbwt_result_write_csv", "edsbwt_search_to_csv", "edsbwt_string_check", "edsbwt_search_into_fixed",
     "edsbwt_search_into_packed", "edsbwt_pack_patterns", "edsbwt_pack_patterns_alphabet",
+    "edsbwt_multi_open", "edsbwt_multi_info", "edsbwt_multi_handle", "edsbwt_multi_close", "edsbwt_search_multi",
+    "edsbwt_multi_result_info", "edsbwt_multi_result_device_ptrs", "edsbwt_multi_result_fetch", "edsbwt_multi_result_write_csv",
+    "edsbwt_multi_result_free", "edsbwt_gather_bench_cfg", "edsbwt_move_table_save",
 ]
 
 
@@ -35,12 +38,18 @@ class Info(C.Structure):
     _fields_ = [("n", C.c_uint32), ("n_text", C.c_uint32), ("n_seg", C.c_uint32), ("sigma", C.c_uint32),
                 ("alphabet", C.c_uint8 * 8), ("table_occ", C.c_uint32 * 25), ("seed_k", C.c_uint32),
                 ("locate_mode", C.c_uint32), ("device_bytes", C.c_uint64), ("seed_intervals", C.c_uint64),
-                ("move_runs", C.c_uint32), ("move_intervals", C.c_uint32), ("move_a", C.c_uint32), ("move_rounds", C.c_uint32)]
+                ("move_runs", C.c_uint32), ("move_intervals", C.c_uint32), ("move_a", C.c_uint32), ("move_rounds", C.c_uint32),
+                ("from_file", C.c_uint32)]
+
+
+class GatherCfg(C.Structure):
+    _fields_ = [("buffer_bytes", C.c_uint64), ("n_access", C.c_uint64), ("iters", C.c_int32), ("granule_bytes", C.c_int32), ("ilp", C.c_int32),
+                ("ctas_per_sm", C.c_int32), ("dependent", C.c_int32), ("reserved", C.c_int32), ("mix_bytes", C.c_uint64), ("mix_frac", C.c_double)]
 
 
 class OpenOpts(C.Structure):
     _fields_ = [("seed_k", C.c_int32), ("locate_mode", C.c_int32), ("verify", C.c_int32), ("build_move", C.c_int32),
-                ("engine", C.c_int32), ("fused_cap", C.c_int32), ("fused_cap2", C.c_int32), ("move_a", C.c_int32)]
+                ("engine", C.c_int32), ("fused_cap", C.c_int32), ("fused_cap2", C.c_int32), ("move_a", C.c_int32), ("cache", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -93,8 +102,23 @@ def lib():
         L.edsbwt_pack_patterns.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]
         L.edsbwt_pack_patterns_alphabet.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p,
                                                     C.POINTER(C.c_uint32)]
+        L.edsbwt_multi_open.argtypes = [C.c_char_p, C.POINTER(C.c_int), C.c_int, C.POINTER(OpenOpts), C.POINTER(C.c_void_p)]
+        L.edsbwt_multi_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_int)]
+        L.edsbwt_multi_handle.argtypes = [C.c_void_p, C.c_int]
+        L.edsbwt_multi_handle.restype = C.c_void_p
+        L.edsbwt_multi_close.argtypes = [C.c_void_p]
+        L.edsbwt_multi_close.restype = None
+        L.edsbwt_search_multi.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.edsbwt_multi_result_info.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint32), C.POINTER(C.c_double),
+                                               C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
+        L.edsbwt_multi_result_device_ptrs.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
+        L.edsbwt_multi_result_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.edsbwt_multi_result_write_csv.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_uint64)]
+        L.edsbwt_multi_result_free.argtypes = [C.c_void_p]
+        L.edsbwt_multi_result_free.restype = None
         L.edsbwt_search_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
         L.edsbwt_move_table_build.argtypes = [C.c_void_p]
+        L.edsbwt_move_table_save.argtypes = [C.c_void_p, C.c_char_p]
         L.edsbwt_move_table_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
         L.edsbwt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_uint64]
         L.edsbwt_host_free.argtypes = [C.c_void_p]
@@ -118,6 +142,7 @@ def lib():
         L.edsbwt_build_from_eds.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         L.edsbwt_build_from_collection.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_char_p, C.c_int]
         L.edsbwt_gather_bench.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_double)]
+        L.edsbwt_gather_bench_cfg.argtypes = [C.c_int, C.POINTER(GatherCfg), C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.edsbwt_gather_bench_ex.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_double)]
         _lib = L
     return _lib
@@ -143,10 +168,10 @@ class Index:
     """Device-resident EDS-BWT index (edsbwt_index_open_ex)."""
 
     def __init__(self, base, device=0, seed_k=-1, locate_mode=LOCATE_SA, verify=True, build_move=False,
-                 engine=ENGINE_FUSED, fused_cap=0, fused_cap2=0, move_a=0):
+                 engine=ENGINE_FUSED, fused_cap=0, fused_cap2=0, move_a=0, cache=False):
         self._h = C.c_void_p()
         o = OpenOpts(seed_k=seed_k, locate_mode=locate_mode, verify=int(verify), build_move=int(build_move),
-                     engine=engine, fused_cap=fused_cap, fused_cap2=fused_cap2, move_a=move_a)
+                     engine=engine, fused_cap=fused_cap, fused_cap2=fused_cap2, move_a=move_a, cache=int(cache))
         _check(lib().edsbwt_index_open_ex(os.fsencode(base), device, C.byref(o), C.byref(self._h)))
         self.device = device
 
@@ -198,6 +223,10 @@ class Index:
             occ = np.frombuffer(buf, dtype=OCC_DTYPE).copy()
             lib().edsbwt_free(occ_p)
         return counts[:npat], occ
+
+    def save_move_table(self, path=None):
+        """edsbwt_move_table_save: <base>_MLF.edsbwt (or path); later opens of the same index files load it"""
+        _check(lib().edsbwt_move_table_save(self._h, os.fsencode(path) if path else None))
 
     def move_table(self):
         """-> (p, q, dest, sym) columns of the move table (builds it when needed)."""
@@ -284,6 +313,63 @@ class Index:
         _check(lib().edsbwt_search_device_at(self._h, C.c_void_p(d_bytes_ptr), C.c_void_p(d_off_ptr), npat, total_bytes,
                                              max_len, int(locate), lf_variant, pat_base, C.byref(r)))
         return DeviceResult(r)
+
+
+class MultiIndex:
+    """The index replicated on several GPUs of this process (edsbwt_multi_open); patterns are sharded, the results gathered
+    on the first device with NCCL while the next chunk is searched."""
+
+    def __init__(self, base, devices=None, seed_k=-1, locate_mode=LOCATE_SA, verify=True, build_move=False, engine=ENGINE_FUSED,
+                 fused_cap=0, fused_cap2=0, move_a=0):
+        self._h = C.c_void_p()
+        o = OpenOpts(seed_k=seed_k, locate_mode=locate_mode, verify=int(verify), build_move=int(build_move),
+                     engine=engine, fused_cap=fused_cap, fused_cap2=fused_cap2, move_a=move_a, cache=0)
+        devs = (C.c_int * len(devices))(*devices) if devices else None
+        _check(lib().edsbwt_multi_open(os.fsencode(base), devs, len(devices) if devices else 0, C.byref(o), C.byref(self._h)))
+        n, nccl = C.c_int(), C.c_int()
+        d = (C.c_int * 64)()
+        _check(lib().edsbwt_multi_info(self._h, C.byref(n), d, 64, C.byref(nccl)))
+        self.devices, self.nccl = list(d[:n.value]), bool(nccl.value)
+
+    def close(self):
+        if self._h:
+            lib().edsbwt_multi_close(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def set_row_order(self, reference=True):
+        for i in range(len(self.devices)):
+            _check(lib().edsbwt_set_row_order(lib().edsbwt_multi_handle(self._h, i), ROWS_REFERENCE if reference else ROWS_GROUPED))
+
+    def search(self, patterns, locate=True, lf_variant=LF_RANK, chunks_per_gpu=0, fixed_len=0, csv_path=None, move=False):
+        """patterns: list of bytes or (uint8 data, uint64 offsets); fixed_len > 0: data holds equal-length patterns, no offsets.
+        -> (counts, occurrence tuples in ascending pattern order, info dict)"""
+        if fixed_len:
+            data = np.ascontiguousarray(patterns, dtype=np.uint8); off = None; npat = len(data) // fixed_len
+        else:
+            data, off = pack_patterns(patterns) if isinstance(patterns, (list, tuple)) and not (
+                len(patterns) == 2 and isinstance(patterns[0], np.ndarray)) else patterns
+            data = np.ascontiguousarray(data, dtype=np.uint8); off = np.ascontiguousarray(off, dtype=np.uint64); npat = len(off) - 1
+        r = C.c_void_p()
+        _check(lib().edsbwt_search_multi(self._h, data.ctypes.data, off.ctypes.data if off is not None else None, fixed_len, npat,
+                                         int(locate), lf_variant, chunks_per_gpu, C.byref(r)))
+        try:
+            n, o, ns = C.c_uint32(), C.c_uint64(), C.c_uint32()
+            sm, gm, wm, gb = C.c_double(), C.c_double(), C.c_double(), C.c_uint64()
+            _check(lib().edsbwt_multi_result_info(r, C.byref(n), C.byref(o), C.byref(ns), C.byref(sm), C.byref(gm), C.byref(wm), C.byref(gb)))
+            counts = np.zeros(max(n.value, 1), np.uint32); occ = np.zeros(max(o.value, 1), OCC_DTYPE)
+            _check(lib().edsbwt_multi_result_fetch(r, counts.ctypes.data, occ.ctypes.data))
+            if csv_path:
+                _check(lib().edsbwt_multi_result_write_csv(self._h, r, os.fsencode(csv_path), int(move), 0, None))
+            info = {"segments": ns.value, "search_ms": sm.value, "gather_ms": gm.value, "wall_ms": wm.value, "gather_bytes": gb.value}
+        finally:
+            lib().edsbwt_multi_result_free(r)
+        return counts[:n.value], occ[:o.value], info
 
 
 class DeviceResult:
@@ -394,6 +480,16 @@ def build_from_collection(text, str_off, seg_first, out_base, device=0):
     seg_first = np.ascontiguousarray(seg_first, dtype=np.uint8)
     _check(lib().edsbwt_build_from_collection(text.ctypes.data if text.size else None, str_off.ctypes.data, len(seg_first),
                                               seg_first.ctypes.data, os.fsencode(out_base), device))
+
+
+def gather_bench_cfg(device=0, buffer_bytes=4 << 30, n_access=1 << 27, iters=3, granule=64, ilp=4, ctas_per_sm=0, dependent=False,
+                     mix_bytes=0, mix_frac=0.0):
+    """-> (algorithmic GB/s, requests/s) of the random-gather microbenchmark in one configuration (csrc/gather_bench.cu)"""
+    cfg = GatherCfg(buffer_bytes=buffer_bytes, n_access=n_access, iters=iters, granule_bytes=granule, ilp=ilp, ctas_per_sm=ctas_per_sm,
+                    dependent=int(dependent), reserved=0, mix_bytes=mix_bytes, mix_frac=mix_frac)
+    g, r = C.c_double(), C.c_double()
+    _check(lib().edsbwt_gather_bench_cfg(device, C.byref(cfg), C.byref(g), C.byref(r)))
+    return g.value, r.value
 
 
 def gather_bench(device=0, buffer_bytes=4 << 30, n_access=1 << 26, iters=5, granule=64):

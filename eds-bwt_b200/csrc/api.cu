@@ -37,9 +37,18 @@ int edsbwt_index_open_ex(const char* base, int device, const edsbwt_open_opts* o
     edsbwt_index* h = nullptr;
     rc = guarded([&] {
         h = new edsbwt_index;
-        h->ix.device = device;
-        load_host_index(base, o.verify != 0, h->ix.host);
-        build_device_index(h->ix, o);
+        Index& ix = h->ix;
+        ix.device = device; ix.base = base; ix.cache_mode = o.cache;
+        ix.move_a_explicit = o.move_a > 0; ix.move_a = o.move_a > 0 ? (uint32_t)o.move_a : 8u;
+        if (o.cache && image_cache_load(ix, o)) {          // <base>.edsbwt written by an earlier open of these very files
+            ix.image_from_file = true;
+            init_index_runtime(ix, o);
+            if (o.build_move) build_move_table(ix);
+        } else {
+            load_host_index(base, o.verify != 0, ix.host);
+            build_device_index(ix, o);
+            if (o.cache) image_cache_save(ix);
+        }
     });
     if (rc) { cudaSetDevice(device); delete h; return rc; }
     *out = h;
@@ -62,6 +71,7 @@ int edsbwt_index_info(const edsbwt_index* idx, edsbwt_info* info) {
     for (uint32_t i = 0; i < h.sigma * h.sigma && i < 25; ++i) info->table_occ[i] = h.table_occ[i];
     info->seed_k = idx->ix.seed_k; info->locate_mode = (uint32_t)idx->ix.locate_mode;
     info->device_bytes = idx->ix.device_bytes(); info->seed_intervals = idx->ix.seed_intervals;
+    info->from_file = (idx->ix.image_from_file ? 1u : 0u) | (idx->ix.move_from_file ? 2u : 0u);
     if (const MoveTable* mt = idx->ix.move) { info->move_runs = mt->r_runs; info->move_intervals = mt->r; info->move_a = mt->a; info->move_rounds = mt->rounds; }
     return EDSBWT_OK;
 }
@@ -447,6 +457,12 @@ int edsbwt_move_table_build(edsbwt_index* idx) {
     if (!idx) return EDSBWT_E_ARG;
     return guarded([&] { std::lock_guard<std::mutex> lock(idx->ix.mu); build_move_table(idx->ix); });
 }
+int edsbwt_move_table_save(edsbwt_index* idx, const char* path) {
+    if (!idx) return EDSBWT_E_ARG;
+    int rc = edsbwt_move_table_build(idx);
+    if (rc) return rc;
+    return guarded([&] { std::lock_guard<std::mutex> lock(idx->ix.mu); move_cache_save(idx->ix, path ? std::string(path) : idx->ix.base + "_MLF.edsbwt"); });
+}
 int edsbwt_move_table_fetch(edsbwt_index* idx, uint32_t* p, uint32_t* q, uint32_t* dest, uint8_t* sym, uint32_t cap, uint32_t* r) {
     if (!idx || !r) return EDSBWT_E_ARG;
     int rc = edsbwt_move_table_build(idx);
@@ -492,6 +508,17 @@ int edsbwt_gather_bench_ex(int device, uint64_t buffer_bytes, uint64_t n_access,
     int rc = require_device(device);
     if (rc) return rc;
     return guarded([&] { *gb_per_s = gather_bench(device, buffer_bytes, n_access, iters, granule_bytes); });
+}
+
+int edsbwt_gather_bench_cfg(int device, const edsbwt_gather_cfg* cfg, double* gb_per_s, double* req_per_s) {
+    if (!cfg || !gb_per_s) return EDSBWT_E_ARG;
+    int rc = require_device(device);
+    if (rc) return rc;
+    return guarded([&] {
+        GatherCfg c; c.buffer_bytes = cfg->buffer_bytes; c.n_access = cfg->n_access; c.iters = cfg->iters; c.granule = cfg->granule_bytes; c.ilp = cfg->ilp;
+        c.ctas_per_sm = cfg->ctas_per_sm; c.dependent = cfg->dependent; c.mix_bytes = cfg->mix_bytes; c.mix_frac = cfg->mix_frac;
+        *gb_per_s = gather_bench_cfg(device, c, req_per_s);
+    });
 }
 
 int edsbwt_build_from_collection(const uint8_t* text, const uint64_t* str_off, uint32_t nstr, const uint8_t* seg_first,

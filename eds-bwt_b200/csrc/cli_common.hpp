@@ -73,6 +73,7 @@ inline int run_cli(int argc, char** argv, bool move) {
     opts.locate_mode = env_int("EDSBWT_LOCATE_WALK", 0) ? EDSBWT_LOCATE_WALK : EDSBWT_LOCATE_SA;
     opts.verify = env_int("EDSBWT_VERIFY", 1);
     opts.build_move = move ? 1 : 0;
+    opts.cache = env_int("EDSBWT_CACHE", 0);               // 1: keep / reuse the HBM image in <index>.edsbwt
     edsbwt_index* idx = nullptr;
     int rc = edsbwt_index_open_ex(fileInput.c_str(), device, &opts, &idx);
     if (rc) die(("Error opening " + fileInput + "_info.aux / index files").c_str(), rc);
@@ -118,7 +119,28 @@ inline int run_cli(int argc, char** argv, bool move) {
     edsbwt_occ* occ = nullptr; uint64_t nocc = 0;
     const int lf = move ? EDSBWT_LF_MOVE : EDSBWT_LF_RANK;
     // locate: rows come out in the reference's csv order and are formatted to text on the device
-    if (recover) rc = edsbwt_search_to_csv(idx, bytes, off, npat, lf, counts.data(), csv.c_str(), &nocc);
+    // EDSBWT_DEVICES = all | <n>: the batch is sharded over that many GPUs of the box, results gathered on the first one over
+    // NCCL / NVLink (edsbwt_search_multi) and written from there; the handle opened above stays the one that reports the index
+    const char* devs = getenv("EDSBWT_DEVICES");
+    const int want_dev = (devs && *devs) ? (strcmp(devs, "all") == 0 ? 0 : atoi(devs)) : 1;
+    if (recover && want_dev != 1) {
+        edsbwt_index_close(idx); idx = nullptr;          // the multi handle opens its own replicas
+        std::vector<int> list;
+        for (int d = 0; d < want_dev; ++d) list.push_back(d);
+        edsbwt_multi* mh = nullptr;
+        rc = edsbwt_multi_open(fileInput.c_str(), want_dev ? list.data() : nullptr, want_dev, &opts, &mh);
+        if (rc) die("multi-GPU open failed", rc);
+        int nd = 0; edsbwt_multi_info(mh, &nd, nullptr, 0, nullptr);
+        for (int d = 0; d < nd; ++d) edsbwt_set_row_order(edsbwt_multi_handle(mh, d), EDSBWT_ROWS_REFERENCE);
+        edsbwt_multi_result* mr = nullptr;
+        rc = edsbwt_search_multi(mh, bytes, off, 0, npat, 1, lf, env_int("EDSBWT_CHUNKS", 4), &mr);
+        if (rc) die("search failed", rc);
+        rc = edsbwt_multi_result_fetch(mr, counts.data(), nullptr);
+        if (!rc) rc = edsbwt_multi_result_write_csv(mh, mr, csv.c_str(), move ? 1 : 0, 1, nullptr);
+        edsbwt_multi_result_free(mr);
+        edsbwt_multi_close(mh);
+    }
+    else if (recover) rc = edsbwt_search_to_csv(idx, bytes, off, npat, lf, counts.data(), csv.c_str(), &nocc);
     else { interrupted.assign(npat ? npat : 1, 0); rc = edsbwt_search_trace(idx, bytes, off, npat, lf, counts.data(), interrupted.data()); }
     if (rc) die("search failed", rc);
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
@@ -165,7 +187,7 @@ inline int run_cli(int argc, char** argv, bool move) {
     edsbwt_free(occ); edsbwt_free(bytes); edsbwt_free(off);
     if (recover) std::cerr << "\nThe csv file is ready! \n";                 // mainEDS-BWT.cpp:72-76
     else std::cerr << "\nThe search is finished! \n";
-    edsbwt_index_close(idx);
+    if (idx) edsbwt_index_close(idx);
     std::cerr << "The End!\n";
     return 1;                  // mainEDS-BWT.cpp:82, mainMove_EDSBWT.cpp:61: success IS exit status 1
 }

@@ -724,7 +724,7 @@ static void build_seed_table(Index& ix, uint32_t k) {
     CUDA_OK(cudaStreamSynchronize(s));
     CUDA_OK(cudaGetLastError());
 }
-void build_device_index(Index& ix, const edsbwt_open_opts& o) {
+void init_index_runtime(Index& ix, const edsbwt_open_opts& o) {
     HostIndex& h = ix.host;
     CUDA_OK(cudaSetDevice(ix.device));
     CUDA_OK(cudaStreamCreateWithFlags(&ix.stream, cudaStreamNonBlocking));
@@ -744,7 +744,14 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     if (ix.fused_cap2 < 4) ix.fused_cap2 = 4;
     { Lut l = make_lut(h); ix.lut.ensure(256); CUDA_OK(cudaMemcpyAsync(ix.lut.p, l.code, 256, cudaMemcpyHostToDevice, s)); CUDA_OK(cudaStreamSynchronize(s)); }
     ws.scalars.ensure(16);
+    if (const char* e = getenv("EDSBWT_OCC_LIMIT")) { const unsigned long long v = strtoull(e, nullptr, 10); if (v && v < ix.occ_limit) ix.occ_limit = v; }
+}
 
+void build_device_index(Index& ix, const edsbwt_open_opts& o) {
+    HostIndex& h = ix.host;
+    init_index_runtime(ix, o);
+    cudaStream_t s = ix.stream;
+    Workspace& ws = *ix.ws;
     IndexView& v = ix.view;
     v.n = h.n; v.n_text = h.n_text; v.n_seg = h.n_seg; v.nletters = h.sigma - 1;
     for (uint32_t c = 0; c < 5; ++c) v.Cl[c] = c < h.sigma - 1 ? h.pile_start[c + 1] : h.n;
@@ -837,8 +844,6 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     ix.seed_k = (uint32_t)k;
     build_seed_table(ix, ix.seed_k);
     CUDA_OK(cudaGetLastError());
-    ix.move_a = o.move_a > 0 ? (uint32_t)o.move_a : 8u;
-    if (const char* e = getenv("EDSBWT_OCC_LIMIT")) { const unsigned long long v = strtoull(e, nullptr, 10); if (v && v < ix.occ_limit) ix.occ_limit = v; }
     if (o.build_move) build_move_table(ix);
     h.ebwt.clear(); h.ebwt.shrink_to_fit();
     h.seg_first_bit.clear(); h.seg_first_bit.shrink_to_fit();

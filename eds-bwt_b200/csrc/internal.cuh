@@ -214,7 +214,7 @@ __device__ __forceinline__ void lf_range_loaded(Blk& B, const uint4* __restrict_
     const uint32_t blkA = a >> 7, blkB = b >> 7;
     if (blkA == blkB) {
         const int offA = (int)(a & 127u), offB = (int)(b & 127u);
-        uint32_t r = c == 0 ? B.w[0] : c == 1 ? B.w[4] : c == 2 ? B.w[8] : B.w[12];
+        uint32_t r = (c & 2) ? ((c & 1) ? B.w[12] : B.w[8]) : ((c & 1) ? B.w[4] : B.w[0]);      // selects, not branches: lanes hold different letters
         uint32_t in = 0, hin = 0;
         #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -356,6 +356,9 @@ struct ResultPool {
 
 struct Index {
     int device = 0;
+    std::string base;     // <indexBase> of the reference's files (the persisted tables live next to them, cache.cu)
+    int cache_mode = 0;   // edsbwt_open_opts.cache
+    bool image_from_file = false, move_from_file = false, move_a_explicit = false;
     cudaStream_t stream = nullptr;
     std::mutex mu;        // one search (run_search / csv emission / move-table build) at a time on the handle's stream and workspace
     std::mutex call_mu;   // one host-buffer call at a time: the chunk pipeline (Pipe) is per handle; taken before mu, never after
@@ -395,7 +398,14 @@ struct Lut { uint8_t code[256]; };     // 0..3 letter code, 4 = end-marker, 255 
 Lut make_lut(const HostIndex& h);
 void build_occ_blocks(const uint8_t* d_bytes, uint32_t n, const Lut& lut, DevBuf<uint4>& occ, DevBuf<uint8_t>& cubtmp, cudaStream_t s,
                       uint32_t tot[4], unsigned int* bad_out);
+void init_index_runtime(Index& ix, const edsbwt_open_opts& o);      // stream, workspace, engine options, byte -> code table
 void build_device_index(Index& ix, const edsbwt_open_opts& o);
+// cache.cu -- persisted tables: <base>.edsbwt (whole HBM image, opt-in) and <base>_MLF.edsbwt (move table)
+uint64_t source_fingerprint(const std::string& base);
+bool image_cache_load(Index& ix, const edsbwt_open_opts& o);
+void image_cache_save(Index& ix);
+bool move_cache_load(Index& ix, const std::string& path);
+void move_cache_save(Index& ix, const std::string& path);
 // what a call knows about its batch besides bytes + offsets
 struct PatHint {
     uint32_t fixed_len = 0;              // > 0: every pattern has this many characters; pattern q starts at byte fixed_base + q * fixed_len of d_bytes (d_off may be null)
@@ -444,6 +454,9 @@ uint64_t write_csv_device(Index& ix, const edsbwt_occ* d_occ, uint64_t nocc, uin
 void build_index_files(const uint8_t* letters, const uint64_t* str_off, uint32_t nstr, const uint8_t* seg_first,
                        const std::string& out_base, int device);
 // gather_bench.cu
+struct GatherCfg { uint64_t buffer_bytes = 0, n_access = 0; int iters = 3, granule = 64, ilp = 4, ctas_per_sm = 0, dependent = 0;
+                   uint64_t mix_bytes = 0; double mix_frac = 0; };
+double gather_bench_cfg(int device, const GatherCfg& c, double* req_per_s);
 double gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, int granule = 64);
 
 }  // namespace edsbwt

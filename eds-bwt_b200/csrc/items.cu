@@ -108,7 +108,12 @@ constexpr int ITEM_WARPS = FUSED_THREADS / 32;
 
 }  // namespace
 
-template <bool STATS, int MINB>
+// PERIOD: everything that is not an Occ item -- results of finished patterns, refill, link records, further seed intervals,
+// pattern words, the Dol' ++ F' splice -- runs only in every PERIOD-th sweep.  Those branches are taken by one or two lanes at a
+// time, so run in every sweep they cost the warp more instructions than the Occ items themselves (ncu: 45 % of all
+// instructions at 1.3 - 2 active lanes); batched, a lane waits PERIOD/2 sweeps on average for its turn and the branches run a
+// PERIOD-th as often.
+template <bool STATS, int MINB, int PERIOD>
 __global__ void __launch_bounds__(FUSED_THREADS, MINB)
 search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant__ SeedView sv, uint32_t k, const __grid_constant__ PackedPats pp,
                     uint32_t npat, uint32_t cap, FusedOut out, uint32_t* __restrict__ work, StatsDev* __restrict__ st, uint32_t kc) {
@@ -184,9 +189,10 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     };
 
     grab_pool();
-    for (;;) {
+    for (uint32_t sweep = 0;; ++sweep) {
+        const bool gate = PERIOD == 1 || sweep % PERIOD == 0;
         // ---------------- finished lanes write their results; they and the idle lanes take the next patterns of the pool
-        const uint32_t needy = __ballot_sync(FULL, kind <= K_FIN);
+        const uint32_t needy = gate ? __ballot_sync(FULL, kind <= K_FIN) : 0u;
         if (needy) {
             if (kind == K_FIN) {
                 // count + the final interval list.  One interval (nearly every found pattern) travels inside the plist entry
@@ -272,9 +278,11 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         if (occ_item) {
             const uint4* p = ix.occ + (size_t)(SLOT(slot).x >> 7) * 4;
             ld256(p, B); ld256(p + 2, B + 8);
-        } else if (kind == K_LINK) ld64(ix.link_rec + cur, B);
-        else if (kind == K_SEEDIV) ld64(s_iv[m < k ? m : k] + cur, B);
-        else if (kind == K_WORD) ld64(pp.words + wb + (spos >> 5), B);
+        } else if (gate) {
+            if (kind == K_LINK) ld64(ix.link_rec + cur, B);
+            else if (kind == K_SEEDIV) ld64(s_iv[m < k ? m : k] + cur, B);
+            else if (kind == K_WORD) ld64(pp.words + wb + (spos >> 5), B);
+        }
 
         // ---------------- consume
         if (occ_item) {
@@ -288,7 +296,8 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
             const bool pass2 = kind == K_OCCD;
             uint32_t no = pass2 ? aux : nout;
             if (rcb > rca) {
-                const uint32_t Cc = s_Cl[c], nlo = Cc + rca, nhi = Cc + rcb - 1;
+                const uint32_t Cc = (c & 2) ? ((c & 1) ? ix.Cl[3] : ix.Cl[2]) : ((c & 1) ? ix.Cl[1] : ix.Cl[0]);
+                const uint32_t nlo = Cc + rca, nhi = Cc + rcb - 1;
                 const uint32_t prev = pass2 ? cap - no : no - 1;      // slot of the last output (valid when no > 0)
                 if (no && SLOT(prev).y + 1 == nlo) SLOT(prev).y = nhi;
                 else { SLOT(pass2 ? cap - 1 - no : no) = make_uint2(nlo, nhi); ++no; }
@@ -303,6 +312,8 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
                     else { nF = nout; ++spos; next_step(); }
                 }
             }
+        } else if (!gate) {
+            // every other kind waits for its sweep
         } else if (kind == K_LINK) {
             // pile-0 range [l, h] of the preceding segment(s) -> sorted, merged Dol set at the top of the column
             uint32_t l = B[0], h = B[1];
@@ -339,7 +350,7 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
             win = ((uint64_t)B[1] << 32) | B[0];
             kind = K_OCCF; j = 0; nout = 0; ndol = 0;
         }
-        if (kind == K_ENDP2) {                                    // F <- Dol' ++ F'   (aux = length of Dol')
+        if (gate && kind == K_ENDP2) {                            // F <- Dol' ++ F'   (aux = length of Dol')
             if (aux) {
                 if (nout + 2 * aux > cap) { ovf = true; kind = K_FIN; }
                 else {
@@ -367,10 +378,10 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
 }
 
 namespace {
-template <bool STATS, int MINB>
+template <bool STATS, int MINB, int PERIOD>
 void launch_items_instance(size_t smem, cudaStream_t s, const IndexView& ix, const SeedView& sv, uint32_t k, const PackedPats& pp, uint32_t npat,
                            uint32_t cap, const FusedOut& out, uint32_t* work, StatsDev* st, uint32_t kc) {
-    auto kern = search_items_kernel<STATS, MINB>;
+    auto kern = search_items_kernel<STATS, MINB, PERIOD>;
     CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
     int dev = 0, sms = 148, per_sm = 1;
     CUDA_OK(cudaGetDevice(&dev));
@@ -390,12 +401,14 @@ void launch_items_search(const IndexView& ix, const SeedView& sv, uint32_t k, co
     if (npat == 0) return;
     if (npat > 0xff000000u) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 - 2^24 patterns in one search call; split the batch");
     const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
-    const char* e = getenv("EDSBWT_ITEMS_MINB");      // A/B of the occupancy target (profiles/scripts/r02_items_ab.py)
-    const int minb = e ? atoi(e) : 0;
-    if (st) launch_items_instance<true, 8>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
-    else if (cap > 16 || minb == 8) launch_items_instance<false, 8>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
-    else if (minb == 9) launch_items_instance<false, 9>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
-    else launch_items_instance<false, 10>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    const char* e = getenv("EDSBWT_ITEMS_PERIOD");      // A/B of the batching period (profiles/scripts/r02_items_ab.py)
+    const int period = e ? atoi(e) : 1;
+    if (st) launch_items_instance<true, 8, 1>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    else if (cap > 16) launch_items_instance<false, 8, 1>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    else if (period == 2) launch_items_instance<false, 10, 2>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    else if (period == 3) launch_items_instance<false, 10, 3>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    else if (period == 4) launch_items_instance<false, 10, 4>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    else launch_items_instance<false, 10, 1>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
     CUDA_OK(cudaGetLastError());
 }
 

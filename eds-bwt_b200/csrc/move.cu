@@ -118,6 +118,9 @@ __global__ void row_run0_kernel(const uint32_t* __restrict__ P, const uint32_t* 
 void build_move_table(Index& ix) {
     if (ix.move) return;
     CUDA_OK(cudaSetDevice(ix.device));
+    // a table written earlier by build_MLF / edsbwt_move_table_save for these very index files (the reference's
+    // retrieve_MLF, MOVE_EDSBWTSearch.cpp:186-192): stale or foreign files are ignored and the table is built
+    if (!ix.base.empty() && move_cache_load(ix, ix.base + "_MLF.edsbwt")) return;
     cudaStream_t s = ix.stream;
     const IndexView& v = ix.view;
     const uint32_t n = v.n, a = ix.move_a < 2 ? 2 : ix.move_a;

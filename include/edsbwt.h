@@ -59,6 +59,7 @@ typedef struct {
     uint32_t move_intervals;    /* move table: input intervals after a-balancing (Move-r's r')   */
     uint32_t move_a;            /* balancing parameter                                          */
     uint32_t move_rounds;       /* balancing rounds the builder needed                          */
+    uint32_t from_file;         /* bit 0: the HBM image was read from <base>.edsbwt; bit 1: the move table from <base>_MLF.edsbwt */
 } edsbwt_info;
 
 #define EDSBWT_LOCATE_SA    0   /* row -> (string, offset) table in HBM: one gather per occurrence           */
@@ -84,7 +85,10 @@ typedef struct {
     int32_t  engine;            /* EDSBWT_ENGINE_FUSED (default) / _LEVELSYNC / _FUSED_STEP                   */
     int32_t  fused_cap;         /* frontier slots per pattern of the first pass (0 = default 13)                */
     int32_t  fused_cap2;        /* slots of the second pass over the patterns that outgrew the first (0 = 192) */
-    int32_t  move_a;            /* balancing parameter a of the move table (build_MLF's <a>); 0 = default 8             */
+    int32_t  move_a;            /* balancing parameter a of the move table (build_MLF's <a>); 0 = default 8 (or whatever a valid <base>_MLF.edsbwt was built with) */
+    int32_t  cache;             /* 1 = keep the whole HBM image in <base>.edsbwt: read it when it is there and was written for these very index */
+                                /* files (sizes, times and sampled contents are fingerprinted), otherwise build and write it.  The file is as large */
+                                /* as the image (gigabytes: seed and locate tables are derived data) -- worth it when it stays in the page cache   */
 } edsbwt_open_opts;
 
 /* Canonical byte-model counters of DESIGN.md + engine statistics of the last search. */
@@ -214,6 +218,10 @@ int  edsbwt_set_stats(edsbwt_index* idx, int collect_counters, uint32_t canonica
  *     copies the columns to host arrays of `cap` entries (test / inspection hook): p = first row of input interval i,
  *     q = LF(p), dest = input interval containing q, sym = alphabet byte of the run.  *r = number of intervals. */
 int  edsbwt_move_table_build(edsbwt_index* idx);
+/* Writes the table to path (NULL: <base>_MLF.edsbwt, our documented format next to the reference's <base>_MLF.aux: csrc/cache.cu);
+ * every later open of the same index files loads it instead of building (MOVE_EDSBWT::retrieve_MLF, MOVE_EDSBWTSearch.cpp:186-192).
+ * The executable build_MLF <index> <a> is this call (build_MLF.cpp:53-164). */
+int  edsbwt_move_table_save(edsbwt_index* idx, const char* path);
 int  edsbwt_move_table_fetch(edsbwt_index* idx, uint32_t* p, uint32_t* q, uint32_t* dest, uint8_t* sym, uint32_t cap, uint32_t* r);
 
 /* --- output: replaces the csv writing of EDSBWT's constructor (:179-193) and of
@@ -255,7 +263,18 @@ int  edsbwt_string_check(const char* in_path, const char* out_path);
 
 /* --- roofline denominator: 64-byte random gather over buffer_bytes of HBM (kernel K7). */
 int  edsbwt_gather_bench(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, double* gb_per_s);
-int  edsbwt_gather_bench_ex(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, int granule_bytes /* 32, 64, 128 */, double* gb_per_s);
+int  edsbwt_gather_bench_ex(int device, uint64_t buffer_bytes, uint64_t n_access, int iters, int granule_bytes /* 32, 64 */, double* gb_per_s);
+/* The full sweep space (csrc/gather_bench.cu): one thread fetches a whole block with the search kernels' own 256-bit loads;
+ * ilp = independent blocks in flight per thread (1, 2, 4, 8); ctas_per_sm = resident CTAs of 256 threads (0: as many as fit);
+ * dependent = 1: every chain's next address comes out of the loaded data (what a backward search does); mix_bytes / mix_frac:
+ * a second buffer and the fraction of accesses that also gather 16 bytes from it (the seed / link / locate gathers).
+ * *gb_per_s counts granule_bytes per block + 16 per side gather; *req_per_s (may be NULL) the requests. */
+typedef struct {
+    uint64_t buffer_bytes, n_access;
+    int32_t  iters, granule_bytes, ilp, ctas_per_sm, dependent, reserved;
+    uint64_t mix_bytes; double mix_frac;
+} edsbwt_gather_cfg;
+int  edsbwt_gather_bench_cfg(int device, const edsbwt_gather_cfg* cfg, double* gb_per_s, double* req_per_s);
 
 void        edsbwt_free(void* p);
 const char* edsbwt_strerror(int code);

@@ -312,7 +312,11 @@ def test_occurrence_overflow_halves_the_chunk(eb, tmp_path, monkeypatch):
         idx.search_to_csv(pats, csv_ref)
     biggest = int(c_ref.max())
     assert len(o_ref) > 20 * biggest
-    monkeypatch.setenv("EDSBWT_OCC_LIMIT", str(3 * biggest))
+    # packed batches are halved at multiples of 32 patterns: the limit must admit the heaviest block of 32 length-3 patterns
+    w3 = [int(c_ref[i]) for i, p in enumerate(pats) if len(p) == 3]
+    limit = max(3 * biggest, max(sum(w3[i:i + 32]) for i in range(0, len(w3), 32)))
+    assert len(o_ref) > 3 * limit
+    monkeypatch.setenv("EDSBWT_OCC_LIMIT", str(limit))
     with eb.Index(base) as idx:
         c, o = idx.search(pats, locate=True)
         assert c.tolist() == c_ref.tolist() and eb.occ_rows(o) == eb.occ_rows(o_ref)
