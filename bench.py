@@ -63,6 +63,11 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--keep", action="store_true")
     ap.add_argument("--chunk", type=int, default=0, help="patterns per pipeline chunk of the host-buffer search (0 = library default)")
+    ap.add_argument("--config", default="cfg4", choices=["cfg4", "cfg5"],
+                    help="cfg4: the headline (10 M length-32 patterns per GPU, weak scaling); cfg5: BASELINE.json's length sweep -- --total patterns of "
+                         "length --len sharded over the GPUs (strong scaling), count-only and locate, on the same 250 Mbp index")
+    ap.add_argument("--total", type=int, default=100000000, help="cfg5: patterns of the whole job")
+    ap.add_argument("--gather-chunks", type=int, default=4, help="chunks per shard of the multi-GPU leg (gather of chunk c overlaps the search of chunk c+1)")
     ap.add_argument("--engine", default="items", choices=["items", "step"], help="hot kernel: items.cu (default) or the round-1 step-loop kernel (A/B)")
     return ap.parse_args()
 
@@ -316,6 +321,16 @@ def main():
     log("rank %d: index open in %.1fs: n=%d nText=%d nSeg=%d seed_k=%d seed_intervals=%d device_bytes=%.2f GB" % (
         rank, time.time() - t0, info.n, info.n_text, info.n_seg, info.seed_k, info.seed_intervals, info.device_bytes / 1e9))
 
+    if args.config == "cfg5":
+        out = cfg5_leg(args, eb, synth, idx, info, base, rank, world, local_rank)
+        idx.close()
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        if rank == 0:
+            emit(out)
+        return 0
+
     # ---- patterns of this rank (every rank regenerates the collection; seeds differ per rank)
     t0 = time.time()
     col = synth.chromosome_eds(args.mbp, seed=4)
@@ -386,40 +401,90 @@ def main():
         if it >= 2:
             e2o_ms += dt
     counts_generic = np.array(p_counts, copy=True)
-    # (b) the call for equal-length batches (this workload): no offset array crosses PCIe -- the headline e2e
-    e2e_ms, d2h, e2e_launches = 0.0, 0, 0
+    # (b) the call for equal-length batches of bytes: no offset array crosses PCIe
+    e2f_ms = 0.0
     for it in range(2 + args.steps):
         barrier()
         t1 = time.perf_counter()
         got = idx.search_into_fixed(p_data, args.plen, p_counts, p_occ, locate=True)
         dt = (time.perf_counter() - t1) * 1e3
         if it >= 2:
+            e2f_ms += dt
+    assert np.array_equal(counts_generic, np.asarray(p_counts)), "fixed-length and offset-array entry points disagree"
+    counts_fixed = np.array(p_counts, copy=True)
+    # (c) the headline e2e: the caller holds the batch as 2-bit words (edsbwt_search_into_packed): a quarter of the bytes over PCIe.
+    #     The host packer that makes them from bytes is timed separately (it belongs to reading the pattern file, not to a search)
+    stride = (args.plen + 31) // 32
+    p_words = eb.pinned_empty(args.npat * stride, np.uint64)
+    p_inval = eb.pinned_empty((args.npat + 31) // 32, np.uint32)
+    t1 = time.perf_counter()
+    _, _, nbad = idx.pack_patterns(p_data, args.plen, nthreads=os.cpu_count() or 1, words=p_words, invalid=p_inval)
+    pack_ms = (time.perf_counter() - t1) * 1e3
+    e2e_ms, d2h = 0.0, 0
+    for it in range(2 + args.steps):
+        barrier()
+        t1 = time.perf_counter()
+        got = idx.search_into_packed(p_words, p_inval, args.plen, args.npat, p_counts, p_occ, locate=True)
+        dt = (time.perf_counter() - t1) * 1e3
+        if it >= 2:
             e2e_ms += dt
             d2h = p_counts.nbytes + got * eb.OCC_DTYPE.itemsize
-    h2d = data.nbytes
-    assert np.array_equal(counts_generic, np.asarray(p_counts)), "fixed-length and offset-array entry points disagree"
+    h2d = p_words.nbytes + p_inval.nbytes
+    assert nbad == 0 and np.array_equal(counts_fixed, np.asarray(p_counts)), "packed and byte entry points disagree"
     gpu_counts = np.array(p_counts, copy=True)
     gpu_occ_total = int(got)
     gpu_occ_head = np.array(p_occ[:min(int(got), 1 << 18)], copy=True)      # tuples of the first patterns: row parity against the reference sample
     # ---- multi-GPU result gather (north star: "only an NCCL/NVLink gather of per-pattern counts and occurrence buffers"):
     #      shard search + all-gather of the counts + gather-v of the tuples to rank 0, timed on the device
-    gather_ms, gather_bytes = 0.0, 0
+    gather_ms, gather_bytes, gather_parity, nchunks = 0.0, 0, None, args.gather_chunks
     if world > 1:
+        # every shard is searched in chunks; the counts and tuples of chunk c are put on the wire (ncclSend / ncclRecv, one group
+        # per chunk) as soon as it is searched and travel while chunk c + 1 is searched.  Timed on the device: CUDA events on this
+        # rank's stream from before the first chunk to after the last transfer has landed, max over ranks below.
         sh = importlib.import_module("eds-bwt_b200.sharded")
+        size_group = dist.new_group(backend="gloo")          # 8-byte size exchanges go over the host, never behind the bulk transfers
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        gnpat = args.npat * world
+        d_off64 = d_off
+        csum = None
         for it in range(2 + args.steps):
             barrier()
             ev0.record()
-            r = idx.search_device(d_data.data_ptr(), d_off.data_ptr(), args.npat, total_bytes, args.plen, locate=True, pat_base=rank * args.npat)
-            c_loc, o_loc = sh.device_result_tensors(r, local_rank)
-            allc, allo, tots = sh.gather_results(c_loc, o_loc, args.npat * world, None, 0)
+            g = sh.ChunkedGather(gnpat, nchunks, None, size_group, 0)
+            live = []
+            for c in range(nchunks):
+                cb, ce = sh.chunk_range(0, args.npat, nchunks, c)
+                # (offsets are absolute: the byte pointer stays the batch's, the offset pointer moves to the chunk)
+                r = idx.search_device(d_data.data_ptr(), d_off64.data_ptr() + cb * 8, ce - cb, (ce - cb) * args.plen, args.plen,
+                                      locate=True, pat_base=rank * args.npat + cb)
+                live.append(r)
+                c_loc, o_loc = sh.device_result_tensors(r, local_rank)
+                g.post(c, c_loc, o_loc)
+            allc, segs = g.finish()
             ev1.record()
             torch.cuda.synchronize()
-            r.free()
             if it >= 2:
                 gather_ms += ev0.elapsed_time(ev1)
-                gather_bytes = 4 * args.npat * world + 20 * sum(tots)
-            del allc, allo
+                gather_bytes = g.bytes_moved
+            if it == 2 + args.steps - 1:
+                # gather parity: what arrived on rank 0 against what every rank computed (sums over its own shard, all-reduced)
+                loc = torch.zeros(3, dtype=torch.int64, device="cuda")
+                for r in live:
+                    c_loc, o_loc = sh.device_result_tensors(r, local_rank)
+                    loc[0] += c_loc.to(torch.int64).sum(); loc[1] += o_loc.shape[0]
+                    if o_loc.shape[0]:
+                        loc[2] += (o_loc[:, 0].to(torch.int64) & 0xffffffff).sum()
+                dist.all_reduce(loc)
+                if rank == 0:
+                    got3 = [int(allc.to(torch.int64).sum()), sum(int(x.shape[0]) for x in segs),
+                            sum(int((x[:, 0].to(torch.int64) & 0xffffffff).sum()) for x in segs if x.shape[0])]
+                    asc = all(bool((x[1:, 0].to(torch.int64) >= x[:-1, 0].to(torch.int64)).all()) for x in segs if x.shape[0] > 1)
+                    own = bool(torch.equal(allc[:args.npat].cpu(), torch.from_numpy(gpu_counts.view(np.int32))))
+                    gather_parity = "ok (%d counts, %d tuples: sums of counts / tuple count / pattern ids match all ranks; segments ascending)" % (
+                        gnpat, got3[1]) if (got3 == [int(v) for v in loc.tolist()] and asc and own) else "MISMATCH %r vs %r" % (got3, loc.tolist())
+            for r in live:
+                r.free()
+            del allc, segs, g
 
     def allmax(x):
         if world == 1:
@@ -433,8 +498,13 @@ def main():
     e2e_ms_max = allmax(e2e_ms)
     e2o_ms_max = allmax(e2o_ms)
     gather_ms_max = allmax(gather_ms) if world > 1 else 0.0
+    e2f_ms_max = allmax(e2f_ms)
     total_pat = args.npat * world * args.steps
-    value = total_pat / (dev_ms_max * 1e-3)
+    value_no_gather = total_pat / (dev_ms_max * 1e-3)
+    # N > 1: the north star's collective is part of the job, so it is part of `value` (shard search + NCCL gather of counts and
+    # tuples on rank 0, overlapped); N = 1 has nothing to gather
+    value = total_pat / (gather_ms_max * 1e-3) if world > 1 else value_no_gather
+    step_ms_max = gather_ms_max if world > 1 else dev_ms_max
     e2e_val = total_pat / (e2e_ms_max * 1e-3)
 
     out = None
@@ -457,15 +527,21 @@ def main():
         achieved = alg_bytes / (lf_ms_step * 1e-3) / 1e9 if lf_ms_step > 0 else 0.0
         traffic, traffic_src = ncu_traffic(args, int(info.seed_k))
         canon = 8.0 * (args.npat + st_c["I"]) + 128.0 * st_c["S"] + 16.0 * st_c["E"] + 64.0 * st_c["L"] + 28.0 * st_c["O"]
+        # random-access ceilings measured in this run (csrc/gather_bench.cu: the kernel's own 64-byte fetch, one thread per block):
+        # best of a few independent-access configurations over a buffer of the size of the Occ array, over 4 GiB, and for the
+        # kernel's own mix (block fetches over the Occ-sized buffer + 18 % 16-byte gathers over 5 GB)
+        occ_bytes = max(64 << 20, int(info.n // 128 + 1) * 64)
         try:
-            g_big = eb.gather_bench(local_rank, 4 << 30, 1 << 26, 3)
-            g_idx = eb.gather_bench(local_rank, max(64 << 20, int(info.n // 128 + 1) * 64), 1 << 26, 3)
+            g_idx = max(eb.gather_bench_cfg(local_rank, occ_bytes, 1 << 27, 2, 64, ilp, 0, False)[0] for ilp in (4, 8))
+            g_big = max(eb.gather_bench_cfg(local_rank, 4 << 30, 1 << 27, 2, 64, ilp, 0, False)[0] for ilp in (4, 8))
+            g_mix = max(eb.gather_bench_cfg(local_rank, occ_bytes, 1 << 27, 2, 64, ilp, 0, False, 5 << 30, 0.18)[0] for ilp in (4, 8))
+            g_dep = eb.gather_bench_cfg(local_rank, occ_bytes, 1 << 27, 2, 64, 1, 0, True)[0]
         except Exception as e:      # noqa
             log("gather bench failed:", e)
-            g_big = g_idx = None
+            g_big = g_idx = g_mix = g_dep = None
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": step_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u32", "data": "synthetic",
             "config": {"workload": workload_name(args), "index_rows": info.n, "strings": info.n_text, "segments": info.n_seg,
                        "patterns_per_gpu": args.npat, "pattern_len": args.plen, "seed_k": info.seed_k, "locate": "sa-table",
@@ -474,12 +550,20 @@ def main():
                        "l2": "inputs larger than L2 (patterns %.0f MB + index %.2f GB per step; no flush needed)" % (data.nbytes / 1e6, info.device_bytes / 1e9)},
             "wall_ms_per_step": wall_ms_max / args.steps,
             "occurrences_per_step": int(nocc),
+            "value_no_gather": value_no_gather, "ms_per_step_no_gather": dev_ms_max / args.steps,
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": e2e_ms_max / args.steps, "call": "edsbwt_search_into_fixed (pinned host buffers, equal-length batch)",
+                    "ms_per_step": e2e_ms_max / args.steps,
+                    "call": "edsbwt_search_into_packed (pinned host buffers; patterns as 2-bit words, 8 B per length-32 pattern, + the invalid bitmap)",
+                    "host_packer": {"call": "edsbwt_pack_patterns", "ms": pack_ms, "threads": os.cpu_count() or 1, "patterns_per_s": args.npat / (pack_ms * 1e-3),
+                                    "note": "bytes -> words on the host, once per pattern set; not inside the e2e region"},
+                    "ascii_fixed": {"value": total_pat / (e2f_ms_max * 1e-3), "ms_per_step": e2f_ms_max / args.steps, "h2d_bytes_per_step": int(data.nbytes),
+                                    "call": "edsbwt_search_into_fixed (raw pattern bytes, packed on the device)"},
                     "with_offset_array": {"value": total_pat / (e2o_ms_max * 1e-3), "ms_per_step": e2o_ms_max / args.steps,
                                           "h2d_bytes_per_step": int(data.nbytes + off.nbytes), "call": "edsbwt_search_into"}},
-            "gather": ({"value": total_pat / (gather_ms_max * 1e-3), "unit": UNIT, "ms_per_step": gather_ms_max / args.steps,
-                        "bytes_per_step": int(gather_bytes), "what": "shard search + ncclAllGather(counts) + gather-v(tuples) to rank 0, device-timed"}
+            "gather": ({"in_value": True, "chunks_per_shard": nchunks, "ms_per_step": gather_ms_max / args.steps, "nvlink_bytes_per_step": int(gather_bytes),
+                        "GBps_into_rank0": gather_bytes / (gather_ms_max / args.steps * 1e-3) / 1e9 if gather_ms_max else None,
+                        "gather_parity": gather_parity,
+                        "what": "per chunk: search, then ncclSend/ncclRecv of its counts and tuples to rank 0 while the next chunk is searched; CUDA events, max over ranks"}
                        if world > 1 else None),
             "gpu_launches": int(launches),
             "clocks": clocks,
@@ -487,8 +571,9 @@ def main():
                          "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "alg_bytes_per_step": alg_bytes, "kernel_ms_per_step": lf_ms_step,
                          "kernel_share_of_step": lf_ms_step / (dev_ms / args.steps) if dev_ms else None,
-                         "gather64_gbs_4GiB": g_big, "gather64_gbs_index_sized": g_idx,
-                         "frac_of_gather64": (achieved / g_big) if g_big else None,
+                         "gather64_gbs_4GiB": g_big, "gather64_gbs_occ_sized": g_idx, "gather_mix_gbs": g_mix, "gather64_dependent_chains_gbs": g_dep,
+                         "frac_of_gather64": (achieved / g_idx) if g_idx else None, "frac_of_gather_mix": (achieved / g_mix) if g_mix else None,
+                         "gather_note": "independent 64-byte block fetches, best of ilp 4 / 8 at full occupancy; the Occ array is what the kernel gathers from",
                          "locate_kernel_ms_per_step": loc_ms / args.steps, "overflow_patterns": st_a["overflow_patterns"], "occ_blocks": occ_blocks,
                          "lf_intervals": st_a["lf_intervals"], "link_records": st_a["E"], "seed_intervals_read": st_a["I"],
                          "canonical_model": {"k": 12, "I": st_c["I"], "S": st_c["S"], "E": st_c["E"], "L": st_c["L"], "O": st_c["O"],
@@ -521,6 +606,111 @@ def main():
         if not args.keep and not os.environ.get("EDSBWT_BENCH_KEEP"):
             pass        # index files stay in the work dir for the reference arm that the driver runs next
     return 0
+
+
+def device_patterns(col, npat, m, seed, device):
+    """synth.sample_patterns' 90/10 recipe on the GPU (data preparation only, torch): 100 M patterns of length 256 are 25.6 GB,
+    too slow to sample with numpy on the host.  -> uint8 tensor [npat, m] on `device`"""
+    import torch
+    g = torch.Generator(device=device); g.manual_seed(seed)
+    rng = np.random.default_rng(seed)
+    acgt = torch.tensor(list(b"ACGT"), dtype=torch.uint8, device=device)
+    out = torch.empty((npat, m), dtype=torch.uint8, device=device)
+    n_path = int(round(npat * 0.9))
+    ar = torch.arange(m, device=device, dtype=torch.int64)
+    H = torch.from_numpy(synth_haplotype(col, rng)).to(device)
+    step = max(1, (1 << 28) // m)
+    for b in range(0, npat, step):
+        e = min(npat, b + step)
+        np_rows = max(0, min(e, n_path) - b)
+        if np_rows:
+            st = torch.randint(0, H.numel() - m + 1, (np_rows,), generator=g, device=device)
+            out[b:b + np_rows] = H[st[:, None] + ar[None, :]]
+        if e - b > np_rows:
+            out[b + np_rows:e] = acgt[torch.randint(0, 4, (e - b - np_rows, m), generator=g, device=device)]
+    n_mut = int(round(n_path * 0.1))                      # one substitution in a tenth of the path patterns
+    who = torch.randperm(n_path, generator=g, device=device)[:n_mut]
+    where = torch.randint(0, m, (n_mut,), generator=g, device=device)
+    cur = out[who, where]
+    code = torch.searchsorted(acgt.to(torch.int16), cur.to(torch.int16))
+    out[who, where] = acgt[(code + torch.randint(1, 4, (n_mut,), generator=g, device=device)) % 4]
+    return out[torch.randperm(npat, generator=g, device=device)].contiguous()
+
+
+def synth_haplotype(col, rng):
+    import importlib
+    return importlib.import_module("eds-bwt_b200.synth").haplotype(col, rng)
+
+
+def cfg5_leg(args, eb, synth, idx, info, base, rank, world, local_rank):
+    """BASELINE.json config 5: --total patterns of length --len on the cfg4 index, sharded over the ranks (strong scaling),
+    count-only and locate; a sample of this rank's patterns is checked against the unmodified reference (counts and rows)."""
+    import torch
+    import torch.distributed as dist
+    m = args.plen
+    lo, hi = (args.total * rank) // world, (args.total * (rank + 1)) // world
+    npat = hi - lo
+    col = synth.chromosome_eds(args.mbp, seed=4)
+    t0 = time.time()
+    d_pats = device_patterns(col, npat, m, 55 + m + 1000 * rank, torch.device("cuda", local_rank))
+    del col
+    d_off = torch.arange(npat + 1, dtype=torch.int64, device=d_pats.device) * m
+    torch.cuda.synchronize()
+    log("rank %d: %d patterns of length %d sampled on the device in %.1fs" % (rank, npat, m, time.time() - t0))
+    # locate: a length-8 key has thousands of occurrences -- locate only as many patterns as give ~2^27 tuples (cap stated in the line)
+    r = idx.search_device(d_pats.data_ptr(), d_off.data_ptr(), min(npat, 1 << 16), min(npat, 1 << 16) * m, m, locate=False)
+    c0, _ = r.fetch(); r.free()
+    per = max(1.0, float(c0.astype(np.float64).mean()))
+    nloc = int(min(npat, max(1024, (1 << 27) / per)))
+
+    def run(n, locate):
+        ms = 0.0; nocc = 0
+        for it in range(max(args.warmup, 3) + args.steps):
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            rr = idx.search_device(d_pats.data_ptr(), d_off.data_ptr(), n, n * m, m, locate=locate)
+            st = idx.last_stats(); nocc = rr.nocc; rr.free()
+            if it >= max(args.warmup, 3):
+                ms += st["total_ms"]
+        return ms, nocc
+
+    ms_count, _ = run(npat, False)
+    ms_loc, nocc = run(nloc, True)
+
+    def allmax(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    ms_count, ms_loc = allmax(ms_count), allmax(ms_loc)
+    # oracle sample on rank 0: the reference binary on the first patterns of the shard
+    parity = None
+    if rank == 0 and not args.no_cpu:
+        nref = 256 if m >= 16 else 64
+        rr = idx.search_device(d_pats.data_ptr(), d_off.data_ptr(), nref, nref * m, m, locate=True)
+        gc, go = rr.fetch(); rr.free()
+        cb = cpu_reference_run(base, d_pats[:nref].cpu().numpy(), args.cpu_seconds, min(os.cpu_count() or 1, nref), "cfg5 m=%d" % m, per=max(1, nref // min(os.cpu_count() or 1, nref)))
+        n = cb["n"]
+        gsub = go[go["pat"] < n]
+        rows = sorted(zip(gsub["pat"].tolist(), gsub["str"].tolist(), gsub["seg"].tolist(), gsub["idx_in_seg"].tolist(), gsub["off"].tolist()))
+        ok = cb["counts"] == gc[:n].tolist() and sorted(cb["rows"]) == rows
+        parity = {"kind": cb["kind"], "patterns": n, "rows": len(cb["rows"]), "result": "counts+rows ok" if ok else "MISMATCH",
+                  "reference_patterns_per_s": cb["value"], "cores": cb["cores"]}
+    if rank != 0:
+        return None
+    tot_count = args.total * args.steps
+    return {"metric": "patterns/sec located (len %d)" % m, "value": (nloc * world * args.steps) / (ms_loc * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_loc / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic (patterns sampled on the device, 90/10 recipe, seed 55+m)",
+            "config": {"workload": "cfg5: %d patterns of length %d on the synthetic %g Mbp EDS, sharded over %d GPU(s)" % (args.total, m, args.mbp, world),
+                       "patterns_per_gpu": npat, "pattern_len": m, "seed_k": info.seed_k,
+                       "located_patterns_per_gpu": nloc, "locate_cap": "locate leg runs on the first %d patterns of each shard (~2^27 tuples; a length-%d key has %.1f occurrences on average)" % (nloc, m, per)},
+            "count_only": {"value": tot_count / (ms_count * 1e-3), "unit": UNIT, "ms_per_step": ms_count / args.steps, "patterns_per_step": args.total},
+            "locate": {"value": (nloc * world * args.steps) / (ms_loc * 1e-3), "unit": UNIT, "ms_per_step": ms_loc / args.steps, "occurrences_per_step_rank0": int(nocc)},
+            "parity_vs_reference": parity}
 
 
 def reference_arm(args, eb, synth, workdir, base, done_flag):

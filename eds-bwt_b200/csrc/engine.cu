@@ -997,7 +997,11 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             if (items) {
                 // ---- the hot kernel (items.cu): patterns as 2-bit words, persistent warps, lanes refilled
                 PackedPats pp{};
+                // short patterns that arrived as bytes are packed by the kernel itself, lane by lane, as they are taken (a caller's
+                // max_len is only a hint: a longer pattern found on the device goes to the second pass)
+                const bool fused_pack = !caller_words && ((fixed_len && fixed_len <= 32) || (!fixed_len && max_len && max_len <= 32));
                 if (caller_words) { pp.words = caller_words; pp.invalid = hint->d_invalid; pp.poff = nullptr; }
+                else if (fused_pack) { pp.words = nullptr; pp.invalid = nullptr; pp.poff = fixed_len ? nullptr : d_off; pp.bytes = d_bytes; pp.lut = ix.lut.p; pp.fixed_base = hint ? hint->fixed_base : 0ull; }
                 else {
                     const uint64_t nwords = fixed_len ? (uint64_t)npat * stride : (total_bytes >> 5) + npat + 1;
                     if (nwords > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 pattern words in one batch; split the batch");

@@ -294,11 +294,14 @@ constexpr uint32_t PLIST_INLINE = 0x40000000u;
 // word w holds characters [max(0, m - 32(w+1)), m - 32w), the last of them in bits 62..63, code = rank of the letter in
 // the index alphabet.  invalid: bit q & 31 of word q >> 5 is set when pattern q holds a byte outside the alphabet (such a
 // pattern has 0 occurrences); nullptr = all valid.
+// words == nullptr: the item kernel packs each pattern itself when it takes it (bytes + lut; patterns of at most 32 characters --
+// a longer one is handed to the second pass), which saves the separate packing pass over a batch of short patterns.
 struct PackedPats {
     const uint64_t* words;
     const uint64_t* poff;
     const uint32_t* invalid;
     uint32_t fixed_len, stride;
+    const uint8_t* bytes; const uint8_t* lut; uint64_t fixed_base;
 };
 
 struct StatsDev { unsigned long long I, S, E, L, O, lf_intervals, occ_blocks, overflow; };

@@ -108,12 +108,7 @@ constexpr int ITEM_WARPS = FUSED_THREADS / 32;
 
 }  // namespace
 
-// PERIOD: everything that is not an Occ item -- results of finished patterns, refill, link records, further seed intervals,
-// pattern words, the Dol' ++ F' splice -- runs only in every PERIOD-th sweep.  Those branches are taken by one or two lanes at a
-// time, so run in every sweep they cost the warp more instructions than the Occ items themselves (ncu: 45 % of all
-// instructions at 1.3 - 2 active lanes); batched, a lane waits PERIOD/2 sweeps on average for its turn and the branches run a
-// PERIOD-th as often.
-template <bool STATS, int MINB, int PERIOD>
+template <bool STATS, int MINB>
 __global__ void __launch_bounds__(FUSED_THREADS, MINB)
 search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant__ SeedView sv, uint32_t k, const __grid_constant__ PackedPats pp,
                     uint32_t npat, uint32_t cap, FusedOut out, uint32_t* __restrict__ work, StatsDev* __restrict__ st, uint32_t kc) {
@@ -127,8 +122,10 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     __shared__ uint64_t s_pw[ITEM_WARPS][32];         // word 0 of the pattern
     __shared__ uint4 s_ps[ITEM_WARPS][32];            // seed entry {first interval lo, hi, offset of the entry, number of intervals}
     __shared__ uint2 s_pm[ITEM_WARPS][32];            // {length (0: nothing to search), first word}
+    __shared__ uint8_t s_lut[256];                    // byte -> code, only when the kernel packs the patterns itself
     if (threadIdx.x < 17) { s_off[threadIdx.x] = sv.off[threadIdx.x]; s_iv[threadIdx.x] = sv.iv[threadIdx.x]; s_cnt[threadIdx.x] = sv.cnt[threadIdx.x]; }
     if (threadIdx.x < 5) s_Cl[threadIdx.x] = ix.Cl[threadIdx.x];
+    if (!pp.words) for (int i = threadIdx.x; i < 256; i += FUSED_THREADS) s_lut[i] = pp.lut[i];
     __syncthreads();
 #define SLOT(i) s_list[(i) * FUSED_THREADS + threadIdx.x]
 #define LIST(j) SLOT(j)
@@ -147,16 +144,20 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         pool_n = npat - base < 32u ? npat - base : 32u;
         if (lane < pool_n) {
             const uint32_t pq = base + lane;
-            uint32_t mm, pwb;
+            uint32_t mm, pwb; uint64_t pbase;
             if (pp.poff) {
                 const uint64_t a = __ldg(pp.poff + pq), len64 = __ldg(pp.poff + pq + 1) - a;
                 mm = len64 > 0xffffffffull ? 0u : (uint32_t)len64;
-                pwb = (uint32_t)(((a - __ldg(pp.poff)) >> 5) + pq);
-            } else { mm = pp.fixed_len; pwb = pq * pp.stride; }
+                pwb = (uint32_t)(((a - __ldg(pp.poff)) >> 5) + pq); pbase = a;
+            } else { mm = pp.fixed_len; pwb = pq * pp.stride; pbase = pp.fixed_base + (uint64_t)pq * pp.fixed_len; }
             if (pp.invalid && ((__ldg(pp.invalid + (pq >> 5)) >> (pq & 31u)) & 1u)) mm = 0;
             uint64_t w = 0; uint4 se = make_uint4(1u, 0u, 0u, 0u);
-            if (mm) {
-                w = __ldg(pp.words + pwb);
+            if (mm && !pp.words) {                                // the batch arrived as bytes: pack this pattern here
+                if (mm > 32) { se.w = 0xffffffffu; pwb = 0xffffffffu; }           // too long for one word: frontier "too large" -> second pass, which reads bytes
+                else { uint64_t cw; if (fetch_codes(pp.bytes + pbase, mm, s_lut, cw)) w = cw << (2 * (32 - mm)); else mm = 0; }
+            }
+            if (mm && pwb != 0xffffffffu) {
+                if (pp.words) w = __ldg(pp.words + pwb);
                 // seed entry of the last min(m, k) characters: the frontier after that many backward steps
                 const uint32_t L0 = mm < k ? mm : k, key = (uint32_t)(w >> (64 - 2 * L0));
                 if (sv.first && L0 == sv.first_level) se = __ldg(sv.first + key);
@@ -189,10 +190,9 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     };
 
     grab_pool();
-    for (uint32_t sweep = 0;; ++sweep) {
-        const bool gate = PERIOD == 1 || sweep % PERIOD == 0;
+    for (;;) {
         // ---------------- finished lanes write their results; they and the idle lanes take the next patterns of the pool
-        const uint32_t needy = gate ? __ballot_sync(FULL, kind <= K_FIN) : 0u;
+        const uint32_t needy = __ballot_sync(FULL, kind <= K_FIN);
         if (needy) {
             if (kind == K_FIN) {
                 // count + the final interval list.  One interval (nearly every found pattern) travels inside the plist entry
@@ -278,18 +278,16 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         if (occ_item) {
             const uint4* p = ix.occ + (size_t)(SLOT(slot).x >> 7) * 4;
             ld256(p, B); ld256(p + 2, B + 8);
-        } else if (gate) {
-            if (kind == K_LINK) ld64(ix.link_rec + cur, B);
-            else if (kind == K_SEEDIV) ld64(s_iv[m < k ? m : k] + cur, B);
-            else if (kind == K_WORD) ld64(pp.words + wb + (spos >> 5), B);
-        }
+        } else if (kind == K_LINK) ld64(ix.link_rec + cur, B);
+        else if (kind == K_SEEDIV) ld64(s_iv[m < k ? m : k] + cur, B);
+        else if (kind == K_WORD) ld64(pp.words + wb + (spos >> 5), B);
 
         // ---------------- consume
         if (occ_item) {
+            const uint2 iv = SLOT(slot);
             const int c = (int)((win >> (2 * (31 - (spos & 31u)))) & 3u);
             const uint32_t x0 = (c & 1) ? 0u : 0xffffffffu, x1 = (c & 2) ? 0u : 0xffffffffu;
             uint32_t rca, rcb, rda, rdb, nblk;
-            const uint2 iv = SLOT(slot);
             lf_range_loaded(*reinterpret_cast<Blk*>(B), ix.occ, iv.x, iv.y + 1, c, x0, x1, rca, rcb, rda, rdb, nblk);
             if (STATS) { tLF += 1; tBlk += nblk; if (spos >= kc) { tS += 1; tE += rdb - rda; } }
             // one code path for both passes: the output list grows from the bottom (F', length nout) or from the top (Dol', length aux)
@@ -312,8 +310,6 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
                     else { nF = nout; ++spos; next_step(); }
                 }
             }
-        } else if (!gate) {
-            // every other kind waits for its sweep
         } else if (kind == K_LINK) {
             // pile-0 range [l, h] of the preceding segment(s) -> sorted, merged Dol set at the top of the column
             uint32_t l = B[0], h = B[1];
@@ -350,7 +346,7 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
             win = ((uint64_t)B[1] << 32) | B[0];
             kind = K_OCCF; j = 0; nout = 0; ndol = 0;
         }
-        if (gate && kind == K_ENDP2) {                            // F <- Dol' ++ F'   (aux = length of Dol')
+        if (kind == K_ENDP2) {                                    // F <- Dol' ++ F'   (aux = length of Dol')
             if (aux) {
                 if (nout + 2 * aux > cap) { ovf = true; kind = K_FIN; }
                 else {
@@ -378,10 +374,10 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
 }
 
 namespace {
-template <bool STATS, int MINB, int PERIOD>
+template <bool STATS, int MINB>
 void launch_items_instance(size_t smem, cudaStream_t s, const IndexView& ix, const SeedView& sv, uint32_t k, const PackedPats& pp, uint32_t npat,
                            uint32_t cap, const FusedOut& out, uint32_t* work, StatsDev* st, uint32_t kc) {
-    auto kern = search_items_kernel<STATS, MINB, PERIOD>;
+    auto kern = search_items_kernel<STATS, MINB>;
     CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
     int dev = 0, sms = 148, per_sm = 1;
     CUDA_OK(cudaGetDevice(&dev));
@@ -401,14 +397,10 @@ void launch_items_search(const IndexView& ix, const SeedView& sv, uint32_t k, co
     if (npat == 0) return;
     if (npat > 0xff000000u) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 - 2^24 patterns in one search call; split the batch");
     const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
-    const char* e = getenv("EDSBWT_ITEMS_PERIOD");      // A/B of the batching period (profiles/scripts/r02_items_ab.py)
-    const int period = e ? atoi(e) : 1;
-    if (st) launch_items_instance<true, 8, 1>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
-    else if (cap > 16) launch_items_instance<false, 8, 1>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
-    else if (period == 2) launch_items_instance<false, 10, 2>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
-    else if (period == 3) launch_items_instance<false, 10, 3>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
-    else if (period == 4) launch_items_instance<false, 10, 4>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
-    else launch_items_instance<false, 10, 1>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    // 10 CTAs / SM at 48 registers (A/B against 8, 9 and 12: profiles/r02_items_ab.txt); long frontiers and counting runs: 8
+    if (st) launch_items_instance<true, 8>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    else if (cap > 16) launch_items_instance<false, 8>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
+    else launch_items_instance<false, 10>(smem, s, ix, sv, k, pp, npat, cap, out, work, st, kc);
     CUDA_OK(cudaGetLastError());
 }
 

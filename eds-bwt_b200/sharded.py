@@ -76,6 +76,79 @@ def gather_results(counts_local, occ_local, npat, group=None, dst=0):
     return counts, occ, tots
 
 
+def chunk_range(b, e, nchunks, c):
+    """Chunk c of the shard [b, e): [b + (e-b)*c/C, b + (e-b)*(c+1)/C)."""
+    n = e - b
+    return b + (n * c) // nchunks, b + (n * (c + 1)) // nchunks
+
+
+class ChunkedGather:
+    """Gather to rank `dst` of a shard that is searched in chunks: the counts and tuples of chunk c are put on the wire as soon
+    as the chunk has been searched and travel while chunk c + 1 is searched, so the collective hides behind the kernels
+    (round 1 gathered the whole shard after the search: the 7-to-1 incast doubled the step at N = 8).
+
+        g = ChunkedGather(npat, nchunks, group, size_group, dst)
+        for c in range(nchunks): g.post(c, counts_c, occ_c)       # right after chunk c has been searched
+        counts, segments = g.finish()                               # rank dst: counts of the whole batch + tuple segments
+
+    Sizes are exchanged chunk by chunk over `size_group` (a group of its own -- gloo on the host in bench.py -- so that a size
+    exchange never queues behind the bulk transfers on the NCCL stream).  The tuples of (rank r, chunk c) land in their own
+    buffer; the list of segments in (r, c) order is the batch in ascending pattern order, without a final copy.  Everything is
+    issued as non-blocking isend / irecv (ncclSend / ncclRecv in one group per chunk); nothing waits before finish()."""
+
+    def __init__(self, npat, nchunks, group=None, size_group=None, dst=0):
+        self.npat, self.nchunks, self.group, self.dst = npat, nchunks, group, dst
+        self.size_group = size_group if size_group is not None else group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.works, self.keep, self.segs, self.counts = [], [], {}, None
+        self.bytes_moved = 0
+
+    def post(self, c, counts_c, occ_c):
+        dev = counts_c.device
+        k = int(occ_c.shape[0])
+        # sizes of this chunk on every rank (8 bytes each; host tensors when size_group is a gloo group)
+        sdev = torch.device("cpu") if dist.get_backend(self.size_group) == "gloo" else dev
+        tots = torch.empty(self.world, dtype=torch.int64, device=sdev)
+        dist.all_gather_into_tensor(tots, torch.tensor([k], dtype=torch.int64, device=sdev), group=self.size_group)
+        tots = [int(x) for x in tots.tolist()]
+        ops = []
+        if self.rank == self.dst:
+            if self.counts is None:
+                self.counts = torch.empty(self.npat, dtype=torch.int32, device=dev)
+            for r in range(self.world):
+                b, e = shard_range(self.npat, self.world, r)
+                cb, ce = chunk_range(b, e, self.nchunks, c)
+                if r == self.dst:
+                    self.counts[cb:ce] = counts_c
+                    self.segs[(r, c)] = occ_c
+                    continue
+                if ce > cb:
+                    ops.append(dist.P2POp(dist.irecv, self.counts[cb:ce], _global_rank(r, self.group), self.group))
+                seg = torch.empty((tots[r], 5), dtype=torch.int32, device=dev)
+                self.segs[(r, c)] = seg
+                if tots[r]:
+                    ops.append(dist.P2POp(dist.irecv, seg, _global_rank(r, self.group), self.group))
+                self.bytes_moved += 4 * (ce - cb) + 20 * tots[r]
+        else:
+            if counts_c.numel():
+                ops.append(dist.P2POp(dist.isend, counts_c, _global_rank(self.dst, self.group), self.group))
+            if k:
+                ops.append(dist.P2POp(dist.isend, occ_c, _global_rank(self.dst, self.group), self.group))
+        self.keep.append((counts_c, occ_c))
+        if ops:
+            self.works += dist.batch_isend_irecv(ops)
+        return tots
+
+    def finish(self):
+        for w in self.works:
+            w.wait()
+        self.works, self.keep = [], []
+        if self.rank != self.dst:
+            return None, None
+        order = [(r, c) for r in range(self.world) for c in range(self.nchunks)]
+        return self.counts, [self.segs[k] for k in order]
+
+
 def _global_rank(r, group):
     return r if group is None else dist.get_global_rank(group, r)
 

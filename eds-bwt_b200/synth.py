@@ -140,6 +140,47 @@ def sarscov2_like_eds(n_sites=5000, seed=3):
     return from_segments(segs, "sarscov2_like_%d_seed%d" % (n_sites, seed))
 
 
+def repetitive_eds(unit_len=30000, copies=100, divergence=0.001, site_every=100, seed=7):
+    """A repetitive EDS for the MOVE_EDSBWTSearch variant: the non-degenerate backbone is `copies` copies
+    of one random unit of unit_len bases, every copy carrying its own substitutions at rate `divergence` (a pangenome laid end
+    to end / segmental duplications -- what makes the eBWT run-compressible; an EDS built from an alignment of near-identical
+    genomes is NOT repetitive by itself, the alignment has already collapsed the copies), cut by one variant site every
+    ~site_every bases with 2-4 alleles of length 1 (75 %), 0 (15 %, at most one) or 2-6 (10 %), like cfg3/cfg4."""
+    rng = np.random.default_rng(seed)
+    unit = ACGT[rng.integers(0, 4, unit_len, dtype=np.uint8)]
+    backbone = np.tile(unit, copies)
+    nmut = int(round(len(backbone) * divergence))
+    if nmut:
+        where = rng.integers(0, len(backbone), nmut)
+        backbone[where] = ACGT[(np.searchsorted(ACGT, backbone[where]) + rng.integers(1, 4, nmut)) % 4]
+    total = len(backbone)
+    nd = max(1, total // site_every - 1)
+    cuts = np.sort(rng.choice(np.arange(1, total), nd, replace=False))
+    nondeg_len = np.diff(np.concatenate([[0], cuts, [total]])).astype(np.int64)
+    v = rng.integers(2, 5, nd).astype(np.int64)
+    ns = int(v.sum())
+    u = rng.random(ns)
+    allele_len = np.where(u < 0.75, 1, np.where(u < 0.90, 0, rng.integers(2, 7, ns))).astype(np.int64)
+    z = (allele_len == 0).astype(np.int64)
+    cz = np.cumsum(z)
+    site_start = np.zeros(nd, dtype=np.int64)
+    np.cumsum(v[:-1], out=site_start[1:])
+    before_site = np.repeat(cz[site_start] - z[site_start], v)
+    allele_len[(z == 1) & (cz - before_site > 1)] = 1
+    lens, seg_first = _interleave(nondeg_len, v, allele_len)
+    off = np.zeros(len(lens) + 1, dtype=np.uint64)
+    np.cumsum(lens, out=off[1:].view(np.int64))
+    letters = ACGT[rng.integers(0, 4, int(off[-1]), dtype=np.uint8)]
+    # the non-degenerate strings carry the backbone, in order
+    is_nondeg = np.zeros(len(lens), dtype=bool)
+    cv = np.zeros(nd + 1, dtype=np.int64)
+    np.cumsum(v, out=cv[1:])
+    is_nondeg[np.arange(nd + 1, dtype=np.int64) + cv] = True
+    dst = np.repeat(off[:-1].astype(np.int64)[is_nondeg], lens[is_nondeg]) + (np.arange(total, dtype=np.int64) - np.repeat(np.cumsum(lens[is_nondeg]) - lens[is_nondeg], lens[is_nondeg]))
+    letters[dst] = backbone
+    return Collection(letters, off, seg_first, "repetitive_%dx%d_div%g_seed%d" % (copies, unit_len, divergence, seed))
+
+
 def haplotype(col, rng):
     """One random path through the EDS (uniform allele choice per segment) as a letter array."""
     lens = col.lens()

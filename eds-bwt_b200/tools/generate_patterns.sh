@@ -1,6 +1,7 @@
 #!/bin/bash
-# Pattern files of lengths 8/16/32/64 for every <dir>/*.msa (the reference's generate_Patterns.sh): 100 patterns each,
-# written to <out>/patterns_<name>.msa_<length>.txt.
+# Pattern files of lengths 8/16/32/64 for every <dir>/*.msa: 100 patterns each, written to
+# <out>/patterns_<name>.msa_<length>.txt.  This RESTATES the reference's generate_Patterns.sh:1-18 (same two loops, same file
+# naming -- the naming is the contract the authors' launch scripts rely on); only the extraction tool it calls is ours.
 set -e
 DATASET_DIR=$1
 OUTPUT_DIR=$2

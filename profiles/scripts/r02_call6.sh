@@ -1,0 +1,4 @@
+mkdir -p gpurun_out
+timeout 900 python profiles/scripts/r02_items_ab.py --variants step,items:1,items:2,items:3,items:4 > gpurun_out/r02_items_ab6.jsonl 2> gpurun_out/r02_items_ab6.err; echo "ab rc=$?"; cat gpurun_out/r02_items_ab6.jsonl | cut -c1-230; tail -3 gpurun_out/r02_items_ab6.err
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:search_items_kernel -s 4 -c 1 -f -o gpurun_out/items_r02_e python profiles/scripts/r02_items_ab.py --variants items:3 --steps 3 > gpurun_out/r02_ncu_items6.log 2>&1; tail -2 gpurun_out/r02_ncu_items6.log
+EDSBWT_ITEMS_PERIOD=3 timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "golden or random_vs_port or packed" > gpurun_out/r02_pytest_gpu_6.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/r02_pytest_gpu_6.log

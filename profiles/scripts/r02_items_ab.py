@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Round 2 A/B of the hot kernel at cfg4 (one process, index files and patterns built once):
-the item kernel (items.cu) at several batching periods (items:<period>) against the round-1 step-loop kernel (fused.cu).
+the item kernel (items.cu), packing fused into the kernel or as a separate pass, against the round-1 step-loop kernel (fused.cu).
 
     python profiles/scripts/r02_items_ab.py [--mbp 250] [--npat 10000000] [--steps 10] [--variants items:10,items:8,step]
 Prints one JSON line per variant (device-resident step, CUDA events on the library's stream)."""
@@ -23,7 +23,7 @@ def main():
     ap.add_argument("--npat", type=int, default=10000000)
     ap.add_argument("--len", type=int, default=32, dest="plen")
     ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--variants", default="step,items:1,items:2,items:3,items:4")
+    ap.add_argument("--variants", default="step,items,items-pack")
     ap.add_argument("--caps", default="13")
     args = ap.parse_args()
     import torch
@@ -45,16 +45,15 @@ def main():
     for var in args.variants.split(","):
         for cap in [int(c) for c in args.caps.split(",")]:
             name, _, minb = var.partition(":")
-            os.environ.pop("EDSBWT_ITEMS_PERIOD", None)
-            if minb:
-                os.environ["EDSBWT_ITEMS_PERIOD"] = minb
-            engine = eb.ENGINE_FUSED if name == "items" else eb.ENGINE_FUSED_STEP
+            # items: the kernel packs each short pattern as it takes it; items-pack: separate packing pass first (max_len unknown)
+            engine = eb.ENGINE_FUSED if name.startswith("items") else eb.ENGINE_FUSED_STEP
+            max_len = 0 if name == "items-pack" else args.plen
             t0 = time.time()
             with eb.Index(base, device=0, verify=False, engine=engine, fused_cap=cap) as idx:
                 t_open = time.time() - t0
                 tot = kern = loc = 0.0
                 for it in range(3 + args.steps):
-                    r = idx.search_device(d_data.data_ptr(), d_off.data_ptr(), args.npat, int(data.size), args.plen, locate=True)
+                    r = idx.search_device(d_data.data_ptr(), d_off.data_ptr(), args.npat, int(data.size), max_len, locate=True)
                     st = idx.last_stats()
                     if it == 0:
                         counts, occ = r.fetch()

@@ -343,8 +343,16 @@ def test_occurrence_overflow_halves_the_chunk(eb, tmp_path, monkeypatch):
         assert r.fetch()[0].tolist() == c_ref.tolist()
         r.free()
         with pytest.raises(eb.EdsbwtError) as ei:                    # total_bytes must cover the offsets' span
-            idx.search_device(d_data.data_ptr(), d_off.data_ptr(), len(pats), 64, 16, locate=False)
+            idx.search_device(d_data.data_ptr(), d_off.data_ptr(), len(pats), 64, 0, locate=False)     # (longest pattern unknown: the batch is packed by the separate pass, which sizes its buffer from total_bytes)
         assert ei.value.code == -5
+        # a wrong max_len hint is harmless: patterns longer than the hint are found on the device and take the second pass
+        longp = E.sample_patterns(rng, segs, 300, [5, 40, 70])
+        ld, lo = eb.pack_patterns(longp)
+        c_long, _ = idx.search(longp, locate=False)
+        dl = torch.from_numpy(ld).cuda(); dlo = torch.from_numpy(lo.view(np.int64)).cuda()
+        r = idx.search_device(dl.data_ptr(), dlo.data_ptr(), len(longp), int(ld.size), 8, locate=False)
+        assert r.fetch()[0].tolist() == c_long.tolist()
+        r.free()
 
 
 # ---- count-only trace (RECOVERBW=0 stderr line) and the two drop-in executables ---------------------------------

@@ -94,6 +94,70 @@ def test_gather_over_gloo(world, npat, oracle_built, tmp_path):
             assert occ is None
 
 
+def _gloo_chunk_worker(rank, world, port, base, pf, npat, nchunks, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        sh = importlib.import_module("eds-bwt_b200.sharded")
+        from oracle import run as R
+        size_group = dist.new_group(backend="gloo")
+        b, e = sh.shard_range(npat, world, rank)
+        lines = open(pf, "rb").read().split(b"\n")[:npat]
+        g = sh.ChunkedGather(npat, nchunks, None, size_group, dst=0)
+        for c in range(nchunks):
+            cb, ce = sh.chunk_range(b, e, nchunks, c)
+            counts, rows = [], []
+            if ce > cb:                                     # local "search" of the chunk: the oracle on its lines
+                spf = "%s.%d.%d" % (pf, rank, c)
+                with open(spf, "wb") as f:
+                    f.write(b"\n".join(lines[cb:ce]))
+                counts, rows, _ = R.run_port(base, spf, locate=True)
+            c_loc = torch.tensor(np.array(counts, dtype=np.uint32).view(np.int32), dtype=torch.int32)
+            o = np.array([(p - 1 + cb, w, s, j, r) for (p, w, s, j, r) in rows], dtype=np.uint32).reshape(-1, 5)
+            g.post(c, c_loc, torch.from_numpy(o.view(np.int32).copy()))
+        allc, segs = g.finish()
+        if rank == 0:
+            occ = np.concatenate([s_.numpy().view(np.uint32).reshape(-1, 5) for s_ in segs]) if segs else np.zeros((0, 5), np.uint32)
+            q.put((rank, allc.numpy().view(np.uint32).tolist(), occ.tolist(), len(segs)))
+        else:
+            q.put((rank, None, None, 0))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,npat,nchunks", [(2, 41, 3), (3, 10, 4), (2, 5, 1)])
+def test_chunked_gather_over_gloo(world, npat, nchunks, oracle_built, tmp_path):
+    """the chunk-overlapped gather of bench.py's multi-GPU leg: counts of the whole batch + tuple segments in ascending
+    pattern order on rank 0 (chunks smaller than the world, empty chunks included)"""
+    rng = np.random.default_rng(50 + world)
+    segs = E.random_eds(rng, n_seg=200, max_var=4, max_len=5, p_empty=0.2)
+    ix = E.build_index(segs)
+    base = str(tmp_path / "idx")
+    E.write_index(ix, base)
+    pats = E.sample_patterns(rng, segs, npat, [2, 3, 5, 8, 12])
+    pf = str(tmp_path / "p.txt")
+    E.write_patterns(pf, pats)
+    c_ref, rows_ref, _ = oracle_built.run_port(base, pf, locate=True)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_chunk_worker, args=(r, world, port, base, pf, npat, nchunks, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, counts, occ, nseg in got:
+        if rank == 0:
+            assert counts == c_ref and nseg == world * nchunks
+            rows = [(p + 1, w, s, j, r) for (p, w, s, j, r) in occ]
+            assert sorted(rows) == sorted(rows_ref)
+            assert [r[0] for r in rows] == sorted(r[0] for r in rows)      # ascending pattern order straight from the segments
+
+
 # ---- GPU: the real thing over NCCL -------------------------------------------------------------------------------------
 def _nccl_worker(rank, world, port, base, pats, q):
     sys.path.insert(0, ROOT)
