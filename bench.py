@@ -68,7 +68,8 @@ def parse_args():
                          "length --len sharded over the GPUs (strong scaling), count-only and locate, on the same 250 Mbp index")
     ap.add_argument("--total", type=int, default=100000000, help="cfg5: patterns of the whole job")
     ap.add_argument("--gather-chunks", type=int, default=4, help="chunks per shard of the multi-GPU leg (gather of chunk c overlaps the search of chunk c+1)")
-    ap.add_argument("--engine", default="items", choices=["items", "step"], help="hot kernel: items.cu (default) or the round-1 step-loop kernel (A/B)")
+    ap.add_argument("--engine", default="auto", choices=["auto", "items", "step"],
+                    help="first-pass kernel: auto = the library default (step-loop kernel for bytes, item kernel for 2-bit words), or force one (A/B)")
     return ap.parse_args()
 
 
@@ -144,22 +145,23 @@ def workload_name(args):
         args.mbp, args.npat, args.plen)
 
 
-NCU_CAPTURE = "profiles/r02_items_ncu_full.txt"      # ncu --set full of search_items_kernel at the default workload (cfg4, k = 14)
+NCU_CAPTURE = {"fused_search_kernel": "profiles/r02_fused_ncu_full.txt",       # ncu --set full captures at the default workload (cfg4, k = 14)
+               "search_items_kernel": "profiles/r02_items_ncu_full.txt"}
 
 
-def ncu_traffic(args, seed_k):
+def ncu_traffic(args, seed_k, kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed ncu capture of
     this same command (only valid for the default workload the capture was taken on)."""
-    if args.mbp != 250 or args.npat != 10000000 or args.plen != 32 or seed_k != 14 or args.engine != "items":
+    if args.mbp != 250 or args.npat != 10000000 or args.plen != 32 or seed_k != 14 or kernel not in NCU_CAPTURE:
         return None, None
     try:
         tot = 0.0
-        with open(os.path.join(ROOT, NCU_CAPTURE)) as f:
+        with open(os.path.join(ROOT, NCU_CAPTURE[kernel])) as f:
             for line in f:
                 t = line.split()
                 if len(t) >= 3 and t[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                     tot += float(t[1]) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[t[2]]
-        return (tot or None), NCU_CAPTURE
+        return (tot or None), NCU_CAPTURE[kernel]
     except Exception:
         return None, None
 
@@ -316,7 +318,7 @@ def main():
         dist.barrier()
     t0 = time.time()
     idx = eb.Index(base, device=local_rank, seed_k=args.seed_k, verify=False, fused_cap=args.fused_cap, fused_cap2=args.fused_cap2,
-                   engine=eb.ENGINE_FUSED if args.engine == "items" else eb.ENGINE_FUSED_STEP)
+                   engine={"auto": eb.ENGINE_FUSED, "items": eb.ENGINE_ITEMS, "step": eb.ENGINE_FUSED_STEP}[args.engine])
     info = idx.info()
     log("rank %d: index open in %.1fs: n=%d nText=%d nSeg=%d seed_k=%d seed_intervals=%d device_bytes=%.2f GB" % (
         rank, time.time() - t0, info.n, info.n_text, info.n_seg, info.seed_k, info.seed_intervals, info.device_bytes / 1e9))
@@ -383,6 +385,20 @@ def main():
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop()
+
+    # ---- the other first-pass kernel on the same device-resident batch (the item kernel takes 2-bit words: for bytes that adds the
+    #      packing pass, which is why the library gives bytes to the step-loop kernel): reported next to the roofline of `value`
+    other = None
+    if args.engine == "auto":
+        idx.set_engine(eb.ENGINE_ITEMS)
+        o_ms = o_k = 0.0
+        for it in range(2 + args.steps):
+            st, _ = step_device()
+            if it >= 2:
+                o_ms += st["total_ms"]; o_k += st["search_kernel_ms"]
+        idx.set_engine(eb.ENGINE_FUSED)
+        other = {"kernel": "search_items_kernel", "ms_per_step": o_ms / args.steps, "kernel_ms_per_step": o_k / args.steps,
+                 "value": args.npat / (o_ms / args.steps * 1e-3), "note": "engine = EDSBWT_ENGINE_ITEMS on the same batch of bytes: 2-bit packing pass + item kernel + locate"}
 
     # ---- e2e: host buffers through edsbwt_search_into (pinned caller buffers; H2D + D2H inside the timed region)
     p_data = eb.pinned_empty(data.size, np.uint8); p_data[:] = data
@@ -521,11 +537,12 @@ def main():
         # record + 8 B per seed interval read + the pattern itself: 2-bit words and one 8-byte offset per pattern for the item
         # kernel, the raw bytes and two offsets for the step-loop kernel.  Canonical SURVEY model printed next to it.
         occ_blocks = st_a["occ_blocks"]
+        kernel = "search_items_kernel" if args.engine == "items" else "fused_search_kernel"
         pat_bytes = (8.0 * ((args.plen + 31) // 32) + 8.0) if args.engine == "items" else (args.plen + 16.0)
         alg_bytes = 64.0 * occ_blocks + 8.0 * st_a["E"] + pat_bytes * args.npat + 8.0 * st_a["I"]
         lf_ms_step = lf_ms / args.steps
         achieved = alg_bytes / (lf_ms_step * 1e-3) / 1e9 if lf_ms_step > 0 else 0.0
-        traffic, traffic_src = ncu_traffic(args, int(info.seed_k))
+        traffic, traffic_src = ncu_traffic(args, int(info.seed_k), kernel)
         canon = 8.0 * (args.npat + st_c["I"]) + 128.0 * st_c["S"] + 16.0 * st_c["E"] + 64.0 * st_c["L"] + 28.0 * st_c["O"]
         # random-access ceilings measured in this run (csrc/gather_bench.cu: the kernel's own 64-byte fetch, one thread per block):
         # best of a few independent-access configurations over a buffer of the size of the Occ array, over 4 GiB, and for the
@@ -545,7 +562,7 @@ def main():
             "dtype": "u32", "data": "synthetic",
             "config": {"workload": workload_name(args), "index_rows": info.n, "strings": info.n_text, "segments": info.n_seg,
                        "patterns_per_gpu": args.npat, "pattern_len": args.plen, "seed_k": info.seed_k, "locate": "sa-table",
-                       "search_kernel": "search_items_kernel (persistent warps, lane refill)" if args.engine == "items" else "fused_search_kernel (round-1 step loop)",
+                       "search_kernel": "search_items_kernel (persistent warps, lane refill)" if args.engine == "items" else "fused_search_kernel (step loop, one thread per pattern; the library's choice for batches of bytes)",
                        "parallelism": "patterns sharded x%d, index replicated" % world,
                        "l2": "inputs larger than L2 (patterns %.0f MB + index %.2f GB per step; no flush needed)" % (data.nbytes / 1e6, info.device_bytes / 1e9)},
             "wall_ms_per_step": wall_ms_max / args.steps,
@@ -567,10 +584,12 @@ def main():
                        if world > 1 else None),
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "search_items_kernel" if args.engine == "items" else "fused_search_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "alg_bytes_per_step": alg_bytes, "kernel_ms_per_step": lf_ms_step,
                          "kernel_share_of_step": lf_ms_step / (dev_ms / args.steps) if dev_ms else None,
+                         "item_kernel_on_the_same_batch": (dict(other, achieved=(64.0 * occ_blocks + 8.0 * st_a["E"] + 16.0 * args.npat + 8.0 * st_a["I"]) / (other["kernel_ms_per_step"] * 1e-3) / 1e9,
+                                                                 frac=(64.0 * occ_blocks + 8.0 * st_a["E"] + 16.0 * args.npat + 8.0 * st_a["I"]) / (other["kernel_ms_per_step"] * 1e-3) / 1e9 / peak) if other else None),
                          "gather64_gbs_4GiB": g_big, "gather64_gbs_occ_sized": g_idx, "gather_mix_gbs": g_mix, "gather64_dependent_chains_gbs": g_dep,
                          "frac_of_gather64": (achieved / g_idx) if g_idx else None, "frac_of_gather_mix": (achieved / g_mix) if g_mix else None,
                          "gather_note": "independent 64-byte block fetches, best of ilp 4 / 8 at full occupancy; the Occ array is what the kernel gathers from",

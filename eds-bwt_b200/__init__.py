@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(HERE, "libedsbwt_cuda.so")
 
 LOCATE_SA, LOCATE_WALK = 0, 1
 LF_RANK, LF_MOVE = 0, 1
-ENGINE_FUSED, ENGINE_LEVELSYNC, ENGINE_FUSED_STEP = 0, 1, 2      # _FUSED: item kernel (default); _FUSED_STEP: the round-1 step-loop kernel as first pass
+ENGINE_FUSED, ENGINE_LEVELSYNC, ENGINE_FUSED_STEP, ENGINE_ITEMS = 0, 1, 2, 3      # _FUSED: step-loop kernel for bytes, item kernel for 2-bit words
 ROWS_GROUPED, ROWS_REFERENCE = 0, 1
 
 OCC_DTYPE = np.dtype([("pat", "<u4"), ("str", "<u4"), ("seg", "<u4"), ("idx_in_seg", "<u4"), ("off", "<u4")])
@@ -30,7 +30,7 @@ EXPORTS = [
     "edsbwt_search_into_packed", "edsbwt_pack_patterns", "edsbwt_pack_patterns_alphabet",
     "edsbwt_multi_open", "edsbwt_multi_info", "edsbwt_multi_handle", "edsbwt_multi_close", "edsbwt_search_multi",
     "edsbwt_multi_result_info", "edsbwt_multi_result_device_ptrs", "edsbwt_multi_result_fetch", "edsbwt_multi_result_write_csv",
-    "edsbwt_multi_result_free", "edsbwt_gather_bench_cfg", "edsbwt_move_table_save",
+    "edsbwt_multi_result_free", "edsbwt_gather_bench_cfg", "edsbwt_move_table_save", "edsbwt_set_engine",
 ]
 
 
@@ -135,6 +135,7 @@ def lib():
         L.edsbwt_set_stats.argtypes = [C.c_void_p, C.c_int, C.c_uint32]
         L.edsbwt_write_csv.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_int]
         L.edsbwt_set_row_order.argtypes = [C.c_void_p, C.c_int]
+        L.edsbwt_set_engine.argtypes = [C.c_void_p, C.c_int]
         L.edsbwt_result_write_csv.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_uint64)]
         L.edsbwt_search_to_csv.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_char_p, C.POINTER(C.c_uint64)]
         L.edsbwt_string_check.argtypes = [C.c_char_p, C.c_char_p]
@@ -282,6 +283,9 @@ class Index:
                                                int(locate), lf_variant, counts.ctypes.data, occ.ctypes.data if occ is not None else None,
                                                len(occ) if occ is not None else 0, C.byref(nocc)))
         return nocc.value
+
+    def set_engine(self, engine):
+        _check(lib().edsbwt_set_engine(self._h, engine))
 
     def set_row_order(self, reference=True):
         """ROWS_REFERENCE: tuples of a pattern in the reference's csv order."""

@@ -357,6 +357,13 @@ int edsbwt_search_trace(edsbwt_index* idx, const uint8_t* pat_bytes, const uint6
     });
 }
 
+int edsbwt_set_engine(edsbwt_index* idx, int engine) {
+    if (!idx || engine < EDSBWT_ENGINE_FUSED || engine > EDSBWT_ENGINE_ITEMS) return EDSBWT_E_ARG;
+    std::lock_guard<std::mutex> lock(idx->ix.mu);
+    idx->ix.engine = engine;
+    return EDSBWT_OK;
+}
+
 int edsbwt_set_row_order(edsbwt_index* idx, int order) {
     if (!idx || (order != EDSBWT_ROWS_GROUPED && order != EDSBWT_ROWS_REFERENCE)) return EDSBWT_E_ARG;
     idx->ix.row_order = order;

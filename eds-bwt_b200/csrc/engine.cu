@@ -735,7 +735,7 @@ void init_index_runtime(Index& ix, const edsbwt_open_opts& o) {
     CUDA_OK(cudaMallocHost(&ws.h_pin, 256));
     CUDA_OK(cudaEventCreate(&ws.ev0)); CUDA_OK(cudaEventCreate(&ws.ev1)); CUDA_OK(cudaEventCreate(&ws.evk0)); CUDA_OK(cudaEventCreate(&ws.evk1));
     CUDA_OK(cudaEventCreate(&ws.evf0)); CUDA_OK(cudaEventCreate(&ws.evf1)); CUDA_OK(cudaEventCreate(&ws.evl0)); CUDA_OK(cudaEventCreate(&ws.evl1));
-    ix.engine = (o.engine == EDSBWT_ENGINE_LEVELSYNC || o.engine == EDSBWT_ENGINE_FUSED_STEP) ? o.engine : EDSBWT_ENGINE_FUSED;
+    ix.engine = (o.engine == EDSBWT_ENGINE_LEVELSYNC || o.engine == EDSBWT_ENGINE_FUSED_STEP || o.engine == EDSBWT_ENGINE_ITEMS) ? o.engine : EDSBWT_ENGINE_FUSED;
     ix.fused_cap = o.fused_cap > 0 ? (uint32_t)o.fused_cap : 13u;       // 13 slots: 12 CTAs/SM (40 registers) and >= 60 KB of L1 left (A/B: profiles/r01_ab_keep_sort_sizes.txt)
     ix.fused_cap_auto = o.fused_cap <= 0;
     if (ix.fused_cap < 4) ix.fused_cap = 4;
@@ -983,7 +983,8 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
         uint32_t nstage = 0;
         const uint32_t* ids = nullptr;
         if (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move) {
-            const bool items = !move && ix.engine == EDSBWT_ENGINE_FUSED;
+            // first pass: the item kernel for batches that are (or are asked to be) 2-bit words, the step-loop kernel for bytes
+            const bool items = !move && (ix.engine == EDSBWT_ENGINE_ITEMS || (ix.engine == EDSBWT_ENGINE_FUSED && caller_words));
             size_t want = (size_t)npat * 2 + (1u << 16);
             if (want > 0xfffffff0ull) want = 0xfffffff0ull;
             ws.staging.ensure(want); ws.ovf_ids.ensure(npat);
@@ -997,11 +998,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             if (items) {
                 // ---- the hot kernel (items.cu): patterns as 2-bit words, persistent warps, lanes refilled
                 PackedPats pp{};
-                // short patterns that arrived as bytes are packed by the kernel itself, lane by lane, as they are taken (a caller's
-                // max_len is only a hint: a longer pattern found on the device goes to the second pass)
-                const bool fused_pack = !caller_words && ((fixed_len && fixed_len <= 32) || (!fixed_len && max_len && max_len <= 32));
                 if (caller_words) { pp.words = caller_words; pp.invalid = hint->d_invalid; pp.poff = nullptr; }
-                else if (fused_pack) { pp.words = nullptr; pp.invalid = nullptr; pp.poff = fixed_len ? nullptr : d_off; pp.bytes = d_bytes; pp.lut = ix.lut.p; pp.fixed_base = hint ? hint->fixed_base : 0ull; }
                 else {
                     const uint64_t nwords = fixed_len ? (uint64_t)npat * stride : (total_bytes >> 5) + npat + 1;
                     if (nwords > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "more than 2^32 pattern words in one batch; split the batch");

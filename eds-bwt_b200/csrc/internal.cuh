@@ -208,31 +208,35 @@ __device__ __forceinline__ uint32_t low_mask(int below) {
 // when the range holds no '#' and lies inside one block).  After the seed lookup nearly every range is one or a few rows
 // inside ONE block: that case is a single sweep over the four 32-row words (letter mask computed once, '#' ranks only
 // when a '#' is present).  nblk = Occ blocks fetched (1 or 2).
+// [a, b) inside ONE block (already in registers): a single sweep over the four 32-row words
+__device__ __forceinline__ void lf_same_block(const Blk& B, uint32_t a, uint32_t b, int c, uint32_t x0, uint32_t x1,
+                                              uint32_t& rca, uint32_t& rcb, uint32_t& rda, uint32_t& rdb) {
+    const int offA = (int)(a & 127u), offB = (int)(b & 127u);
+    uint32_t r = (c & 2) ? ((c & 1) ? B.w[12] : B.w[8]) : ((c & 1) ? B.w[4] : B.w[0]);      // selects, not branches: lanes hold different letters
+    uint32_t in = 0, hin = 0;
+    #pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint32_t lmA = low_mask(offA - 32 * j), dm = low_mask(offB - 32 * j) & ~lmA;
+        const uint32_t M = (B.w[4 * j + 1] ^ x0) & (B.w[4 * j + 2] ^ x1) & ~B.w[4 * j + 3];
+        r += __popc(M & lmA); in += __popc(M & dm); hin |= B.w[4 * j + 3] & dm;
+    }
+    rca = r; rcb = r + in; rda = rdb = 0;
+    if (hin) {
+        uint32_t ka = 0, kin = 0;
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t lmA = low_mask(offA - 32 * j), dm = low_mask(offB - 32 * j) & ~lmA;
+            ka += __popc(B.w[4 * j + 3] & lmA); kin += __popc(B.w[4 * j + 3] & dm);
+        }
+        rda = (a & ~127u) - letters_before(B) + ka; rdb = rda + kin;
+    }
+}
 // B = block a >> 7, already in registers (the item kernel issues the fetch one stage before it consumes it)
 __device__ __forceinline__ void lf_range_loaded(Blk& B, const uint4* __restrict__ occ, uint32_t a, uint32_t b, int c, uint32_t x0, uint32_t x1,
                                                 uint32_t& rca, uint32_t& rcb, uint32_t& rda, uint32_t& rdb, uint32_t& nblk) {
     const uint32_t blkA = a >> 7, blkB = b >> 7;
-    if (blkA == blkB) {
-        const int offA = (int)(a & 127u), offB = (int)(b & 127u);
-        uint32_t r = (c & 2) ? ((c & 1) ? B.w[12] : B.w[8]) : ((c & 1) ? B.w[4] : B.w[0]);      // selects, not branches: lanes hold different letters
-        uint32_t in = 0, hin = 0;
-        #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const uint32_t lmA = low_mask(offA - 32 * j), dm = low_mask(offB - 32 * j) & ~lmA;
-            const uint32_t M = (B.w[4 * j + 1] ^ x0) & (B.w[4 * j + 2] ^ x1) & ~B.w[4 * j + 3];
-            r += __popc(M & lmA); in += __popc(M & dm); hin |= B.w[4 * j + 3] & dm;
-        }
-        rca = r; rcb = r + in; rda = rdb = 0; nblk = 1;
-        if (hin) {
-            uint32_t ka = 0, kin = 0;
-            #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const uint32_t lmA = low_mask(offA - 32 * j), dm = low_mask(offB - 32 * j) & ~lmA;
-                ka += __popc(B.w[4 * j + 3] & lmA); kin += __popc(B.w[4 * j + 3] & dm);
-            }
-            rda = blkA * OCC_ROWS - letters_before(B) + ka; rdb = rda + kin;
-        }
-    } else {
+    if (blkA == blkB) { lf_same_block(B, a, b, c, x0, x1, rca, rcb, rda, rdb); nblk = 1; }
+    else {
         uint32_t ka, kb;
         rank_in_blk(B, a & 127u, c, x0, x1, rca, ka);
         rda = blkA * OCC_ROWS - letters_before(B) + ka;
@@ -294,14 +298,11 @@ constexpr uint32_t PLIST_INLINE = 0x40000000u;
 // word w holds characters [max(0, m - 32(w+1)), m - 32w), the last of them in bits 62..63, code = rank of the letter in
 // the index alphabet.  invalid: bit q & 31 of word q >> 5 is set when pattern q holds a byte outside the alphabet (such a
 // pattern has 0 occurrences); nullptr = all valid.
-// words == nullptr: the item kernel packs each pattern itself when it takes it (bytes + lut; patterns of at most 32 characters --
-// a longer one is handed to the second pass), which saves the separate packing pass over a batch of short patterns.
 struct PackedPats {
     const uint64_t* words;
     const uint64_t* poff;
     const uint32_t* invalid;
     uint32_t fixed_len, stride;
-    const uint8_t* bytes; const uint8_t* lut; uint64_t fixed_base;
 };
 
 struct StatsDev { unsigned long long I, S, E, L, O, lf_intervals, occ_blocks, overflow; };

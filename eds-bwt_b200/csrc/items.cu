@@ -122,10 +122,8 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     __shared__ uint64_t s_pw[ITEM_WARPS][32];         // word 0 of the pattern
     __shared__ uint4 s_ps[ITEM_WARPS][32];            // seed entry {first interval lo, hi, offset of the entry, number of intervals}
     __shared__ uint2 s_pm[ITEM_WARPS][32];            // {length (0: nothing to search), first word}
-    __shared__ uint8_t s_lut[256];                    // byte -> code, only when the kernel packs the patterns itself
     if (threadIdx.x < 17) { s_off[threadIdx.x] = sv.off[threadIdx.x]; s_iv[threadIdx.x] = sv.iv[threadIdx.x]; s_cnt[threadIdx.x] = sv.cnt[threadIdx.x]; }
     if (threadIdx.x < 5) s_Cl[threadIdx.x] = ix.Cl[threadIdx.x];
-    if (!pp.words) for (int i = threadIdx.x; i < 256; i += FUSED_THREADS) s_lut[i] = pp.lut[i];
     __syncthreads();
 #define SLOT(i) s_list[(i) * FUSED_THREADS + threadIdx.x]
 #define LIST(j) SLOT(j)
@@ -144,20 +142,16 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         pool_n = npat - base < 32u ? npat - base : 32u;
         if (lane < pool_n) {
             const uint32_t pq = base + lane;
-            uint32_t mm, pwb; uint64_t pbase;
+            uint32_t mm, pwb;
             if (pp.poff) {
                 const uint64_t a = __ldg(pp.poff + pq), len64 = __ldg(pp.poff + pq + 1) - a;
                 mm = len64 > 0xffffffffull ? 0u : (uint32_t)len64;
-                pwb = (uint32_t)(((a - __ldg(pp.poff)) >> 5) + pq); pbase = a;
-            } else { mm = pp.fixed_len; pwb = pq * pp.stride; pbase = pp.fixed_base + (uint64_t)pq * pp.fixed_len; }
+                pwb = (uint32_t)(((a - __ldg(pp.poff)) >> 5) + pq);
+            } else { mm = pp.fixed_len; pwb = pq * pp.stride; }
             if (pp.invalid && ((__ldg(pp.invalid + (pq >> 5)) >> (pq & 31u)) & 1u)) mm = 0;
             uint64_t w = 0; uint4 se = make_uint4(1u, 0u, 0u, 0u);
-            if (mm && !pp.words) {                                // the batch arrived as bytes: pack this pattern here
-                if (mm > 32) { se.w = 0xffffffffu; pwb = 0xffffffffu; }           // too long for one word: frontier "too large" -> second pass, which reads bytes
-                else { uint64_t cw; if (fetch_codes(pp.bytes + pbase, mm, s_lut, cw)) w = cw << (2 * (32 - mm)); else mm = 0; }
-            }
-            if (mm && pwb != 0xffffffffu) {
-                if (pp.words) w = __ldg(pp.words + pwb);
+            if (mm) {
+                w = __ldg(pp.words + pwb);
                 // seed entry of the last min(m, k) characters: the frontier after that many backward steps
                 const uint32_t L0 = mm < k ? mm : k, key = (uint32_t)(w >> (64 - 2 * L0));
                 if (sv.first && L0 == sv.first_level) se = __ldg(sv.first + key);
@@ -272,15 +266,23 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         }
 
         // ---------------- issue: one fetch per lane, all in flight together
-        uint32_t B[16];
+        // The 8-byte fetches go out FIRST, ahead of the Occ fetches.  The loads are volatile asm and keep their order, so placed
+        // here the compiler cannot sink them into the branches that consume them; placed after the Occ loads it did (same
+        // condition, no dependence), the warp then ran "Occ lanes: load, wait, consume" and only afterwards "link lanes: load,
+        // wait, consume", and the latencies added up: three long-scoreboard stall sites instead of one in ncu, kernel 12 %
+        // slower (profiles/r02_items_ab.txt).
+        // (Registers of their own for the 8 bytes: sharing B, the Occ load behind them waited for them to land -- a
+        // write-after-write hazard on the scoreboard, 10 % of all stall samples.)
+        uint32_t B[16], S[2];
+        if (kind == K_LINK) ld64(ix.link_rec + cur, S);
+        else if (kind == K_SEEDIV) ld64(s_iv[m < k ? m : k] + cur, S);
+        else if (kind == K_WORD) ld64(pp.words + wb + (spos >> 5), S);
         const bool occ_item = kind == K_OCCF || kind == K_OCCD;
         const uint32_t slot = kind == K_OCCD ? cap - 1 - j : j;  // pass 2 walks the Dol set at the top of the column
         if (occ_item) {
             const uint4* p = ix.occ + (size_t)(SLOT(slot).x >> 7) * 4;
             ld256(p, B); ld256(p + 2, B + 8);
-        } else if (kind == K_LINK) ld64(ix.link_rec + cur, B);
-        else if (kind == K_SEEDIV) ld64(s_iv[m < k ? m : k] + cur, B);
-        else if (kind == K_WORD) ld64(pp.words + wb + (spos >> 5), B);
+        }
 
         // ---------------- consume
         if (occ_item) {
@@ -312,7 +314,7 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
             }
         } else if (kind == K_LINK) {
             // pile-0 range [l, h] of the preceding segment(s) -> sorted, merged Dol set at the top of the column
-            uint32_t l = B[0], h = B[1];
+            uint32_t l = S[0], h = S[1];
             if (l <= h) {                                         // l > h: string of the first segment, no predecessor
                 uint32_t i = 0;
                 while (i < ndol && DOL(i).y + 1 < l) ++i;
@@ -339,11 +341,11 @@ search_items_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
                 }
             }
         } else if (kind == K_SEEDIV) {
-            LIST(j) = make_uint2(B[0], B[1]);
+            LIST(j) = make_uint2(S[0], S[1]);
             ++cur;
             if (++j == nF) next_step();
         } else if (kind == K_WORD) {
-            win = ((uint64_t)B[1] << 32) | B[0];
+            win = ((uint64_t)S[1] << 32) | S[0];
             kind = K_OCCF; j = 0; nout = 0; ndol = 0;
         }
         if (kind == K_ENDP2) {                                    // F <- Dol' ++ F'   (aux = length of Dol')

@@ -64,12 +64,15 @@ typedef struct {
 
 #define EDSBWT_LOCATE_SA    0   /* row -> (string, offset) table in HBM: one gather per occurrence           */
 #define EDSBWT_LOCATE_WALK  1   /* LF-walk each row to its string start (the reference's a9/a13 arithmetic)  */
-#define EDSBWT_ENGINE_FUSED      0  /* whole backward search in one launch: persistent warps, one frontier item per lane */
-                                    /* per sweep, finished lanes refilled with new patterns (items.cu); frontiers that   */
-                                    /* outgrow it go to the step-loop kernel with 192 slots and then to:                 */
-#define EDSBWT_ENGINE_LEVELSYNC  1  /* level-synchronous interval-parallel engine (also builds the seed table)           */
-#define EDSBWT_ENGINE_FUSED_STEP 2  /* round-1 hot kernel as the first pass: one thread per pattern, per-thread step loop */
-                                    /* (fused.cu; kept as the second pass of ENGINE_FUSED and for A/B measurements)       */
+#define EDSBWT_ENGINE_FUSED      0  /* default: whole backward search in one launch, the kernel chosen by the form the batch    */
+                                    /* arrives in -- bytes: the step-loop kernel (one thread per pattern, fused.cu); 2-bit     */
+                                    /* words: the item kernel (items.cu).  The two are within 3 % of each other at cfg4; the    */
+                                    /* item kernel would need a packing pass over bytes first.  Frontiers that  */
+                                    /* outgrow the first pass go to the step-loop kernel with 192 slots and then to:            */
+#define EDSBWT_ENGINE_LEVELSYNC  1  /* level-synchronous interval-parallel engine (also builds the seed table)                  */
+#define EDSBWT_ENGINE_FUSED_STEP 2  /* step-loop kernel as the first pass for every batch (2-bit words are unpacked on the device) */
+#define EDSBWT_ENGINE_ITEMS      3  /* item kernel as the first pass for every batch: persistent warps, one frontier item per   */
+                                    /* lane per sweep, finished lanes refilled from a warp-wide pool (bytes are packed first)   */
 #define EDSBWT_LF_RANK      0   /* EDSBWTsearch:      LF by blocked rank                                      */
 #define EDSBWT_LF_MOVE      1   /* MOVE_EDSBWTSearch: LF by move table                                        */
 
@@ -82,7 +85,7 @@ typedef struct {
     int32_t  locate_mode;       /* EDSBWT_LOCATE_SA / _WALK                                                   */
     int32_t  verify;            /* 1 = cross-check _bv_<p>.aux (rrr) and tableOcc against the pile bytes      */
     int32_t  build_move;        /* 1 = also build the move table (EDSBWT_LF_MOVE searches)                    */
-    int32_t  engine;            /* EDSBWT_ENGINE_FUSED (default) / _LEVELSYNC / _FUSED_STEP                   */
+    int32_t  engine;            /* EDSBWT_ENGINE_FUSED (default) / _LEVELSYNC / _FUSED_STEP / _ITEMS          */
     int32_t  fused_cap;         /* frontier slots per pattern of the first pass (0 = default 13)                */
     int32_t  fused_cap2;        /* slots of the second pass over the patterns that outgrew the first (0 = 192) */
     int32_t  move_a;            /* balancing parameter a of the move table (build_MLF's <a>); 0 = default 8 (or whatever a valid <base>_MLF.edsbwt was built with) */
@@ -210,6 +213,7 @@ int  edsbwt_multi_result_fetch(const edsbwt_multi_result* r, uint32_t* counts, e
 int  edsbwt_multi_result_write_csv(edsbwt_multi* m, const edsbwt_multi_result* r, const char* path, int move, int append, uint64_t* bytes);
 void edsbwt_multi_result_free(edsbwt_multi_result* r);
 
+int  edsbwt_set_engine(edsbwt_index* idx, int engine);      /* EDSBWT_ENGINE_* for every later search on this handle (A/B measurements) */
 int  edsbwt_last_stats(const edsbwt_index* idx, edsbwt_stats* st);
 int  edsbwt_set_stats(edsbwt_index* idx, int collect_counters, uint32_t canonical_k);
 

@@ -46,7 +46,7 @@ def main():
         for cap in [int(c) for c in args.caps.split(",")]:
             name, _, minb = var.partition(":")
             # items: the kernel packs each short pattern as it takes it; items-pack: separate packing pass first (max_len unknown)
-            engine = eb.ENGINE_FUSED if name.startswith("items") else eb.ENGINE_FUSED_STEP
+            engine = eb.ENGINE_ITEMS if name.startswith("items") else eb.ENGINE_FUSED_STEP
             max_len = 0 if name == "items-pack" else args.plen
             t0 = time.time()
             with eb.Index(base, device=0, verify=False, engine=engine, fused_cap=cap) as idx:

@@ -43,7 +43,7 @@ def test_image_cache_roundtrip_and_staleness(eb, tmp_path):
         c, o = idx.search(pats, locate=True)
         assert c.tolist() == c_ref.tolist() and eb.occ_rows(o) == eb.occ_rows(o_ref)
     assert os.path.getsize(base + ".edsbwt") > 4096
-    for engine in (eb.ENGINE_FUSED, eb.ENGINE_LEVELSYNC, eb.ENGINE_FUSED_STEP):
+    for engine in (eb.ENGINE_FUSED, eb.ENGINE_LEVELSYNC, eb.ENGINE_ITEMS):
         with eb.Index(base, cache=True, engine=engine) as idx:         # later opens: everything comes from the file
             info = idx.info()
             assert info.from_file == 3 and info.seed_k == k and info.move_intervals > 0

@@ -91,7 +91,7 @@ def test_cfg5_lengths_against_reference(eb, synth, oracle_built, tmp_path, m, nr
     pats = synth.sample_patterns(col, npat, m, seed=55 + m)
     data, off = synth.pack_fixed(pats)
     c_ref, rows_ref, kind = _reference_rows(oracle_built, base, pats[:nref], tmp_path, "m%d" % m)
-    for engine in (eb.ENGINE_FUSED, eb.ENGINE_FUSED_STEP):
+    for engine in (eb.ENGINE_FUSED, eb.ENGINE_ITEMS):
         with eb.Index(base, engine=engine) as idx:
             counts, occ = idx.search((data, off), locate=True)
             assert counts[:nref].tolist() == c_ref, (m, engine)
