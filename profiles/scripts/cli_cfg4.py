@@ -34,7 +34,10 @@ lines.tofile(pf)
 del lines, pats
 exe = os.path.join(ROOT, "eds-bwt_b200", "EDSBWTsearch")
 out = {}
-for mode, env in (("locate (RECOVERBW=1)", {}), ("count-only (RECOVERBW=0)", {"EDSBWT_RECOVERBW": "0"})):
+# round 2: also with the persisted HBM image (EDSBWT_CACHE=1: the first run builds and writes <index>.edsbwt, the second reads it)
+for mode, env in (("locate (RECOVERBW=1)", {}), ("count-only (RECOVERBW=0)", {"EDSBWT_RECOVERBW": "0"}),
+                  ("locate, EDSBWT_CACHE=1, first run (writes the image)", {"EDSBWT_CACHE": "1"}),
+                  ("locate, EDSBWT_CACHE=1, second run (reads the image)", {"EDSBWT_CACHE": "1"})):
     e = dict(os.environ); e.update(env); e["EDSBWT_VERIFY"] = "0"
     t0 = time.time()
     with open(os.devnull, "w") as null, open(os.path.join(work, "cli_stdout.txt"), "w") as so:
@@ -45,10 +48,14 @@ for mode, env in (("locate (RECOVERBW=1)", {}), ("count-only (RECOVERBW=0)", {"E
     csv = pf + "output.csv"
     rec = {"mode": mode, "rc": r.returncode, "wall_s": round(wall, 2), "bs_took_s": float(m.group(1)) if m else None,
            "patterns": npat, "found_lines": True, "stderr_tail": r.stderr[-120:]}
-    if os.path.exists(csv) and not env:
+    if os.path.exists(base + ".edsbwt"):
+        rec["image_file_bytes"] = os.path.getsize(base + ".edsbwt")
+    if os.path.exists(csv) and "EDSBWT_RECOVERBW" not in env:
         rec["csv_bytes"] = os.path.getsize(csv)
         with open(csv) as f:
             rec["csv_head"] = [f.readline().rstrip("\n"), f.readline().rstrip("\n")]
         os.remove(csv)
     out[mode] = rec
+if os.path.exists(base + ".edsbwt"):
+    os.remove(base + ".edsbwt")
 print(json.dumps({"config": "cfg4, %d length-32 patterns, eds-bwt_b200/EDSBWTsearch <index> <patterns file>" % npat, **out}))
