@@ -67,6 +67,7 @@ def parse_args():
                     help="cfg4: the headline (10 M length-32 patterns per GPU, weak scaling); cfg5: BASELINE.json's length sweep -- --total patterns of "
                          "length --len sharded over the GPUs (strong scaling), count-only and locate, on the same 250 Mbp index")
     ap.add_argument("--total", type=int, default=100000000, help="cfg5: patterns of the whole job")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="multi-GPU result gather: peer copies into an IPC arena on rank 0 (default) or ncclSend/ncclRecv")
     ap.add_argument("--gather-chunks", type=int, default=4, help="chunks per shard of the multi-GPU leg (gather of chunk c overlaps the search of chunk c+1)")
     ap.add_argument("--engine", default="auto", choices=["auto", "items", "step"],
                     help="first-pass kernel: auto = the library default (step-loop kernel for bytes, item kernel for 2-bit words), or force one (A/B)")
@@ -458,15 +459,19 @@ def main():
         # per chunk) as soon as it is searched and travel while chunk c + 1 is searched.  Timed on the device: CUDA events on this
         # rank's stream from before the first chunk to after the last transfer has landed, max over ranks below.
         sh = importlib.import_module("eds-bwt_b200.sharded")
-        size_group = dist.new_group(backend="gloo")          # 8-byte size exchanges go over the host, never behind the bulk transfers
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         gnpat = args.npat * world
         d_off64 = d_off
-        csum = None
+        # default: the gather over peer memory (CUDA IPC arena on rank 0, asynchronous NVLink peer copies, no size exchange);
+        # --gather nccl: ncclSend / ncclRecv per chunk with the sizes exchanged over a gloo group (A/B)
+        peer = sh.PeerGather(eb, idx, gnpat, nchunks, int(nocc * 1.25) + 4096, None, 0) if args.gather == "peer" else None
+        size_group = dist.new_group(backend="gloo") if peer is None else None
         for it in range(2 + args.steps):
             barrier()
             ev0.record()
-            g = sh.ChunkedGather(gnpat, nchunks, None, size_group, 0)
+            if peer is not None:
+                peer.begin()
+            g = sh.ChunkedGather(gnpat, nchunks, None, size_group, 0) if peer is None else peer
             live = []
             for c in range(nchunks):
                 cb, ce = sh.chunk_range(0, args.npat, nchunks, c)
@@ -474,8 +479,11 @@ def main():
                 r = idx.search_device(d_data.data_ptr(), d_off64.data_ptr() + cb * 8, ce - cb, (ce - cb) * args.plen, args.plen,
                                       locate=True, pat_base=rank * args.npat + cb)
                 live.append(r)
-                c_loc, o_loc = sh.device_result_tensors(r, local_rank)
-                g.post(c, c_loc, o_loc)
+                if peer is not None:
+                    peer.push(c, r)
+                else:
+                    c_loc, o_loc = sh.device_result_tensors(r, local_rank)
+                    g.post(c, c_loc, o_loc)
             allc, segs = g.finish()
             ev1.record()
             torch.cuda.synchronize()
@@ -501,6 +509,9 @@ def main():
             for r in live:
                 r.free()
             del allc, segs, g
+        if peer is not None:
+            barrier()
+            peer.close()
 
     def allmax(x):
         if world == 1:
@@ -580,7 +591,8 @@ def main():
             "gather": ({"in_value": True, "chunks_per_shard": nchunks, "ms_per_step": gather_ms_max / args.steps, "nvlink_bytes_per_step": int(gather_bytes),
                         "GBps_into_rank0": gather_bytes / (gather_ms_max / args.steps * 1e-3) / 1e9 if gather_ms_max else None,
                         "gather_parity": gather_parity,
-                        "what": "per chunk: search, then ncclSend/ncclRecv of its counts and tuples to rank 0 while the next chunk is searched; CUDA events, max over ranks"}
+                        "transport": "NVLink peer copies into a CUDA-IPC arena on rank 0 (edsbwt_result_push)" if args.gather == "peer" else "ncclSend / ncclRecv, sizes over gloo",
+                        "what": "per chunk: search, then its counts and tuples go to rank 0 while the next chunk is searched; one all-gather of the chunk sizes per step; CUDA events, max over ranks"}
                        if world > 1 else None),
             "gpu_launches": int(launches),
             "clocks": clocks,

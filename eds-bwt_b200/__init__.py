@@ -31,6 +31,7 @@ EXPORTS = [
     "edsbwt_multi_open", "edsbwt_multi_info", "edsbwt_multi_handle", "edsbwt_multi_close", "edsbwt_search_multi",
     "edsbwt_multi_result_info", "edsbwt_multi_result_device_ptrs", "edsbwt_multi_result_fetch", "edsbwt_multi_result_write_csv",
     "edsbwt_multi_result_free", "edsbwt_gather_bench_cfg", "edsbwt_move_table_save", "edsbwt_set_engine",
+    "edsbwt_device_alloc", "edsbwt_device_free", "edsbwt_ipc_export", "edsbwt_ipc_open", "edsbwt_ipc_close", "edsbwt_result_push", "edsbwt_push_wait",
 ]
 
 
@@ -136,6 +137,14 @@ def lib():
         L.edsbwt_write_csv.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_int]
         L.edsbwt_set_row_order.argtypes = [C.c_void_p, C.c_int]
         L.edsbwt_set_engine.argtypes = [C.c_void_p, C.c_int]
+        L.edsbwt_device_alloc.argtypes = [C.c_int, C.c_uint64, C.POINTER(C.c_void_p)]
+        L.edsbwt_device_free.argtypes = [C.c_int, C.c_void_p]
+        L.edsbwt_device_free.restype = None
+        L.edsbwt_ipc_export.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+        L.edsbwt_ipc_open.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+        L.edsbwt_ipc_close.argtypes = [C.c_int, C.c_void_p]
+        L.edsbwt_result_push.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.edsbwt_push_wait.argtypes = [C.c_void_p]
         L.edsbwt_result_write_csv.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_uint64)]
         L.edsbwt_search_to_csv.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_char_p, C.POINTER(C.c_uint64)]
         L.edsbwt_string_check.argtypes = [C.c_char_p, C.c_char_p]
@@ -283,6 +292,13 @@ class Index:
                                                int(locate), lf_variant, counts.ctypes.data, occ.ctypes.data if occ is not None else None,
                                                len(occ) if occ is not None else 0, C.byref(nocc)))
         return nocc.value
+
+    def push(self, result, d_counts_dst, d_occ_dst):
+        """edsbwt_result_push: asynchronous copy of a DeviceResult's counts / tuples to device pointers (peer memory included)"""
+        _check(lib().edsbwt_result_push(self._h, result._h, C.c_void_p(d_counts_dst) if d_counts_dst else None, C.c_void_p(d_occ_dst) if d_occ_dst else None))
+
+    def push_wait(self):
+        _check(lib().edsbwt_push_wait(self._h))
 
     def set_engine(self, engine):
         _check(lib().edsbwt_set_engine(self._h, engine))
@@ -445,6 +461,33 @@ def pack_patterns_alphabet(alphabet, data, pat_len, nthreads=1):
     _check(lib().edsbwt_pack_patterns_alphabet(alphabet.ctypes.data, len(alphabet), data.ctypes.data, pat_len, npat, nthreads,
                                                words.ctypes.data, invalid.ctypes.data, C.byref(nbad)))
     return words, invalid, nbad.value
+
+
+def device_alloc(device, nbytes):
+    p = C.c_void_p()
+    _check(lib().edsbwt_device_alloc(device, nbytes, C.byref(p)))
+    return p.value
+
+
+def device_free(device, ptr):
+    lib().edsbwt_device_free(device, C.c_void_p(ptr))
+
+
+def ipc_export(device, ptr):
+    h = (C.c_uint8 * 64)()
+    _check(lib().edsbwt_ipc_export(device, C.c_void_p(ptr), h))
+    return bytes(h)
+
+
+def ipc_open(device, handle):
+    h = (C.c_uint8 * 64).from_buffer_copy(handle)
+    p = C.c_void_p()
+    _check(lib().edsbwt_ipc_open(device, h, C.byref(p)))
+    return p.value
+
+
+def ipc_close(device, ptr):
+    _check(lib().edsbwt_ipc_close(device, C.c_void_p(ptr)))
 
 
 def occ_rows(occ, pat_base=0):

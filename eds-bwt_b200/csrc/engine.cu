@@ -524,6 +524,7 @@ Index::~Index() {
     delete pipe;
     delete move;
     free_csv_scratch(csv);
+    if (push) cudaStreamDestroy(push);
     if (stream) cudaStreamDestroy(stream);
 }
 uint64_t Index::device_bytes() const {

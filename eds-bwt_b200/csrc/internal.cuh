@@ -380,6 +380,7 @@ struct Index {
     uint64_t seed_intervals = 0;
     Workspace* ws = nullptr;
     Pipe* pipe = nullptr;
+    cudaStream_t push = nullptr;        // peer pushes of finished results (edsbwt_result_push), created on first use
     MoveTable* move = nullptr;          // built at open (opts.build_move) or by the first EDSBWT_LF_MOVE search
     CsvScratch* csv = nullptr;          // scratch of the row-order sort and of the device csv formatter (csv.cu)
     DevBuf<uint32_t> eof_inv;           // string -> rank of its '#' row (inverse of eof_flat); built by the first ordered search

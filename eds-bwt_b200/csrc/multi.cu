@@ -359,4 +359,47 @@ int edsbwt_multi_result_write_csv(edsbwt_multi* m, const edsbwt_multi_result* r,
 
 void edsbwt_multi_result_free(edsbwt_multi_result* r) { delete r; }
 
+// ---- one process per GPU: the gather over peer memory -------------------------------------------------------------------------
+// The root process allocates an arena in its HBM and exports it (CUDA IPC); every other process maps it and, as soon as a chunk
+// of its shard has been searched, pushes the chunk's counts and tuples straight to their place in the arena with asynchronous
+// peer copies over NVLink (copy engines, not SMs), on a stream of its own: the transfer of chunk c runs under the search of
+// chunk c + 1, nobody exchanges sizes first and the root posts nothing.  Rank r owns a fixed region of the arena and fills it
+// front to back, so every destination is known locally.
+int edsbwt_device_alloc(int device, uint64_t bytes, void** d_ptr) {
+    if (!d_ptr) return EDSBWT_E_ARG;
+    *d_ptr = nullptr;
+    return guarded_multi([&] { CUDA_OK(cudaSetDevice(device)); CUDA_OK(cudaMalloc(d_ptr, bytes ? bytes : 1)); });
+}
+void edsbwt_device_free(int device, void* d_ptr) { if (d_ptr) { cudaSetDevice(device); cudaFree(d_ptr); } }
+int edsbwt_ipc_export(int device, const void* d_ptr, uint8_t handle[64]) {
+    if (!d_ptr || !handle) return EDSBWT_E_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    return guarded_multi([&] { CUDA_OK(cudaSetDevice(device)); cudaIpcMemHandle_t h; CUDA_OK(cudaIpcGetMemHandle(&h, const_cast<void*>(d_ptr))); memcpy(handle, &h, 64); });
+}
+int edsbwt_ipc_open(int device, const uint8_t handle[64], void** d_ptr) {
+    if (!d_ptr || !handle) return EDSBWT_E_ARG;
+    *d_ptr = nullptr;
+    return guarded_multi([&] { CUDA_OK(cudaSetDevice(device)); cudaIpcMemHandle_t h; memcpy(&h, handle, 64);
+                               CUDA_OK(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess)); });
+}
+int edsbwt_ipc_close(int device, void* d_ptr) {
+    if (!d_ptr) return EDSBWT_OK;
+    return guarded_multi([&] { CUDA_OK(cudaSetDevice(device)); CUDA_OK(cudaIpcCloseMemHandle(d_ptr)); });
+}
+int edsbwt_result_push(edsbwt_index* idx, const edsbwt_result* res, uint32_t* d_counts_dst, edsbwt_occ* d_occ_dst) {
+    if (!idx || !res) return EDSBWT_E_ARG;
+    return guarded_multi([&] {
+        Index& ix = idx->ix;
+        CUDA_OK(cudaSetDevice(ix.device));
+        if (!ix.push) CUDA_OK(cudaStreamCreateWithFlags(&ix.push, cudaStreamNonBlocking));
+        const SearchOut& o = *res->outp;           // the search has completed (run_search returns with its stream idle)
+        if (d_counts_dst && o.npat) CUDA_OK(cudaMemcpyAsync(d_counts_dst, o.counts.p, (size_t)o.npat * 4, cudaMemcpyDefault, ix.push));
+        if (d_occ_dst && o.nocc) CUDA_OK(cudaMemcpyAsync(d_occ_dst, o.occ.p, (size_t)o.nocc * sizeof(edsbwt_occ), cudaMemcpyDefault, ix.push));
+    });
+}
+int edsbwt_push_wait(edsbwt_index* idx) {
+    if (!idx) return EDSBWT_E_ARG;
+    return guarded_multi([&] { if (idx->ix.push) { CUDA_OK(cudaSetDevice(idx->ix.device)); CUDA_OK(cudaStreamSynchronize(idx->ix.push)); } });
+}
+
 }  // extern "C"

@@ -149,6 +149,85 @@ class ChunkedGather:
         return self.counts, [self.segs[k] for k in order]
 
 
+class PeerGather:
+    """The gather over peer memory (CUDA IPC + NVLink peer copies; include/edsbwt.h edsbwt_result_push): rank `dst` owns an arena
+    in its HBM -- counts[npat] followed by one tuple region of `tuple_cap` entries per rank -- which every other rank maps once.
+    A rank pushes chunk c of its shard as soon as it has searched it: the counts to their final place, the tuples behind the
+    previous chunk's in its own region.  Nothing is exchanged beforehand and rank dst posts nothing, so a chunk costs its rank two
+    cudaMemcpyAsync calls and travels under the search of the next chunk; finish() waits for the rank's own pushes and all-gathers
+    the chunk sizes (one small collective per batch), after which rank dst holds the batch: counts + tuple segments in (rank,
+    chunk) order = ascending pattern order.
+
+        g = PeerGather(eb, index, npat, nchunks, tuple_cap, group, dst)        # once: arena + IPC handshake
+        g.begin(); [g.push(c, device_result_c) ...]; counts, segments = g.finish()   # per batch
+    """
+
+    def __init__(self, eb, index, npat, nchunks, tuple_cap, group=None, dst=0):
+        self.eb, self.index, self.npat, self.nchunks, self.cap, self.group, self.dst = eb, index, npat, nchunks, int(tuple_cap), group, dst
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.dev = index.device
+        self.tup_off = (4 * npat + 255) & ~255
+        nbytes = self.tup_off + 20 * self.cap * self.world
+        box = [None]
+        if self.rank == dst:
+            self.base = eb.device_alloc(self.dev, nbytes)
+            box[0] = eb.ipc_export(self.dev, self.base)
+        if self.world > 1:
+            dist.broadcast_object_list(box, src=_global_rank(dst, group), group=group)
+        if self.rank != dst:
+            self.base = eb.ipc_open(self.dev, box[0])
+        self.b, self.e = shard_range(npat, self.world, self.rank)
+        self.live, self.sizes, self.used = [], [], 0
+        self.bytes_moved = 0
+
+    def begin(self):
+        self.live, self.sizes, self.used = [], [], 0
+
+    def push(self, c, result):
+        cb, ce = chunk_range(self.b, self.e, self.nchunks, c)
+        assert result.npat == ce - cb and len(self.sizes) == c
+        if self.used + result.nocc > self.cap:
+            raise RuntimeError("PeerGather: rank %d needs more than its %d tuple slots; raise tuple_cap" % (self.rank, self.cap))
+        self.index.push(result, self.base + 4 * cb, self.base + self.tup_off + 20 * (self.rank * self.cap + self.used))
+        self.live.append(result)                      # its buffers are the source of the copy until finish()
+        self.sizes.append(result.nocc)
+        self.used += result.nocc
+
+    def finish(self):
+        self.index.push_wait()                        # this rank's chunks have landed
+        dev = torch.device("cuda", self.dev)
+        mine = torch.tensor(self.sizes, dtype=torch.int64, device=dev)
+        allsz = torch.empty(self.world * self.nchunks, dtype=torch.int64, device=dev)
+        if self.world > 1:
+            dist.all_gather_into_tensor(allsz, mine, group=self.group)      # ... and once everybody says so, the batch is complete
+        else:
+            allsz.copy_(mine)
+        self.live = []
+        self.bytes_moved = 0
+        if self.rank != self.dst:
+            return None, None
+        sz = allsz.cpu().view(self.world, self.nchunks)
+        counts = torch.as_tensor(_DevArray(self.base, (self.npat,)), device=dev)
+        segs = []
+        for r in range(self.world):
+            off = 0
+            for c in range(self.nchunks):
+                n = int(sz[r, c])
+                ptr = self.base + self.tup_off + 20 * (r * self.cap + off)
+                segs.append(torch.as_tensor(_DevArray(ptr, (n, 5)), device=dev) if n else torch.zeros((0, 5), dtype=torch.int32, device=dev))
+                off += n
+                if r != self.dst:
+                    self.bytes_moved += 20 * n
+        self.bytes_moved += 4 * (self.npat - (self.e - self.b))
+        return counts, segs
+
+    def close(self):
+        if self.rank == self.dst:
+            self.eb.device_free(self.dev, self.base)
+        else:
+            self.eb.ipc_close(self.dev, self.base)
+
+
 def _global_rank(r, group):
     return r if group is None else dist.get_global_rank(group, r)
 

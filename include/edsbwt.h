@@ -213,6 +213,20 @@ int  edsbwt_multi_result_fetch(const edsbwt_multi_result* r, uint32_t* counts, e
 int  edsbwt_multi_result_write_csv(edsbwt_multi* m, const edsbwt_multi_result* r, const char* path, int move, int append, uint64_t* bytes);
 void edsbwt_multi_result_free(edsbwt_multi_result* r);
 
+/* --- multi-GPU, one process per GPU (torchrun and the like): the gather over peer memory.  The root process allocates an arena
+ *     in its HBM (edsbwt_device_alloc) and exports it (edsbwt_ipc_export, a 64-byte CUDA IPC handle that travels by any means);
+ *     the others map it (edsbwt_ipc_open) and push every finished chunk of their shard -- counts and tuples of a device-resident
+ *     result -- to its place in the arena with asynchronous peer copies over NVLink (edsbwt_result_push: copy engines, a stream of
+ *     its own, returns at once; the result must stay alive until edsbwt_push_wait).  No sizes are exchanged first and the root
+ *     posts nothing, so the transfer of chunk c runs under the search of chunk c + 1 (eds-bwt_b200/sharded.py PeerGather). */
+int  edsbwt_device_alloc(int device, uint64_t bytes, void** d_ptr);
+void edsbwt_device_free(int device, void* d_ptr);
+int  edsbwt_ipc_export(int device, const void* d_ptr, uint8_t handle[64]);
+int  edsbwt_ipc_open(int device, const uint8_t handle[64], void** d_ptr);
+int  edsbwt_ipc_close(int device, void* d_ptr);
+int  edsbwt_result_push(edsbwt_index* idx, const edsbwt_result* res, uint32_t* d_counts_dst, edsbwt_occ* d_occ_dst);
+int  edsbwt_push_wait(edsbwt_index* idx);
+
 int  edsbwt_set_engine(edsbwt_index* idx, int engine);      /* EDSBWT_ENGINE_* for every later search on this handle (A/B measurements) */
 int  edsbwt_last_stats(const edsbwt_index* idx, edsbwt_stats* st);
 int  edsbwt_set_stats(edsbwt_index* idx, int collect_counters, uint32_t canonical_k);

@@ -175,6 +175,28 @@ def _nccl_worker(rank, world, port, base, pats, q):
             for lf in (eb.LF_RANK, eb.LF_MOVE):
                 counts, occ = s.search(data, off, locate=True, lf_variant=lf)
                 out.append((counts.tolist(), None if occ is None else eb.occ_rows(occ)))
+            # the gather over peer memory: every chunk of the shard pushed into rank 0's arena (CUDA IPC, NVLink peer copies)
+            npat = len(off) - 1
+            b, e = sh.shard_range(npat, world, rank)
+            for nchunks in (1, 3):
+                g = sh.PeerGather(eb, idx, npat, nchunks, 4 * npat + 64, None, 0)
+                for rep in range(2):                                    # the arena is reused batch after batch
+                    g.begin()
+                    for c in range(nchunks):
+                        cb, ce = sh.chunk_range(b, e, nchunks, c)
+                        d_data = torch.from_numpy(np.ascontiguousarray(data[int(off[cb]):int(off[ce])]) if off[ce] > off[cb] else np.zeros(1, np.uint8)).cuda()
+                        d_off = torch.from_numpy((off[cb:ce + 1] - off[cb]).astype(np.int64)).cuda()
+                        r = idx.search_device(d_data.data_ptr(), d_off.data_ptr(), ce - cb, int(off[ce] - off[cb]), 0, locate=True, pat_base=cb)
+                        g.push(c, r)
+                    allc, segs = g.finish()
+                if rank == 0:
+                    occ = torch.cat(segs).cpu().numpy().view(np.uint32).reshape(-1).view(eb.OCC_DTYPE) if segs else np.zeros(0, eb.OCC_DTYPE)
+                    assert len(segs) == world * nchunks and np.all(np.diff(occ["pat"].astype(np.int64)) >= 0)
+                    out.append((allc.cpu().numpy().view(np.uint32).tolist(), eb.occ_rows(occ)))
+                else:
+                    out.append((out[0][0], None))
+                dist.barrier()
+                g.close()
         q.put((rank, out))
     finally:
         dist.destroy_process_group()
