@@ -354,7 +354,7 @@ struct MoveTable {
 struct ResultPool {
     std::mutex mu; std::vector<SearchOut*> free_list;
     SearchOut* get() { std::lock_guard<std::mutex> l(mu); if (free_list.empty()) return new SearchOut; SearchOut* r = free_list.back(); free_list.pop_back(); return r; }
-    void put(SearchOut* r) { { std::lock_guard<std::mutex> l(mu); if (free_list.size() < 4) { free_list.push_back(r); return; } } delete r; }
+    void put(SearchOut* r) { { std::lock_guard<std::mutex> l(mu); if (free_list.size() < 16) { free_list.push_back(r); return; } } delete r; }
     ~ResultPool() { for (SearchOut* r : free_list) delete r; }
 };
 

@@ -166,6 +166,10 @@ class PeerGather:
         self.eb, self.index, self.npat, self.nchunks, self.cap, self.group, self.dst = eb, index, npat, nchunks, int(tuple_cap), group, dst
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.dev = index.device
+        if self.world > 1:                            # every rank must lay the arena out the same way: the largest capacity asked for
+            t = torch.tensor([self.cap], dtype=torch.int64, device=torch.device("cuda", self.dev))
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+            self.cap = int(t.item())
         self.tup_off = (4 * npat + 255) & ~255
         nbytes = self.tup_off + 20 * self.cap * self.world
         box = [None]

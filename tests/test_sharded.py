@@ -179,7 +179,7 @@ def _nccl_worker(rank, world, port, base, pats, q):
             npat = len(off) - 1
             b, e = sh.shard_range(npat, world, rank)
             for nchunks in (1, 3):
-                g = sh.PeerGather(eb, idx, npat, nchunks, 4 * npat + 64, None, 0)
+                g = sh.PeerGather(eb, idx, npat, nchunks, len(out[0][1]) + 64 + rank if out[0][1] is not None else 1, None, 0)   # (capacities differ per rank: the largest wins)
                 for rep in range(2):                                    # the arena is reused batch after batch
                     g.begin()
                     for c in range(nchunks):
