@@ -32,6 +32,7 @@ EXPORTS = [
     "edsbwt_multi_result_info", "edsbwt_multi_result_device_ptrs", "edsbwt_multi_result_fetch", "edsbwt_multi_result_write_csv",
     "edsbwt_multi_result_free", "edsbwt_gather_bench_cfg", "edsbwt_move_table_save", "edsbwt_set_engine",
     "edsbwt_device_alloc", "edsbwt_device_free", "edsbwt_ipc_export", "edsbwt_ipc_open", "edsbwt_ipc_close", "edsbwt_result_push", "edsbwt_push_wait",
+    "edsbwt_count_static",
 ]
 
 
@@ -333,6 +334,16 @@ class Index:
         _check(lib().edsbwt_search_device_at(self._h, C.c_void_p(d_bytes_ptr), C.c_void_p(d_off_ptr), npat, total_bytes,
                                              max_len, int(locate), lf_variant, pat_base, C.byref(r)))
         return DeviceResult(r)
+
+    def count_static(self, d_bytes_ptr, d_off_ptr, npat, d_counts_ptr):
+        """edsbwt_count_static: count-only search that allocates nothing (scratch in a static device array).
+        -> number of patterns left unresolved (0 on success); raises on any other error."""
+        left = C.c_uint32()
+        rc = lib().edsbwt_count_static(self._h, C.c_void_p(d_bytes_ptr), C.c_void_p(d_off_ptr), npat, C.c_void_p(d_counts_ptr), C.byref(left))
+        if rc == -7 and left.value:          # EDSBWT_E_NOSPACE with a count: partial answer
+            return left.value
+        _check(rc)
+        return 0
 
 
 class MultiIndex:

@@ -10,7 +10,7 @@ LIB = os.path.join(HERE, "libedsbwt_cuda.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-Xptxas", "-v"]
-LIB_SRCS = ["engine.cu", "fused.cu", "items.cu", "multi.cu", "cache.cu", "move.cu", "api.cu", "gather_bench.cu", "builder.cu", "csv.cu", "host_io.cpp", "pack_host.cc"]
+LIB_SRCS = ["engine.cu", "fused.cu", "items.cu", "multi.cu", "cache.cu", "move.cu", "api.cu", "gather_bench.cu", "static_scratch.cu", "builder.cu", "csv.cu", "host_io.cpp", "pack_host.cc"]
 CLIS = {"EDSBWTsearch": "cli_edsbwtsearch.cpp", "MOVE_EDSBWTSearch": "cli_move_edsbwtsearch.cpp", "stringCheck": "cli_stringcheck.cpp", "build_MLF": "cli_build_mlf.cpp"}
 
 

@@ -294,6 +294,22 @@ typedef struct {
 } edsbwt_gather_cfg;
 int  edsbwt_gather_bench_cfg(int device, const edsbwt_gather_cfg* cfg, double* gb_per_s, double* req_per_s);
 
+/* Count-only search of a device-resident batch that ALLOCATES NOTHING (csrc/static_scratch.cu).  No counterpart in the
+ * reference: added for callers that cannot call cudaMalloc (CUDA graph capture, tight
+ * serving loops, harnesses that forbid allocation).  Same kernel and same answers as edsbwt_search_device(locate = 0), but its
+ * scratch lives in one file-scope device array of EDSBWT_STATIC_SCRATCH_BYTES per GPU (held until the process exits) instead
+ * of the handle's growable workspace.  d_pat_bytes / d_pat_off (npat + 1 offsets) / d_counts (npat) are DEVICE pointers of the
+ * handle's device.  npat > EDSBWT_STATIC_MAX_PATTERNS -> EDSBWT_E_NOSPACE, nothing launched.  Patterns whose frontier needs
+ * more than the array holds (the ones the other entry points hand to the level-synchronous engine) -> EDSBWT_E_NOSPACE,
+ * *n_unresolved = how many, their counts read 0, all other counts valid.  Returns with the handle's stream idle.  The array is
+ * shared by all calls and handles on a device: calls are serialised inside the library; do not overlap them on the GPU with
+ * anything else that uses this entry point from another process-wide context.  The first call on a device looks the array's
+ * address up (cudaGetSymbolAddress); no call uses cudaMalloc / cudaFree. */
+#define EDSBWT_STATIC_SCRATCH_BYTES (8u << 20)
+#define EDSBWT_STATIC_MAX_PATTERNS  65536u
+int  edsbwt_count_static(edsbwt_index* idx, const uint8_t* d_pat_bytes, const uint64_t* d_pat_off, uint32_t npat,
+                         uint32_t* d_counts, uint32_t* n_unresolved);
+
 void        edsbwt_free(void* p);
 const char* edsbwt_strerror(int code);
 const char* edsbwt_last_error(void);   /* thread-local detail of the last failure */
