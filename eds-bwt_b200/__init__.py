@@ -41,7 +41,7 @@ class Info(C.Structure):
                 ("alphabet", C.c_uint8 * 8), ("table_occ", C.c_uint32 * 25), ("seed_k", C.c_uint32),
                 ("locate_mode", C.c_uint32), ("device_bytes", C.c_uint64), ("seed_intervals", C.c_uint64),
                 ("move_runs", C.c_uint32), ("move_intervals", C.c_uint32), ("move_a", C.c_uint32), ("move_rounds", C.c_uint32),
-                ("from_file", C.c_uint32)]
+                ("from_file", C.c_uint32), ("engine", C.c_uint32), ("table_occ_wide", C.c_uint32 * 64)]
 
 
 class GatherCfg(C.Structure):

@@ -68,7 +68,9 @@ int edsbwt_index_info(const edsbwt_index* idx, edsbwt_info* info) {
     memset(info, 0, sizeof *info);
     info->n = h.n; info->n_text = h.n_text; info->n_seg = h.n_seg; info->sigma = h.sigma;
     memcpy(info->alphabet, h.alphabet, 8);
-    for (uint32_t i = 0; i < h.sigma * h.sigma && i < 25; ++i) info->table_occ[i] = h.table_occ[i];
+    if (h.sigma <= 5) for (uint32_t i = 0; i < h.sigma * h.sigma; ++i) info->table_occ[i] = h.table_occ[i];
+    for (uint32_t i = 0; i < h.sigma * h.sigma && i < 64; ++i) info->table_occ_wide[i] = h.table_occ[i];
+    info->engine = (uint32_t)idx->ix.engine;
     info->seed_k = idx->ix.seed_k; info->locate_mode = (uint32_t)idx->ix.locate_mode;
     info->device_bytes = idx->ix.device_bytes(); info->seed_intervals = idx->ix.seed_intervals;
     info->from_file = (idx->ix.image_from_file ? 1u : 0u) | (idx->ix.move_from_file ? 2u : 0u);
@@ -366,6 +368,10 @@ int edsbwt_search_trace(edsbwt_index* idx, const uint8_t* pat_bytes, const uint6
 int edsbwt_set_engine(edsbwt_index* idx, int engine) {
     if (!idx || engine < EDSBWT_ENGINE_FUSED || engine > EDSBWT_ENGINE_ITEMS) return EDSBWT_E_ARG;
     std::lock_guard<std::mutex> lock(idx->ix.mu);
+    if (idx->ix.wide && engine != EDSBWT_ENGINE_LEVELSYNC) {
+        set_error("an alphabet of %u letters is searched by the level-synchronous engine only (the other kernels pack 2-bit letter codes)", idx->ix.host.sigma - 1);
+        return EDSBWT_E_UNSUPPORTED;
+    }
     idx->ix.engine = engine;
     return EDSBWT_OK;
 }

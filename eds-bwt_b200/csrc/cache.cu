@@ -258,6 +258,7 @@ bool move_cache_load(Index& ix, const std::string& path) {
 
 // ---- whole image: <base>.edsbwt ---------------------------------------------------------------------------------
 void image_cache_save(Index& ix) {
+    if (ix.wide) return;          // the image format describes the 2-bit layout only: wide-alphabet indexes are rebuilt at every open
     CUDA_OK(cudaSetDevice(ix.device));
     CUDA_OK(cudaStreamSynchronize(ix.stream));
     Writer w; w.open(ix.base + ".edsbwt", 16 + 4 * 17);

@@ -89,13 +89,13 @@ inline int run_cli(int argc, char** argv, bool move) {
     std::cout << "\n";
     std::cout << "\nFrom " << fnInfoFile << " file (TableOcc):\n";           // :1647-1652
     for (uint32_t j = 0; j < info.sigma; ++j) {
-        for (uint32_t h = 0; h < info.sigma; ++h) std::cout << info.table_occ[j * info.sigma + h] << "\t";
+        for (uint32_t h = 0; h < info.sigma; ++h) std::cout << info.table_occ_wide[j * info.sigma + h] << "\t";
         std::cout << std::endl;
     }
     if (!move) {
         for (uint32_t x = 0; x < info.sigma; ++x) {                             // computeVectorOcc, :1341-1347 (freq[] is never filled: prints 0)
             uint64_t pile = 0;
-            for (uint32_t h = 0; h < info.sigma; ++h) pile += info.table_occ[x * info.sigma + h];
+            for (uint32_t h = 0; h < info.sigma; ++h) pile += info.table_occ_wide[x * info.sigma + h];
             std::cerr << "computeVectorUnbuildBCR: freq[" << x << "]= " << 0 << " and numBlocksInPartialBWT[" << x << "]= " << (pile + 1023) / 1024 << "\n";
         }
     } else {

@@ -104,6 +104,66 @@ void build_occ_blocks(const uint8_t* d_bytes, uint32_t n, const Lut& lut, DevBuf
     if (bad_out) *bad_out = hbad;
 }
 
+// ---- wide alphabets: 128-byte blocks (internal.cuh), letter codes 0..7, end-marker code 8
+__global__ void occw_pack_kernel(const uint8_t* __restrict__ bytes, uint32_t n, Lut lut, uint4* __restrict__ occ,
+                                 uint4* __restrict__ cnt_lo, uint4* __restrict__ cnt_hi, uint32_t ngroups, unsigned int* bad) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;          // one thread per 32-row group
+    uint32_t p0 = 0, p1 = 0, p2 = 0, mk = 0;
+    uint32_t c[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (g < ngroups) {
+        uint32_t base = g * 32u;
+        for (uint32_t b = 0; b < 32; ++b) {
+            uint32_t r = base + b;
+            if (r < n) {
+                uint8_t v = lut.code[bytes[r]];
+                if (v == 255) { atomicExch(bad, r + 1); v = 8; }
+                if (v == 8) mk |= 1u << b;
+                else {
+                    p0 |= (uint32_t)(v & 1) << b; p1 |= (uint32_t)((v >> 1) & 1) << b; p2 |= (uint32_t)((v >> 2) & 1) << b;
+                    #pragma unroll
+                    for (int t = 0; t < 8; ++t) c[t] += v == t;
+                }
+            }
+        }
+        occ[(size_t)(g >> 2) * OCCW_U4 + (g & 3)] = make_uint4(p0, p1, p2, mk);
+    }
+    #pragma unroll
+    for (int t = 0; t < 8; ++t) { c[t] += __shfl_xor_sync(0xffffffffu, c[t], 1); c[t] += __shfl_xor_sync(0xffffffffu, c[t], 2); }
+    if (g < ngroups && (g & 3) == 0) { cnt_lo[g >> 2] = make_uint4(c[0], c[1], c[2], c[3]); cnt_hi[g >> 2] = make_uint4(c[4], c[5], c[6], c[7]); }
+}
+__global__ void occw_counts_kernel(uint4* __restrict__ occ, const uint4* __restrict__ pre_lo, const uint4* __restrict__ pre_hi, uint32_t ngroups) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= ngroups) return;
+    const uint32_t j = g & 3;
+    const uint4 p = j < 2 ? pre_lo[g >> 2] : pre_hi[g >> 2];
+    occ[(size_t)(g >> 2) * OCCW_U4 + 4 + j] = (j & 1) ? make_uint4(p.z, p.w, 0u, 0u) : make_uint4(p.x, p.y, 0u, 0u);
+}
+void build_occ_blocks_wide(const uint8_t* d_bytes, uint32_t n, const Lut& lut, DevBuf<uint4>& occ, DevBuf<uint8_t>& cubtmp, cudaStream_t s,
+                           uint32_t tot[8], unsigned int* bad_out) {
+    uint32_t nblk = n / OCC_ROWS + 1, ngroups = nblk * 4;
+    occ.ensure((size_t)nblk * OCCW_U4);
+    DevBuf<uint4> cnt, pre; cnt.ensure((size_t)nblk * 2); pre.ensure((size_t)nblk * 2);
+    DevBuf<unsigned int> bad; bad.ensure(1);
+    CUDA_OK(cudaMemsetAsync(bad.p, 0, 4, s));
+    occw_pack_kernel<<<grid_for(ngroups, 256), 256, 0, s>>>(d_bytes, n, lut, occ.p, cnt.p, cnt.p + nblk, ngroups, bad.p);
+    size_t tmp = 0;
+    CUDA_OK(cub::DeviceScan::ExclusiveScan(nullptr, tmp, cnt.p, pre.p, AddU4(), make_uint4(0, 0, 0, 0), (int)nblk, s));
+    cubtmp.ensure(tmp);
+    CUDA_OK(cub::DeviceScan::ExclusiveScan(cubtmp.p, tmp, cnt.p, pre.p, AddU4(), make_uint4(0, 0, 0, 0), (int)nblk, s));
+    CUDA_OK(cub::DeviceScan::ExclusiveScan(cubtmp.p, tmp, cnt.p + nblk, pre.p + nblk, AddU4(), make_uint4(0, 0, 0, 0), (int)nblk, s));
+    occw_counts_kernel<<<grid_for(ngroups, 256), 256, 0, s>>>(occ.p, pre.p, pre.p + nblk, ngroups);
+    unsigned int hbad = 0;
+    uint4 lp[2], lc[2];
+    CUDA_OK(cudaMemcpyAsync(&hbad, bad.p, 4, cudaMemcpyDeviceToHost, s));
+    for (int h = 0; h < 2; ++h) {
+        CUDA_OK(cudaMemcpyAsync(&lp[h], pre.p + (size_t)h * nblk + (nblk - 1), 16, cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaMemcpyAsync(&lc[h], cnt.p + (size_t)h * nblk + (nblk - 1), 16, cudaMemcpyDeviceToHost, s));
+    }
+    CUDA_OK(cudaStreamSynchronize(s));
+    for (int h = 0; h < 2; ++h) { tot[4 * h] = lp[h].x + lc[h].x; tot[4 * h + 1] = lp[h].y + lc[h].y; tot[4 * h + 2] = lp[h].z + lc[h].z; tot[4 * h + 3] = lp[h].w + lc[h].w; }
+    if (bad_out) *bad_out = hbad;
+}
+
 // ===================================================================================================
 // SA table: row -> (string, offset), by walking every string backwards from its end-marker row
 // (the inverse of the reference's locate rounds, findMultipleDollarsBackward :349-603)
@@ -113,10 +173,7 @@ __global__ void sa_walk_kernel(const __grid_constant__ IndexView ix, uint2* __re
     if (w >= ix.n_text) return;
     uint32_t row = w, d = 0;                     // pile-0 row w is the suffix "$_w"
     sa[w] = make_uint2(w, 0);                    // end-marker rows: (string, distance 0); never read by locate
-    for (;;) {
-        uint32_t s = occ_symbol(ix.occ, row);
-        if (s == 0) break;
-        row = ix.Cl[s - 1] + occ_rank1(ix.occ, row, (int)s - 1);
+    while (lf_row_any(ix, row)) {
         ++d;
         sa[row] = make_uint2(w, d);              // d = distance to the end of the string
     }
@@ -155,12 +212,14 @@ __global__ void zip_kernel(const uint32_t* __restrict__ lo, const uint32_t* __re
 // patterns
 // ===================================================================================================
 struct PatView {
-    const uint64_t* pack;    // [npat * words] 2-bit codes, char i of pattern q at bits 2*(i%32) of pack[q*words + i/32]
+    const uint64_t* pack;    // [npat * words] letter codes, cb bits each (2; 4 for a wide alphabet): char i of pattern q at bits cb*(i % per) of pack[q*words + i/per], per = 64/cb
     const uint32_t* len;     // 0 for patterns that cannot match (bad character / empty)
     uint32_t words, npat, k; // k = seed depth used for this batch
+    uint32_t cb = 2, kb = 2; // kb = bits per character of a seed key (2; 3 for a wide alphabet)
 };
 __global__ void encode_patterns_kernel(const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ off, const uint32_t* __restrict__ ids,
-                                       uint32_t npat, Lut lut, uint32_t words, uint64_t* __restrict__ pack, uint32_t* __restrict__ len) {
+                                       uint32_t npat, Lut lut, uint32_t words, uint64_t* __restrict__ pack, uint32_t* __restrict__ len,
+                                       uint32_t nletters, uint32_t cb) {
     uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= npat) return;
     uint32_t g = ids ? ids[q] : q;               // local pattern q of this pass = pattern g of the batch
@@ -168,16 +227,18 @@ __global__ void encode_patterns_kernel(const uint8_t* __restrict__ bytes, const 
     uint32_t m = (uint32_t)(b - a);
     bool ok = m > 0;
     uint64_t wv = 0;
+    const uint32_t per = 64 / cb;
     for (uint32_t i = 0; i < m; ++i) {
         uint8_t c = lut.code[bytes[a + i]];
-        if (c > 3) { ok = false; c = 0; }
-        wv |= (uint64_t)c << (2 * (i & 31));
-        if ((i & 31) == 31 || i + 1 == m) { pack[(size_t)q * words + (i >> 5)] = wv; wv = 0; }
+        if (c >= nletters) { ok = false; c = 0; }
+        wv |= (uint64_t)c << (cb * (i % per));
+        if ((i % per) == per - 1 || i + 1 == m) { pack[(size_t)q * words + i / per] = wv; wv = 0; }
     }
     len[q] = ok ? m : 0;
 }
 __device__ __forceinline__ uint32_t pat_char(const PatView& pv, uint32_t q, uint32_t idx) {
-    return (uint32_t)(__ldg(pv.pack + (size_t)q * pv.words + (idx >> 5)) >> (2 * (idx & 31))) & 3u;
+    if (pv.cb == 2) return (uint32_t)(__ldg(pv.pack + (size_t)q * pv.words + (idx >> 5)) >> (2 * (idx & 31))) & 3u;
+    return (uint32_t)(__ldg(pv.pack + (size_t)q * pv.words + (idx >> 4)) >> (4 * (idx & 15))) & 15u;
 }
 
 // ===================================================================================================
@@ -192,7 +253,7 @@ __global__ void seed_count_kernel(PatView pv, SeedView sv, uint32_t* __restrict_
     if (m == 0) { cnt[q] = 0; src[q] = 0; return; }
     uint32_t L = m < pv.k ? m : pv.k;
     uint32_t key = 0;
-    for (uint32_t i = 0; i < L; ++i) key |= pat_char(pv, q, m - L + i) << (2 * i);
+    for (uint32_t i = 0; i < L; ++i) key |= pat_char(pv, q, m - L + i) << (pv.kb * i);
     uint32_t a = __ldg(sv.off[L] + key), b = __ldg(sv.off[L] + key + 1);
     cnt[q] = b - a; src[q] = a;
 }
@@ -207,14 +268,14 @@ __global__ void seed_scatter_kernel(PatView pv, SeedView sv, const uint32_t* __r
     uint2 v = __ldg(sv.iv[L] + j);
     fpat[t] = q; flo[t] = v.x; fhi[t] = v.y;
 }
-// level L -> the 4 children of every key, grouped by child key (4*key + c)
+// level L -> the nchild (4; 8 for a wide alphabet) children of every key, grouped by child key (nchild*key + c)
 __global__ void seed_expand_kernel(const uint32_t* __restrict__ pat, const uint2* __restrict__ iv,
-                                   const uint32_t* __restrict__ off, uint32_t nF, uint32_t* __restrict__ opat, uint32_t* __restrict__ olo, uint32_t* __restrict__ ohi) {
+                                   const uint32_t* __restrict__ off, uint32_t nF, uint32_t* __restrict__ opat, uint32_t* __restrict__ olo, uint32_t* __restrict__ ohi,
+                                   uint32_t nchild) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nF) return;
     uint32_t key = pat[i], a = off[key], cnt = off[key + 1] - a, r = i - a, l = iv[i].x, h = iv[i].y;
-    #pragma unroll
-    for (uint32_t c = 0; c < 4; ++c) { uint32_t d = 4 * a + c * cnt + r; opat[d] = 4 * key + c; olo[d] = l; ohi[d] = h; }
+    for (uint32_t c = 0; c < nchild; ++c) { uint32_t d = nchild * a + c * cnt + r; opat[d] = nchild * key + c; olo[d] = l; ohi[d] = h; }
 }
 __global__ void level_keys_kernel(const uint32_t* __restrict__ off, uint32_t nkeys, uint32_t nF, uint32_t* __restrict__ keyof) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -235,7 +296,7 @@ __global__ void key_offsets_kernel(const uint32_t* __restrict__ pat, uint32_t nF
 // (the common case after the seed phase) the block is fetched once.
 //   KEYMODE   : seed-table construction, "pattern" id is the child key, its character is key & 3
 //   otherwise : the character comes from the packed pattern; finished patterns pass through unchanged
-template <bool KEYMODE>
+template <bool KEYMODE, bool WIDE = false>
 __global__ void __launch_bounds__(256)
 lf_step_kernel(const __grid_constant__ IndexView ix, PatView pv, uint32_t step, const uint32_t* __restrict__ pat, const uint32_t* __restrict__ lo,
                const uint32_t* __restrict__ hi, uint32_t nF, uint32_t* __restrict__ olo, uint32_t* __restrict__ ohi,
@@ -247,7 +308,7 @@ lf_step_kernel(const __grid_constant__ IndexView ix, PatView pv, uint32_t step, 
     uint32_t ii = act ? i : 0;
     uint32_t q = __ldg(pat + ii), a = __ldg(lo + ii), b = __ldg(hi + ii) + 1;      // [a, b) half-open
     int c = 0; bool pass = false; uint32_t L = 0, m = 0;
-    if (KEYMODE) c = q & 3;
+    if (KEYMODE) c = WIDE ? (q & 7) : (q & 3);
     else {
         m = __ldg(pv.len + q);
         L = (m < pv.k ? m : pv.k) + step;
@@ -255,17 +316,29 @@ lf_step_kernel(const __grid_constant__ IndexView ix, PatView pv, uint32_t step, 
     }
     bool doload = act && !pass;
     uint32_t blk_a = a >> 7, blk_b = b >> 7;
-    uint4 va = make_uint4(0, 0, 0, 0), vb;
-    if (doload) va = occ_load(ix.occ, blk_a, lane4);
-    vb = va;
-    if (doload && blk_b != blk_a) vb = occ_load(ix.occ, blk_b, lane4);
-    uint32_t rca, rda, rcb, rdb;
-    rank4_from(va, a, c, lane4, rca, rda);
-    rank4_from(vb, b, c, lane4, rcb, rdb);
+    uint32_t rca, rda, rcb, rdb, Cc;
+    if (WIDE) {
+        // the 128-byte layout: planes + mask in entry lane4, the counts of letters 2*lane4, 2*lane4+1 in entry 4 + lane4
+        uint4 va = make_uint4(0, 0, 0, 0), ca = va, vb, cb2;
+        if (doload) { const uint4* p = ix.occ + (size_t)blk_a * OCCW_U4; va = __ldg(p + lane4); ca = __ldg(p + 4 + lane4); }
+        vb = va; cb2 = ca;
+        if (doload && blk_b != blk_a) { const uint4* p = ix.occ + (size_t)blk_b * OCCW_U4; vb = __ldg(p + lane4); cb2 = __ldg(p + 4 + lane4); }
+        rank4w_from(va, ca, a, c, lane4, rca, rda);
+        rank4w_from(vb, cb2, b, c, lane4, rcb, rdb);
+        Cc = ix.Clw[c];
+    } else {
+        uint4 va = make_uint4(0, 0, 0, 0), vb;
+        if (doload) va = occ_load(ix.occ, blk_a, lane4);
+        vb = va;
+        if (doload && blk_b != blk_a) vb = occ_load(ix.occ, blk_b, lane4);
+        rank4_from(va, a, c, lane4, rca, rda);
+        rank4_from(vb, b, c, lane4, rcb, rdb);
+        Cc = ix.Cl[c];
+    }
     uint32_t nlo, nhi, nd = 0;
     bool kept;
     if (pass) { nlo = a; nhi = b - 1; kept = true; }
-    else { nlo = ix.Cl[c] + rca; nhi = ix.Cl[c] + rcb - 1; kept = rcb > rca; nd = rdb - rda; }
+    else { nlo = Cc + rca; nhi = Cc + rcb - 1; kept = rcb > rca; nd = rdb - rda; }
     if (act && lane4 == 0) {
         olo[i] = nlo; ohi[i] = nhi; keep[i] = kept ? 1u : 0u;
         if (dcnt) { dcnt[i] = nd; dstart[i] = rda; }
@@ -403,13 +476,8 @@ __device__ __forceinline__ uint32_t locate_row(const IndexView& ix, uint32_t row
     uint2 si;
     if (WALK) {
         off = 0;
-        for (;;) {
-            uint32_t sy = occ_symbol(ix.occ, row);
-            if (sy == 0) break;
-            row = ix.Cl[sy - 1] + occ_rank1(ix.occ, row, (int)sy - 1);
-            ++off;
-        }
-        w = __ldg(ix.eof_flat + occ_rank_eof(ix.occ, row));
+        while (lf_row_any(ix, row)) ++off;
+        w = __ldg(ix.eof_flat + rank_eof_any(ix, row));
         si = __ldg(ix.str_info + w);
     } else { const uint4 v = __ldg(ix.sa4 + row); w = v.x; off = v.y; si = make_uint2(v.z, v.w); }      // ONE 16-byte gather per occurrence
     edsbwt_occ o; o.pat = pat; o.str = w; o.seg = si.x; o.idx_in_seg = si.y; o.off = off;
@@ -548,7 +616,7 @@ static uint32_t read_u32(Workspace& ws, const uint32_t* d, cudaStream_t s) {
 }
 Lut make_lut(const HostIndex& h) {
     Lut l; memset(l.code, 255, sizeof l.code);
-    l.code[h.alphabet[0]] = 4;
+    l.code[h.alphabet[0]] = h.sigma > 5 ? 8 : 4;      // end-marker: the value the Occ pack kernel of the layout tests for
     for (uint32_t a = 1; a < h.sigma; ++a) l.code[h.alphabet[a]] = (uint8_t)(a - 1);
     return l;
 }
@@ -581,7 +649,9 @@ static uint32_t engine_step(Index& ix, Workspace& ws, PatView pv, uint32_t step,
     if (nF == 0) return 0;
     ws.raw.ensure(nF); ws.keep.ensure(nF + 1); ws.dcnt.ensure(nF + 1); ws.dstart.ensure(nF); ws.dofs.ensure(nF + 2);
     if (time_lf) CUDA_OK(cudaEventRecord(ws.evk0, s));
-    lf_step_kernel<KEYMODE><<<grid_for((size_t)nF * 4, 256), 256, 0, s>>>(ix.view, pv, step, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p, nF,
+    if (ix.wide) lf_step_kernel<KEYMODE, true><<<grid_for((size_t)nF * 4, 256), 256, 0, s>>>(ix.view, pv, step, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p, nF,
+        ws.raw.lo.p, ws.raw.hi.p, ws.dcnt.p, ws.dstart.p, ws.keep.p, st, kc, 0);
+    else lf_step_kernel<KEYMODE><<<grid_for((size_t)nF * 4, 256), 256, 0, s>>>(ix.view, pv, step, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p, nF,
         ws.raw.lo.p, ws.raw.hi.p, ws.dcnt.p, ws.dstart.p, ws.keep.p, st, kc, 0);
     if (time_lf) { CUDA_OK(cudaEventRecord(ws.evk1, s)); }
     ws.launches += 1;
@@ -619,7 +689,9 @@ static uint32_t engine_step(Index& ix, Workspace& ws, PatView pv, uint32_t step,
     // Dol' : LF of the pile-0 ranges, then the same clean-up
     ws.dolraw.ensure(nDol); ws.keep.ensure(nDol + 1); ws.dcnt.ensure(nDol + 1); ws.dstart.ensure(nDol + 1);
     if (time_lf) CUDA_OK(cudaEventRecord(ws.evk0, s));
-    lf_step_kernel<KEYMODE><<<grid_for((size_t)nDol * 4, 256), 256, 0, s>>>(ix.view, pv, step, ws.dol.pat.p, ws.dol.lo.p, ws.dol.hi.p, nDol,
+    if (ix.wide) lf_step_kernel<KEYMODE, true><<<grid_for((size_t)nDol * 4, 256), 256, 0, s>>>(ix.view, pv, step, ws.dol.pat.p, ws.dol.lo.p, ws.dol.hi.p, nDol,
+        ws.dolraw.lo.p, ws.dolraw.hi.p, ws.dcnt.p, ws.dstart.p, ws.keep.p, st, kc, 1);
+    else lf_step_kernel<KEYMODE><<<grid_for((size_t)nDol * 4, 256), 256, 0, s>>>(ix.view, pv, step, ws.dol.pat.p, ws.dol.lo.p, ws.dol.hi.p, nDol,
         ws.dolraw.lo.p, ws.dolraw.hi.p, ws.dcnt.p, ws.dstart.p, ws.keep.p, st, kc, 1);
     if (time_lf) CUDA_OK(cudaEventRecord(ws.evk1, s));
     ws.launches += 1;
@@ -662,19 +734,21 @@ static void build_seed_table(Index& ix, uint32_t k) {
     Workspace& ws = *ix.ws;
     cudaStream_t s = ix.stream;
     ix.seed.assign(k + 1, nullptr);
+    const uint32_t kb = ix.key_bits, nchild = 1u << kb;      // 4 children per key; 8 for a wide alphabet
     // level 1: the piles
     {
-        std::vector<uint32_t> off(5, 0), lo, hi;
-        for (uint32_t c = 0; c < 4; ++c) {
+        std::vector<uint32_t> off(nchild + 1, 0), lo, hi;
+        for (uint32_t c = 0; c < nchild; ++c) {
             off[c] = (uint32_t)lo.size();
-            if (c < ix.view.nletters && ix.view.Cl[c + 1] > ix.view.Cl[c]) { lo.push_back(ix.view.Cl[c]); hi.push_back(ix.view.Cl[c + 1] - 1); }
+            const uint32_t first = ix.host.pile_start[c + 1 <= ix.host.sigma ? c + 1 : ix.host.sigma], next = ix.host.pile_start[c + 2 <= ix.host.sigma ? c + 2 : ix.host.sigma];
+            if (c < ix.view.nletters && next > first) { lo.push_back(first); hi.push_back(next - 1); }
         }
-        off[4] = (uint32_t)lo.size();
+        off[nchild] = (uint32_t)lo.size();
         SeedLevel* L1 = new SeedLevel; ix.seed[1] = L1;
         std::vector<uint2> iv(lo.size());
         for (size_t i = 0; i < lo.size(); ++i) iv[i] = make_uint2(lo[i], hi[i]);
-        L1->off.ensure(5); L1->iv.ensure(lo.size() + 1); L1->n_iv = lo.size();
-        CUDA_OK(cudaMemcpyAsync(L1->off.p, off.data(), 20, cudaMemcpyHostToDevice, s));
+        L1->off.ensure(nchild + 1); L1->iv.ensure(lo.size() + 1); L1->n_iv = lo.size();
+        CUDA_OK(cudaMemcpyAsync(L1->off.p, off.data(), (nchild + 1) * 4, cudaMemcpyHostToDevice, s));
         if (!iv.empty()) CUDA_OK(cudaMemcpyAsync(L1->iv.p, iv.data(), iv.size() * 8, cudaMemcpyHostToDevice, s));
         CUDA_OK(cudaStreamSynchronize(s));
         ix.seed_intervals = lo.size();
@@ -682,8 +756,8 @@ static void build_seed_table(Index& ix, uint32_t k) {
     PatView pv{}; pv.k = 0;
     for (uint32_t L = 1; L < k; ++L) {
         SeedLevel* cur = ix.seed[L];
-        uint32_t nkeys = 1u << (2 * L), nF = (uint32_t)cur->n_iv;
-        size_t nE = (size_t)nF * 4;
+        uint32_t nkeys = 1u << (kb * L), nF = (uint32_t)cur->n_iv;
+        size_t nE = (size_t)nF * nchild;
         if (nE > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "seed level %u too large", L + 1);
         ws.cur.ensure(nE ? nE : 1); ws.nxt.ensure(nF ? nF : 1);
         // pat array of the level = key of every interval (recovered from off)
@@ -692,12 +766,12 @@ static void build_seed_table(Index& ix, uint32_t k) {
             // key of interval i = upper_bound(off, i) - 1
             ws.src.ensure(nF);
             level_keys_kernel<<<grid_for(nF, 256), 256, 0, s>>>(cur->off.p, nkeys, nF, ws.src.p);
-            seed_expand_kernel<<<grid_for(nF, 256), 256, 0, s>>>(ws.src.p, cur->iv.p, cur->off.p, nF, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p);
+            seed_expand_kernel<<<grid_for(nF, 256), 256, 0, s>>>(ws.src.p, cur->iv.p, cur->off.p, nF, ws.cur.pat.p, ws.cur.lo.p, ws.cur.hi.p, nchild);
             ws.launches += 2;
             newF = engine_step<true>(ix, ws, pv, 0, (uint32_t)nE, nullptr, 0, false);
         }
         SeedLevel* nx = new SeedLevel; ix.seed[L + 1] = nx;
-        uint32_t nk2 = nkeys * 4;
+        uint32_t nk2 = nkeys * nchild;
         nx->off.exact((size_t)nk2 + 1); nx->iv.exact((size_t)newF + 1); nx->n_iv = newF;
         if (newF) zip_kernel<<<grid_for(newF, 256), 256, 0, s>>>(ws.cur.lo.p, ws.cur.hi.p, newF, nx->iv.p);
         key_offsets_kernel<<<grid_for((size_t)nk2 + 1, 256), 256, 0, s>>>(ws.cur.pat.p, newF, nk2, nx->off.p);
@@ -709,14 +783,14 @@ static void build_seed_table(Index& ix, uint32_t k) {
     for (uint32_t L = 1; L <= k; ++L) {
         SeedLevel* lv = ix.seed[L];
         ivp[L] = lv->iv.p;
-        if (L == k && k > 8) continue;
-        const uint32_t nkeys = 1u << (2 * L);
+        if (L == k && k > 8 && !ix.wide) continue;
+        const uint32_t nkeys = 1u << (kb * L);
         lv->cnt.exact(nkeys);
         seed_counts_kernel<<<grid_for(nkeys, 256), 256, 0, s>>>(lv->off.p, lv->iv.p, nkeys, lv->cnt.p);
     }
     {                                   // deepest level: the seed lookup of the hot kernel in one 16-byte gather
         SeedLevel* lv = ix.seed[k];
-        const uint32_t nkeys = 1u << (2 * k);
+        const uint32_t nkeys = 1u << (kb * k);
         lv->first.exact(nkeys);
         seed_first_kernel<<<grid_for(nkeys, 256), 256, 0, s>>>(lv->off.p, lv->iv.p, nkeys, lv->first.p);
     }
@@ -756,13 +830,19 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     IndexView& v = ix.view;
     v.n = h.n; v.n_text = h.n_text; v.n_seg = h.n_seg; v.nletters = h.sigma - 1;
     for (uint32_t c = 0; c < 5; ++c) v.Cl[c] = c < h.sigma - 1 ? h.pile_start[c + 1] : h.n;
+    // 5..7 letters: 3-bit codes in 128-byte Occ blocks, base-8 seed keys, level-synchronous engine only
+    ix.wide = h.sigma > 5; ix.key_bits = ix.wide ? 3 : 2;
+    v.wide = ix.wide ? 1u : 0u;
+    for (uint32_t c = 0; c < 9; ++c) v.Clw[c] = c < h.sigma - 1 ? h.pile_start[c + 1] : h.n;
+    if (ix.wide) ix.engine = EDSBWT_ENGINE_LEVELSYNC;
 
     // ---- K1: Occ blocks
     {
         DevBuf<uint8_t> d_bytes; d_bytes.ensure((size_t)h.n + 64);
         CUDA_OK(cudaMemcpyAsync(d_bytes.p, h.ebwt.data(), h.n, cudaMemcpyHostToDevice, s));
-        uint32_t tot[4]; unsigned int hbad = 0;
-        build_occ_blocks(d_bytes.p, h.n, make_lut(h), ix.occ, ws.cubtmp, s, tot, &hbad);
+        uint32_t tot[8] = {0}; unsigned int hbad = 0;
+        if (ix.wide) build_occ_blocks_wide(d_bytes.p, h.n, make_lut(h), ix.occ, ws.cubtmp, s, tot, &hbad);
+        else build_occ_blocks(d_bytes.p, h.n, make_lut(h), ix.occ, ws.cubtmp, s, tot, &hbad);
         if (hbad) EDS_FAIL(EDSBWT_E_FORMAT, "eBWT row %u holds a byte outside the alphabet of info.aux", hbad - 1);
         // totals must reproduce the pile sizes implied by tableOcc
         for (uint32_t c = 0; c + 1 < h.sigma; ++c) {
@@ -839,13 +919,14 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     CUDA_OK(cudaStreamSynchronize(s));
     // ---- seed table
     int k = o.seed_k;
-    if (k < 0) { k = 1; while (k < 14 && (1ull << (2 * (k + 1))) <= (uint64_t)h.n) ++k; }      // floor(log4 n), at most 14
+    const int kmax = ix.wide ? 8 : 14;          // 4^14 = 2^28 keys; 8^8 = 2^24
+    if (k < 0) { k = 1; while (k < kmax && (1ull << (ix.key_bits * (k + 1))) <= (uint64_t)h.n) ++k; }      // floor(log4 n) (log8 when wide)
     if (k < 1) k = 1;
-    if (k > 14) k = 14;
+    if (k > kmax) k = kmax;
     ix.seed_k = (uint32_t)k;
     build_seed_table(ix, ix.seed_k);
     CUDA_OK(cudaGetLastError());
-    if (o.build_move) build_move_table(ix);
+    if (o.build_move && !ix.wide) build_move_table(ix);
     h.ebwt.clear(); h.ebwt.shrink_to_fit();
     h.seg_first_bit.clear(); h.seg_first_bit.shrink_to_fit();
     h.eof_flat.clear(); h.eof_flat.shrink_to_fit();
@@ -866,7 +947,7 @@ __global__ void ls_alive_init_kernel(PatView pv, SeedView sv, const uint32_t* __
         if (cnt[q]) la = L0;
         else for (uint32_t L = L0 - 1; L >= 1; --L) {
             uint32_t key = 0;
-            for (uint32_t i = 0; i < L; ++i) key |= pat_char(pv, q, m - L + i) << (2 * i);
+            for (uint32_t i = 0; i < L; ++i) key |= pat_char(pv, q, m - L + i) << (pv.kb * i);
             if (__ldg(sv.off[L] + key + 1) > __ldg(sv.off[L] + key)) { la = L; break; }
         }
     }
@@ -896,11 +977,12 @@ static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64
                                  StatsDev* st, uint32_t& steps, uint64_t& peak, uint32_t* d_alive, uint32_t k_eff) {
     Workspace& ws = *ix.ws;
     cudaStream_t s = ix.stream;
-    uint32_t words = (max_len + 31) / 32; if (!words) words = 1;
+    const uint32_t cb = ix.wide ? 4u : 2u, per = 64 / cb;
+    uint32_t words = (max_len + per - 1) / per; if (!words) words = 1;
     ws.ppack.ensure((size_t)nsub * words); ws.plen.ensure(nsub);
     Lut lut = make_lut(ix.host);
-    encode_patterns_kernel<<<grid_for(nsub, 128), 128, 0, s>>>(d_bytes, d_off, ids, nsub, lut, words, ws.ppack.p, ws.plen.p);
-    PatView pv{ws.ppack.p, ws.plen.p, words, nsub, k_eff};
+    encode_patterns_kernel<<<grid_for(nsub, 128), 128, 0, s>>>(d_bytes, d_off, ids, nsub, lut, words, ws.ppack.p, ws.plen.p, ix.view.nletters, cb);
+    PatView pv{ws.ppack.p, ws.plen.p, words, nsub, k_eff, cb, ix.key_bits};
     SeedView sv{};
     for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; sv.cnt[L] = ix.seed[L]->cnt.p; }
             sv.first = ix.seed[ix.seed_k]->first.p; sv.first_level = ix.seed_k;
@@ -934,6 +1016,8 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
                 bool locate, int lf_variant, SearchOut& out, uint32_t pat_base, const PatHint* hint) {
     if (lf_variant != EDSBWT_LF_RANK && lf_variant != EDSBWT_LF_MOVE) EDS_FAIL(EDSBWT_E_ARG, "unknown LF variant %d", lf_variant);
     const bool move = lf_variant == EDSBWT_LF_MOVE;
+    if (ix.wide && move) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "the move-table variant packs 2-bit letter codes: an alphabet of %u letters is searched with EDSBWT_LF_RANK only", ix.host.sigma - 1);
+    if (ix.wide && hint && hint->d_words) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "packed 2-bit patterns cannot address an alphabet of %u letters: pass bytes", ix.host.sigma - 1);
     if (move && out.want_alive) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "edsbwt_search_trace is an EDSBWTsearch (RECOVERBW=0) feature; MOVE_EDSBWTSearch always locates");
     const uint32_t fixed_len = hint ? hint->fixed_len : 0u, stride = (fixed_len + 31) / 32;
     const uint64_t* caller_words = hint ? hint->d_words : nullptr;
@@ -983,7 +1067,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
         CUDA_OK(cudaMemsetAsync(ws.fcursor.p, 0, 32, s));
         uint32_t nstage = 0;
         const uint32_t* ids = nullptr;
-        if (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move) {
+        if (!ix.wide && (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move)) {
             // first pass: the item kernel for batches that are (or are asked to be) 2-bit words, the step-loop kernel for bytes
             const bool items = !move && (ix.engine == EDSBWT_ENGINE_ITEMS || (ix.engine == EDSBWT_ENGINE_FUSED && caller_words));
             size_t want = (size_t)npat * 2 + (1u << 16);
@@ -1126,7 +1210,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     ls = edsbwt_stats{};
     ls.I = hs.I; ls.S = hs.S; ls.E = hs.E; ls.L = hs.L; ls.O = hs.O; ls.lf_intervals = hs.lf_intervals; ls.occ_blocks = hs.occ_blocks;
     ls.steps = steps; ls.kernel_launches = ws.launches; ls.lf_kernel_ms = ws.lf_ms; ls.total_ms = ms; ls.frontier_peak = peak;
-    ls.overflow_patterns = (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move) ? novf1 : 0; ls.levelsync_patterns = novf;
+    ls.overflow_patterns = (!ix.wide && (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move)) ? novf1 : 0; ls.levelsync_patterns = novf;
     if (fused_ran) { float fm = 0; CUDA_OK(cudaEventElapsedTime(&fm, ws.evf0, ws.evf1)); ls.search_kernel_ms = fm; }
     if (locate_ran) { float lm = 0; CUDA_OK(cudaEventElapsedTime(&lm, ws.evl0, ws.evl1)); ls.locate_kernel_ms = lm; }
 }

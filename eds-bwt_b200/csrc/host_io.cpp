@@ -217,7 +217,7 @@ void load_host_index(const std::string& base, bool verify, HostIndex& h) {
     if (info.size() < 10) EDS_FAIL(EDSBWT_E_FORMAT, "%s_info.aux is too short", base.c_str());
     memcpy(&h.n, &info[0], 4); memcpy(&h.n_text, &info[4], 4); h.sigma = info[8];
     if (h.sigma < 2) EDS_FAIL(EDSBWT_E_FORMAT, "alphabet of size %u", h.sigma);
-    if (h.sigma > 5) EDS_FAIL(EDSBWT_E_ALPHABET, "alphabet of size %u: this build packs at most 4 letters + end-marker (2-bit Occ blocks)", h.sigma);
+    if (h.sigma > 8) EDS_FAIL(EDSBWT_E_ALPHABET, "alphabet of size %u: this build packs at most 7 letters + end-marker (3-bit Occ blocks)", h.sigma);
     size_t need = 9 + h.sigma + 4ull * h.n_text + 4ull * h.sigma * h.sigma;
     if (info.size() != need) EDS_FAIL(EDSBWT_E_FORMAT, "%s_info.aux has %zu bytes, expected %zu", base.c_str(), info.size(), need);
     memcpy(h.alphabet, &info[9], h.sigma);

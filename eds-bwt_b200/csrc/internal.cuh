@@ -84,6 +84,10 @@ struct IndexView {
                                  // strings of the segments reachable from string eof_flat[r] (x > y: none) -- the whole
                                  // preceding_dollars_finder + empty-string closure of link() in one 8-byte gather
     const uint2*    str_info;    // string -> (1-based segment, index inside the segment)
+    // wide alphabets (5..7 letters + end-marker, e.g. {#,A,C,G,N,T}): 3-bit letter codes, 128-byte Occ blocks (below), searched
+    // by the level-synchronous engine only.  wide == 0: everything above, Cl[] included, is the 2-bit layout.
+    uint32_t wide;
+    uint32_t Clw[9];             // wide: Clw[c] = first row of the pile of letter c, n for c >= nletters
 };
 
 #ifdef __CUDACC__
@@ -134,6 +138,72 @@ __device__ __forceinline__ uint32_t occ_rank_eof(const uint4* __restrict__ occ, 
         if (below > 0) r += __popc(v.w & (below >= 32 ? 0xffffffffu : ((1u << below) - 1u)));
     }
     return r;
+}
+
+// ---- wide alphabets: one 128-byte block per 128 rows = 8 x uint4.  Entry j (0..3) covers rows 32j..32j+31:
+//   [j]      .x .y .z bit-planes 0..2 of the 3-bit letter code, .w end-marker mask ('#' rows have planes 0)
+//   [4 + j]  .x .y   occurrences of letters 2j and 2j+1 in rows [0, 128*blk)
+// so that the same 4-lane group ranks any of up to 8 letters and '#' with two 128-bit loads per lane.
+constexpr uint32_t OCCW_U4 = 8;
+__device__ __forceinline__ uint32_t occw_match(const uint4& v, int c) {
+    return ((c & 1) ? v.x : ~v.x) & ((c & 2) ? v.y : ~v.y) & ((c & 4) ? v.z : ~v.z) & ~v.w;
+}
+__device__ __forceinline__ void rank4w_from(uint4 va, uint4 vb, uint32_t pos, int c, int lane4, uint32_t& rc, uint32_t& rd) {
+    int below = (int)(pos & (OCC_ROWS - 1)) - 32 * lane4;
+    uint32_t lm = below <= 0 ? 0u : (below >= 32 ? 0xffffffffu : ((1u << below) - 1u));
+    uint32_t pc = __popc(occw_match(va, c) & lm) + (lane4 == (c >> 1) ? ((c & 1) ? vb.y : vb.x) : 0u);
+    uint32_t pd = __popc(va.w & lm) - (vb.x + vb.y);          // wraps; the 4-lane sum is exact mod 2^32
+    pc += __shfl_xor_sync(0xffffffffu, pc, 1); pc += __shfl_xor_sync(0xffffffffu, pc, 2);
+    pd += __shfl_xor_sync(0xffffffffu, pd, 1); pd += __shfl_xor_sync(0xffffffffu, pd, 2);
+    rc = pc;
+    rd = pd + (pos & ~(OCC_ROWS - 1));
+}
+__device__ __forceinline__ uint32_t occw_symbol(const uint4* __restrict__ occ, uint32_t row) {   // 0 = '#', 1+c = letter c
+    uint4 v = __ldg(occ + (size_t)(row >> 7) * OCCW_U4 + ((row >> 5) & 3));
+    uint32_t b = row & 31;
+    if ((v.w >> b) & 1) return 0;
+    return 1 + (((v.x >> b) & 1) | (((v.y >> b) & 1) << 1) | (((v.z >> b) & 1) << 2));
+}
+__device__ __forceinline__ uint32_t occw_rank1(const uint4* __restrict__ occ, uint32_t pos, int c) {
+    uint32_t blk = pos >> 7, off = pos & 127;
+    const uint4* b = occ + (size_t)blk * OCCW_U4;
+    const uint4 cn = __ldg(&b[4 + (c >> 1)]);
+    uint32_t r = (c & 1) ? cn.y : cn.x;
+    for (int j = 0; j < 4; ++j) {
+        int below = (int)off - 32 * j;
+        if (below <= 0) break;
+        uint4 v = __ldg(&b[j]);
+        r += __popc(occw_match(v, c) & (below >= 32 ? 0xffffffffu : ((1u << below) - 1u)));
+    }
+    return r;
+}
+__device__ __forceinline__ uint32_t occw_rank_eof(const uint4* __restrict__ occ, uint32_t pos) {
+    uint32_t blk = pos >> 7, off = pos & 127;
+    const uint4* b = occ + (size_t)blk * OCCW_U4;
+    uint32_t r = blk * OCC_ROWS;
+    for (int j = 0; j < 4; ++j) {
+        uint4 v = __ldg(&b[j]), cn = __ldg(&b[4 + j]);
+        r -= cn.x + cn.y;
+        int below = (int)off - 32 * j;
+        if (below > 0) r += __popc(v.w & (below >= 32 ? 0xffffffffu : ((1u << below) - 1u)));
+    }
+    return r;
+}
+// one LF step of a single row, either layout (index build, LF-walk locate): false when the row holds '#'
+__device__ __forceinline__ bool lf_row_any(const IndexView& ix, uint32_t& row) {
+    if (ix.wide) {
+        const uint32_t s = occw_symbol(ix.occ, row);
+        if (s == 0) return false;
+        row = ix.Clw[s - 1] + occw_rank1(ix.occ, row, (int)s - 1);
+    } else {
+        const uint32_t s = occ_symbol(ix.occ, row);
+        if (s == 0) return false;
+        row = ix.Cl[s - 1] + occ_rank1(ix.occ, row, (int)s - 1);
+    }
+    return true;
+}
+__device__ __forceinline__ uint32_t rank_eof_any(const IndexView& ix, uint32_t row) {
+    return ix.wide ? occw_rank_eof(ix.occ, row) : occ_rank_eof(ix.occ, row);
 }
 
 // ---- one-thread-per-pattern kernels (fused.cu, move.cu): whole 64-byte blocks in registers, 2-bit pattern windows
@@ -376,6 +446,8 @@ struct Index {
     IndexView view{};
     uint32_t seed_k = 0;
     int locate_mode = EDSBWT_LOCATE_SA;
+    bool wide = false;               // 5..7 letters: 3-bit codes, 128-byte Occ blocks, level-synchronous engine only
+    uint32_t key_bits = 2;           // bits per character of a seed key (3 when wide)
     std::vector<SeedLevel*> seed;       // seed[L] for L = 1..seed_k (index 0 unused)
     uint64_t seed_intervals = 0;
     Workspace* ws = nullptr;
@@ -399,10 +471,12 @@ struct Index {
 };
 
 // engine.cu
-struct Lut { uint8_t code[256]; };     // 0..3 letter code, 4 = end-marker, 255 = not in the alphabet
+struct Lut { uint8_t code[256]; };     // letter code 0..nletters-1, LUT_EOF = end-marker (4, the narrow kernels test for it; 8 for a wide alphabet), 255 = not in the alphabet
 Lut make_lut(const HostIndex& h);
 void build_occ_blocks(const uint8_t* d_bytes, uint32_t n, const Lut& lut, DevBuf<uint4>& occ, DevBuf<uint8_t>& cubtmp, cudaStream_t s,
                       uint32_t tot[4], unsigned int* bad_out);
+void build_occ_blocks_wide(const uint8_t* d_bytes, uint32_t n, const Lut& lut, DevBuf<uint4>& occ, DevBuf<uint8_t>& cubtmp, cudaStream_t s,
+                           uint32_t tot[8], unsigned int* bad_out);
 void init_index_runtime(Index& ix, const edsbwt_open_opts& o);      // stream, workspace, engine options, byte -> code table
 void build_device_index(Index& ix, const edsbwt_open_opts& o);
 // cache.cu -- persisted tables: <base>.edsbwt (whole HBM image, opt-in) and <base>_MLF.edsbwt (move table)

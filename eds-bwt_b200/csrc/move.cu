@@ -117,6 +117,7 @@ __global__ void row_run0_kernel(const uint32_t* __restrict__ P, const uint32_t* 
 
 void build_move_table(Index& ix) {
     if (ix.move) return;
+    if (ix.wide) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "the move table packs 2-bit letter codes: not built for an alphabet of %u letters", ix.host.sigma - 1);
     CUDA_OK(cudaSetDevice(ix.device));
     // a table written earlier by build_MLF / edsbwt_move_table_save for these very index files (the reference's
     // retrieve_MLF, MOVE_EDSBWTSearch.cpp:186-192): stale or foreign files are ignored and the table is built

@@ -24,7 +24,7 @@ extern "C" {
 #define EDSBWT_OK            0
 #define EDSBWT_E_IO         -1   /* a file of the index / pattern set could not be opened or is truncated   */
 #define EDSBWT_E_FORMAT     -2   /* inconsistent index files (sizes, tableOcc, _bv_ vs _bwt_, .bitvector)    */
-#define EDSBWT_E_ALPHABET   -3   /* more than 4 letters besides the end-marker (2-bit Occ layout only)       */
+#define EDSBWT_E_ALPHABET   -3   /* more than 7 letters besides the end-marker (2-bit / 3-bit Occ layouts)    */
 #define EDSBWT_E_CUDA       -4   /* no device / CUDA runtime error / out of device memory                    */
 #define EDSBWT_E_ARG        -5   /* bad argument                                                             */
 #define EDSBWT_E_UNSUPPORTED -6
@@ -50,7 +50,7 @@ typedef struct {
     uint32_t n_seg;             /* number of degenerate segments                               */
     uint32_t sigma;             /* alphabet size incl. the end-marker                          */
     uint8_t  alphabet[8];       /* alphaInverse[], alphabet[0] == '#'                          */
-    uint32_t table_occ[25];     /* tableOcc[sigma][sigma], row-major (recoverInfo dump)        */
+    uint32_t table_occ[25];     /* tableOcc[sigma][sigma], row-major (recoverInfo dump), sigma <= 5; zero otherwise */
     uint32_t seed_k;            /* depth of the seed table actually built                      */
     uint32_t locate_mode;       /* EDSBWT_LOCATE_*                                             */
     uint64_t device_bytes;      /* HBM held by the handle                                      */
@@ -60,6 +60,8 @@ typedef struct {
     uint32_t move_a;            /* balancing parameter                                          */
     uint32_t move_rounds;       /* balancing rounds the builder needed                          */
     uint32_t from_file;         /* bit 0: the HBM image was read from <base>.edsbwt; bit 1: the move table from <base>_MLF.edsbwt */
+    uint32_t engine;            /* EDSBWT_ENGINE_* in force (an alphabet of 5..7 letters always runs EDSBWT_ENGINE_LEVELSYNC)      */
+    uint32_t table_occ_wide[64];/* tableOcc[sigma][sigma], row-major, for every sigma <= 8                                          */
 } edsbwt_info;
 
 #define EDSBWT_LOCATE_SA    0   /* row -> (string, offset) table in HBM: one gather per occurrence           */

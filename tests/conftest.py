@@ -23,7 +23,13 @@ def oracle_built():
 
 def golden_names():
     d = os.path.join(ROOT, "tests", "golden")
-    return sorted(f[:-5] for f in os.listdir(d) if f.endswith(".json"))
+    return sorted(f[:-5] for f in os.listdir(d) if f.endswith(".json") and not f.startswith("wide_"))
+
+
+def wide_golden_names():
+    """goldens over alphabets of 5..7 letters (3-bit Occ layout, level-synchronous engine only)"""
+    d = os.path.join(ROOT, "tests", "golden")
+    return sorted(f[:-5] for f in os.listdir(d) if f.endswith(".json") and f.startswith("wide_"))
 
 
 def load_golden(name):

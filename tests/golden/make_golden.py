@@ -80,3 +80,15 @@ if __name__ == "__main__":
          [b"A", b"AC", b"ACG", b"GT", b"GACGT", b"CGA", b"CGC", b"CGG", b"CGT", b"CGACGTA", b"GTTT", b"ACGTTT", b"TACGTTT",
           b"CGAT", b"ACGACGT", b"T", b"TT", b"TTT", b"TTTT", b"G"],
          "chains of segments containing the empty string")
+    # ---- alphabets wider than {A,C,G,T} (N / IUPAC codes in real assemblies; Parameters.h lists {$,A,C,G,N,T}).
+    #      Named wide_*: used by tests/test_wide_alphabet.py only (the 2-bit kernels and the move table do not take them).
+    make("wide_kmers_n", b"{TT,TA,C}{T}{TN,A,G}{NT,}{ANT}",
+         [b"TTAT", b"ATNT", b"CTTN", b"NANT", b"TNA", b"N", b"NT", b"TANTANT", b"GANT", b"TTT"],
+         "the cfg1 EDS with N in three strings; sample/test/kmers.txt line 7 holds N")
+    for seed, alpha, kw in [(11, b"ACGNT", dict(n_seg=300, max_var=5, max_len=5, p_empty=0.3, nondeg_len=(1, 12))),
+                            (12, b"ACGNRTY", dict(n_seg=900, max_var=4, max_len=6, p_empty=0.15, nondeg_len=(1, 30)))]:
+        rng = np.random.default_rng(seed)
+        segs = E.random_eds(rng, alphabet=alpha, **kw)
+        pats = sample_patterns(rng, segs, 150, [1, 2, 3, 4, 6, 8, 12, 16, 24, 32, 48])
+        make("wide_random_seed%d" % seed, E.format_eds(segs), pats, "random EDS over %s, numpy default_rng(%d)" % (alpha.decode(), seed))
+
