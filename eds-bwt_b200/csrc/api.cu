@@ -368,8 +368,8 @@ int edsbwt_search_trace(edsbwt_index* idx, const uint8_t* pat_bytes, const uint6
 int edsbwt_set_engine(edsbwt_index* idx, int engine) {
     if (!idx || engine < EDSBWT_ENGINE_FUSED || engine > EDSBWT_ENGINE_ITEMS) return EDSBWT_E_ARG;
     std::lock_guard<std::mutex> lock(idx->ix.mu);
-    if (idx->ix.wide && engine != EDSBWT_ENGINE_LEVELSYNC) {
-        set_error("an alphabet of %u letters is searched by the level-synchronous engine only (the other kernels pack 2-bit letter codes)", idx->ix.host.sigma - 1);
+    if (idx->ix.wide && engine == EDSBWT_ENGINE_ITEMS) {
+        set_error("the item kernel reads 2-bit pattern words: an alphabet of %u letters is searched by the step-loop kernel or the level-synchronous engine", idx->ix.host.sigma - 1);
         return EDSBWT_E_UNSUPPORTED;
     }
     idx->ix.engine = engine;

@@ -104,7 +104,7 @@ void build_occ_blocks(const uint8_t* d_bytes, uint32_t n, const Lut& lut, DevBuf
     if (bad_out) *bad_out = hbad;
 }
 
-// ---- wide alphabets: 128-byte blocks (internal.cuh), letter codes 0..7, end-marker code 8
+// ---- wide alphabets: 96-byte blocks (internal.cuh), letter codes 0..7, end-marker code 8
 __global__ void occw_pack_kernel(const uint8_t* __restrict__ bytes, uint32_t n, Lut lut, uint4* __restrict__ occ,
                                  uint4* __restrict__ cnt_lo, uint4* __restrict__ cnt_hi, uint32_t ngroups, unsigned int* bad) {
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;          // one thread per 32-row group
@@ -135,8 +135,7 @@ __global__ void occw_counts_kernel(uint4* __restrict__ occ, const uint4* __restr
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= ngroups) return;
     const uint32_t j = g & 3;
-    const uint4 p = j < 2 ? pre_lo[g >> 2] : pre_hi[g >> 2];
-    occ[(size_t)(g >> 2) * OCCW_U4 + 4 + j] = (j & 1) ? make_uint4(p.z, p.w, 0u, 0u) : make_uint4(p.x, p.y, 0u, 0u);
+    if (j < 2) occ[(size_t)(g >> 2) * OCCW_U4 + 4 + j] = j ? pre_hi[g >> 2] : pre_lo[g >> 2];      // counts of letters 0..3 / 4..7
 }
 void build_occ_blocks_wide(const uint8_t* d_bytes, uint32_t n, const Lut& lut, DevBuf<uint4>& occ, DevBuf<uint8_t>& cubtmp, cudaStream_t s,
                            uint32_t tot[8], unsigned int* bad_out) {
@@ -215,7 +214,7 @@ struct PatView {
     const uint64_t* pack;    // [npat * words] letter codes, cb bits each (2; 4 for a wide alphabet): char i of pattern q at bits cb*(i % per) of pack[q*words + i/per], per = 64/cb
     const uint32_t* len;     // 0 for patterns that cannot match (bad character / empty)
     uint32_t words, npat, k; // k = seed depth used for this batch
-    uint32_t cb = 2, kb = 2; // kb = bits per character of a seed key (2; 3 for a wide alphabet)
+    uint32_t cb = 2, kr = 4; // kr = radix of a seed key: key = sum of code(char i of the suffix) * kr^i (4; the number of letters for a wide alphabet)
 };
 __global__ void encode_patterns_kernel(const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ off, const uint32_t* __restrict__ ids,
                                        uint32_t npat, Lut lut, uint32_t words, uint64_t* __restrict__ pack, uint32_t* __restrict__ len,
@@ -253,7 +252,7 @@ __global__ void seed_count_kernel(PatView pv, SeedView sv, uint32_t* __restrict_
     if (m == 0) { cnt[q] = 0; src[q] = 0; return; }
     uint32_t L = m < pv.k ? m : pv.k;
     uint32_t key = 0;
-    for (uint32_t i = 0; i < L; ++i) key |= pat_char(pv, q, m - L + i) << (pv.kb * i);
+    for (uint32_t i = 0, mul = 1; i < L; ++i, mul *= pv.kr) key += pat_char(pv, q, m - L + i) * mul;
     uint32_t a = __ldg(sv.off[L] + key), b = __ldg(sv.off[L] + key + 1);
     cnt[q] = b - a; src[q] = a;
 }
@@ -268,7 +267,7 @@ __global__ void seed_scatter_kernel(PatView pv, SeedView sv, const uint32_t* __r
     uint2 v = __ldg(sv.iv[L] + j);
     fpat[t] = q; flo[t] = v.x; fhi[t] = v.y;
 }
-// level L -> the nchild (4; 8 for a wide alphabet) children of every key, grouped by child key (nchild*key + c)
+// level L -> the nchild (4; the number of letters for a wide alphabet) children of every key, grouped by child key (nchild*key + c)
 __global__ void seed_expand_kernel(const uint32_t* __restrict__ pat, const uint2* __restrict__ iv,
                                    const uint32_t* __restrict__ off, uint32_t nF, uint32_t* __restrict__ opat, uint32_t* __restrict__ olo, uint32_t* __restrict__ ohi,
                                    uint32_t nchild) {
@@ -308,7 +307,7 @@ lf_step_kernel(const __grid_constant__ IndexView ix, PatView pv, uint32_t step, 
     uint32_t ii = act ? i : 0;
     uint32_t q = __ldg(pat + ii), a = __ldg(lo + ii), b = __ldg(hi + ii) + 1;      // [a, b) half-open
     int c = 0; bool pass = false; uint32_t L = 0, m = 0;
-    if (KEYMODE) c = WIDE ? (q & 7) : (q & 3);
+    if (KEYMODE) c = WIDE ? (int)(q % pv.kr) : (int)(q & 3);
     else {
         m = __ldg(pv.len + q);
         L = (m < pv.k ? m : pv.k) + step;
@@ -318,11 +317,11 @@ lf_step_kernel(const __grid_constant__ IndexView ix, PatView pv, uint32_t step, 
     uint32_t blk_a = a >> 7, blk_b = b >> 7;
     uint32_t rca, rda, rcb, rdb, Cc;
     if (WIDE) {
-        // the 128-byte layout: planes + mask in entry lane4, the counts of letters 2*lane4, 2*lane4+1 in entry 4 + lane4
-        uint4 va = make_uint4(0, 0, 0, 0), ca = va, vb, cb2;
-        if (doload) { const uint4* p = ix.occ + (size_t)blk_a * OCCW_U4; va = __ldg(p + lane4); ca = __ldg(p + 4 + lane4); }
+        // the 96-byte layout: planes + mask in entry lane4, the counts of letters 2*lane4, 2*lane4+1 in the 8 bytes at 64 + 8*lane4
+        uint4 va = make_uint4(0, 0, 0, 0), vb; uint2 ca = make_uint2(0, 0), cb2;
+        if (doload) { const uint4* p = ix.occ + (size_t)blk_a * OCCW_U4; va = __ldg(p + lane4); ca = __ldg(reinterpret_cast<const uint2*>(p + 4) + lane4); }
         vb = va; cb2 = ca;
-        if (doload && blk_b != blk_a) { const uint4* p = ix.occ + (size_t)blk_b * OCCW_U4; vb = __ldg(p + lane4); cb2 = __ldg(p + 4 + lane4); }
+        if (doload && blk_b != blk_a) { const uint4* p = ix.occ + (size_t)blk_b * OCCW_U4; vb = __ldg(p + lane4); cb2 = __ldg(reinterpret_cast<const uint2*>(p + 4) + lane4); }
         rank4w_from(va, ca, a, c, lane4, rca, rda);
         rank4w_from(vb, cb2, b, c, lane4, rcb, rdb);
         Cc = ix.Clw[c];
@@ -734,7 +733,8 @@ static void build_seed_table(Index& ix, uint32_t k) {
     Workspace& ws = *ix.ws;
     cudaStream_t s = ix.stream;
     ix.seed.assign(k + 1, nullptr);
-    const uint32_t kb = ix.key_bits, nchild = 1u << kb;      // 4 children per key; 8 for a wide alphabet
+    const uint32_t nchild = ix.key_radix;      // 4 children per key; one per letter for a wide alphabet
+    auto keys_at = [&](uint32_t L) { uint64_t v = 1; for (uint32_t i = 0; i < L; ++i) v *= nchild; return (uint32_t)v; };
     // level 1: the piles
     {
         std::vector<uint32_t> off(nchild + 1, 0), lo, hi;
@@ -753,10 +753,10 @@ static void build_seed_table(Index& ix, uint32_t k) {
         CUDA_OK(cudaStreamSynchronize(s));
         ix.seed_intervals = lo.size();
     }
-    PatView pv{}; pv.k = 0;
+    PatView pv{}; pv.k = 0; pv.kr = nchild;
     for (uint32_t L = 1; L < k; ++L) {
         SeedLevel* cur = ix.seed[L];
-        uint32_t nkeys = 1u << (kb * L), nF = (uint32_t)cur->n_iv;
+        uint32_t nkeys = keys_at(L), nF = (uint32_t)cur->n_iv;
         size_t nE = (size_t)nF * nchild;
         if (nE > 0xfffffff0ull) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "seed level %u too large", L + 1);
         ws.cur.ensure(nE ? nE : 1); ws.nxt.ensure(nF ? nF : 1);
@@ -783,14 +783,14 @@ static void build_seed_table(Index& ix, uint32_t k) {
     for (uint32_t L = 1; L <= k; ++L) {
         SeedLevel* lv = ix.seed[L];
         ivp[L] = lv->iv.p;
-        if (L == k && k > 8 && !ix.wide) continue;
-        const uint32_t nkeys = 1u << (kb * L);
+        if (L == k && k > 8) continue;
+        const uint32_t nkeys = keys_at(L);
         lv->cnt.exact(nkeys);
         seed_counts_kernel<<<grid_for(nkeys, 256), 256, 0, s>>>(lv->off.p, lv->iv.p, nkeys, lv->cnt.p);
     }
     {                                   // deepest level: the seed lookup of the hot kernel in one 16-byte gather
         SeedLevel* lv = ix.seed[k];
-        const uint32_t nkeys = 1u << (kb * k);
+        const uint32_t nkeys = keys_at(k);
         lv->first.exact(nkeys);
         seed_first_kernel<<<grid_for(nkeys, 256), 256, 0, s>>>(lv->off.p, lv->iv.p, nkeys, lv->first.p);
     }
@@ -830,11 +830,11 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     IndexView& v = ix.view;
     v.n = h.n; v.n_text = h.n_text; v.n_seg = h.n_seg; v.nletters = h.sigma - 1;
     for (uint32_t c = 0; c < 5; ++c) v.Cl[c] = c < h.sigma - 1 ? h.pile_start[c + 1] : h.n;
-    // 5..7 letters: 3-bit codes in 128-byte Occ blocks, base-8 seed keys, level-synchronous engine only
-    ix.wide = h.sigma > 5; ix.key_bits = ix.wide ? 3 : 2;
+    // 5..7 letters: 3-bit codes in 96-byte Occ blocks, seed keys in radix nletters
+    ix.wide = h.sigma > 5; ix.key_radix = ix.wide ? h.sigma - 1 : 4;
     v.wide = ix.wide ? 1u : 0u;
     for (uint32_t c = 0; c < 9; ++c) v.Clw[c] = c < h.sigma - 1 ? h.pile_start[c + 1] : h.n;
-    if (ix.wide) ix.engine = EDSBWT_ENGINE_LEVELSYNC;
+    if (ix.wide && ix.engine == EDSBWT_ENGINE_ITEMS) ix.engine = EDSBWT_ENGINE_FUSED;      // the item kernel reads 2-bit words
 
     // ---- K1: Occ blocks
     {
@@ -919,8 +919,10 @@ void build_device_index(Index& ix, const edsbwt_open_opts& o) {
     CUDA_OK(cudaStreamSynchronize(s));
     // ---- seed table
     int k = o.seed_k;
-    const int kmax = ix.wide ? 8 : 14;          // 4^14 = 2^28 keys; 8^8 = 2^24
-    if (k < 0) { k = 1; while (k < kmax && (1ull << (ix.key_bits * (k + 1))) <= (uint64_t)h.n) ++k; }      // floor(log4 n) (log8 when wide)
+    // depth = floor(log_radix n), at most 2^28 keys (4^14; 5^12 for {A,C,G,N,T}) and at most the 16 characters of a wide pattern window
+    auto keys_of = [&](int kk) { uint64_t v = 1; for (int i = 0; i < kk; ++i) v *= ix.key_radix; return v; };
+    int kmax = 1; while (kmax < 14 && keys_of(kmax + 1) <= (1ull << 28)) ++kmax;
+    if (k < 0) { k = 1; while (k < kmax && keys_of(k + 1) <= (uint64_t)h.n) ++k; }
     if (k < 1) k = 1;
     if (k > kmax) k = kmax;
     ix.seed_k = (uint32_t)k;
@@ -947,7 +949,7 @@ __global__ void ls_alive_init_kernel(PatView pv, SeedView sv, const uint32_t* __
         if (cnt[q]) la = L0;
         else for (uint32_t L = L0 - 1; L >= 1; --L) {
             uint32_t key = 0;
-            for (uint32_t i = 0; i < L; ++i) key |= pat_char(pv, q, m - L + i) << (pv.kb * i);
+            for (uint32_t i = 0, mul = 1; i < L; ++i, mul *= pv.kr) key += pat_char(pv, q, m - L + i) * mul;
             if (__ldg(sv.off[L] + key + 1) > __ldg(sv.off[L] + key)) { la = L; break; }
         }
     }
@@ -982,7 +984,7 @@ static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64
     ws.ppack.ensure((size_t)nsub * words); ws.plen.ensure(nsub);
     Lut lut = make_lut(ix.host);
     encode_patterns_kernel<<<grid_for(nsub, 128), 128, 0, s>>>(d_bytes, d_off, ids, nsub, lut, words, ws.ppack.p, ws.plen.p, ix.view.nletters, cb);
-    PatView pv{ws.ppack.p, ws.plen.p, words, nsub, k_eff, cb, ix.key_bits};
+    PatView pv{ws.ppack.p, ws.plen.p, words, nsub, k_eff, cb, ix.key_radix};
     SeedView sv{};
     for (uint32_t L = 1; L <= ix.seed_k; ++L) { sv.off[L] = ix.seed[L]->off.p; sv.iv[L] = ix.seed[L]->iv.p; sv.cnt[L] = ix.seed[L]->cnt.p; }
             sv.first = ix.seed[ix.seed_k]->first.p; sv.first_level = ix.seed_k;
@@ -1067,9 +1069,9 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
         CUDA_OK(cudaMemsetAsync(ws.fcursor.p, 0, 32, s));
         uint32_t nstage = 0;
         const uint32_t* ids = nullptr;
-        if (!ix.wide && (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move)) {
+        if (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move) {
             // first pass: the item kernel for batches that are (or are asked to be) 2-bit words, the step-loop kernel for bytes
-            const bool items = !move && (ix.engine == EDSBWT_ENGINE_ITEMS || (ix.engine == EDSBWT_ENGINE_FUSED && caller_words));
+            const bool items = !move && !ix.wide && (ix.engine == EDSBWT_ENGINE_ITEMS || (ix.engine == EDSBWT_ENGINE_FUSED && caller_words));
             size_t want = (size_t)npat * 2 + (1u << 16);
             if (want > 0xfffffff0ull) want = 0xfffffff0ull;
             ws.staging.ensure(want); ws.ovf_ids.ensure(npat);
@@ -1210,7 +1212,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     ls = edsbwt_stats{};
     ls.I = hs.I; ls.S = hs.S; ls.E = hs.E; ls.L = hs.L; ls.O = hs.O; ls.lf_intervals = hs.lf_intervals; ls.occ_blocks = hs.occ_blocks;
     ls.steps = steps; ls.kernel_launches = ws.launches; ls.lf_kernel_ms = ws.lf_ms; ls.total_ms = ms; ls.frontier_peak = peak;
-    ls.overflow_patterns = (!ix.wide && (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move)) ? novf1 : 0; ls.levelsync_patterns = novf;
+    ls.overflow_patterns = (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move) ? novf1 : 0; ls.levelsync_patterns = novf;
     if (fused_ran) { float fm = 0; CUDA_OK(cudaEventElapsedTime(&fm, ws.evf0, ws.evf1)); ls.search_kernel_ms = fm; }
     if (locate_ran) { float lm = 0; CUDA_OK(cudaEventElapsedTime(&lm, ws.evl0, ws.evl1)); ls.locate_kernel_ms = lm; }
 }

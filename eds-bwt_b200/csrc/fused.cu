@@ -25,7 +25,9 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 
 }  // namespace
 
-template <bool STATS, int MINB>
+// WIDE: the 3-bit layout of alphabets of 5..7 letters (96-byte blocks, 4-bit pattern windows of 16 characters, seed keys in
+// radix nletters); every WIDE branch below is a compile-time one, the 2-bit instantiation is the code it was before.
+template <bool STATS, int MINB, bool WIDE = false>
 __global__ void __launch_bounds__(FUSED_THREADS, MINB)
 fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant__ SeedView sv, uint32_t k, const uint8_t* __restrict__ bytes, const uint64_t* __restrict__ poff,
                     const uint32_t* __restrict__ ids, uint32_t npat, const uint8_t* __restrict__ lut, uint32_t cap, FusedOut out,
@@ -37,10 +39,12 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     __shared__ const uint32_t* s_off[17];
     __shared__ const uint2* s_iv[17];
     __shared__ const uint32_t* s_cnt[17];
-    __shared__ uint32_t s_Cl[5];
+    __shared__ uint32_t s_Cl[WIDE ? 9 : 5];
+    constexpr uint32_t PER = WIDE ? 16u : 32u;          // characters per 64-bit window
     for (int i = threadIdx.x; i < 256; i += FUSED_THREADS) s_lut[i] = lut[i];
     if (threadIdx.x < 17) { s_off[threadIdx.x] = sv.off[threadIdx.x]; s_iv[threadIdx.x] = sv.iv[threadIdx.x]; s_cnt[threadIdx.x] = sv.cnt[threadIdx.x]; }
-    if (threadIdx.x < 5) s_Cl[threadIdx.x] = ix.Cl[threadIdx.x];
+    if (WIDE) { if (threadIdx.x < 9) s_Cl[threadIdx.x] = ix.Clw[threadIdx.x]; }
+    else if (threadIdx.x < 5) s_Cl[threadIdx.x] = ix.Cl[threadIdx.x];
     __syncthreads();
 #define LIST(j) s_list[(j) * FUSED_THREADS + threadIdx.x]
 #define DOL(i) s_list[(cap - 1 - (i)) * FUSED_THREADS + threadIdx.x]
@@ -61,13 +65,17 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         // the whole pattern is checked against the alphabet first (a rejected pattern yields 0 and no trace position);
         // the window keeps the last 32 characters, which hold the seed key
         for (uint32_t hi = m; hi > 0 && ok; ) {
-            const uint32_t lo = hi > 32 ? hi - 32 : 0;
+            const uint32_t lo = hi > PER ? hi - PER : 0;
             uint64_t cw;
-            ok = fetch_codes(bytes + base + lo, hi - lo, s_lut, cw);
+            ok = WIDE ? fetch_codes_w(bytes + base + lo, hi - lo, s_lut, cw) : fetch_codes(bytes + base + lo, hi - lo, s_lut, cw);
             if (hi == m) { win = cw; win_lo = lo; }
             hi = lo;
         }
         if (ok) {
+            if (WIDE) {                                   // radix-nletters key of the last L0 characters (L0 <= 14 < 16: inside the window)
+                key = 0;
+                for (uint32_t i = L0; i > 0; --i) key = key * ix.nletters + ((uint32_t)(win >> (4 * (m - L0 - win_lo + i - 1))) & 7u);
+            } else
             key = (uint32_t)(win >> (2 * (m - L0 - win_lo))) & (uint32_t)((1ull << (2 * L0)) - 1);
             uint32_t a, n0; uint2 iv0 = make_uint2(1u, 0u);
             if (sv.first && L0 == sv.first_level) { const uint4 e = __ldg(sv.first + key); iv0 = make_uint2(e.x, e.y); a = e.z; n0 = e.w; }
@@ -93,11 +101,11 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
     for (; s < steps && nF && !ovf; ++s) {
         const uint32_t ci = m - L0 - s - 1;
         if (ci < win_lo) {                                                // the next 32 characters to the left
-            const uint32_t lo = win_lo > 32 ? win_lo - 32 : 0;
-            fetch_codes(bytes + base + lo, win_lo - lo, s_lut, win);
+            const uint32_t lo = win_lo > PER ? win_lo - PER : 0;
+            if (WIDE) fetch_codes_w(bytes + base + lo, win_lo - lo, s_lut, win); else fetch_codes(bytes + base + lo, win_lo - lo, s_lut, win);
             win_lo = lo;
         }
-        const int c = (int)((win >> (2 * (ci - win_lo))) & 3u);
+        const int c = WIDE ? (int)((win >> (4 * (ci - win_lo))) & 7u) : (int)((win >> (2 * (ci - win_lo))) & 3u);
         const uint32_t x0 = (c & 1) ? 0u : 0xffffffffu, x1 = (c & 2) ? 0u : 0xffffffffu;
         const uint32_t Cc = s_Cl[c];
         const bool beyond = STATS && (L0 + s >= kc);
@@ -107,7 +115,8 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         for (uint32_t j = 0; j < nF && !ovf; ++j) {
             const uint2 iv = LIST(j);
             uint32_t rca, rcb, rda, rdb, nblk;
-            lf_range(ix.occ, iv.x, iv.y + 1, c, x0, x1, rca, rcb, rda, rdb, nblk);
+            if (WIDE) lf_range_w(ix.occ, iv.x, iv.y + 1, c, rca, rcb, rda, rdb, nblk);
+            else lf_range(ix.occ, iv.x, iv.y + 1, c, x0, x1, rca, rcb, rda, rdb, nblk);
             if (STATS) { sLF += 1; sBlk += nblk; if (beyond) { sS += 1; sE += rdb - rda; } }
             if (rcb > rca) {
                 const uint32_t nlo = Cc + rca, nhi = Cc + rcb - 1;
@@ -141,7 +150,8 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
             for (uint32_t i = 0; i < ndol; ++i) {
                 const uint2 iv = DOL(i);
                 uint32_t rca, rcb, rda, rdb, nblk;
-                lf_range(ix.occ, iv.x, iv.y + 1, c, x0, x1, rca, rcb, rda, rdb, nblk);
+                if (WIDE) lf_range_w(ix.occ, iv.x, iv.y + 1, c, rca, rcb, rda, rdb, nblk);
+            else lf_range(ix.occ, iv.x, iv.y + 1, c, x0, x1, rca, rcb, rda, rdb, nblk);
                 if (STATS) { sLF += 1; sBlk += nblk; if (beyond) { sS += 1; sE += rdb - rda; } }
                 if (rcb > rca) {
                     const uint32_t nlo = Cc + rca, nhi = Cc + rcb - 1;
@@ -166,7 +176,8 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
         else if (nF || direct) la = m;
         else if (s > 0) la = L0 + s - 1;
         else for (uint32_t L = L0 - 1; L >= 1; --L) {                     // empty seed entry: longest shorter suffix that is not
-            const uint32_t kl = key >> (2 * (L0 - L));
+            uint32_t kl = key >> (2 * (L0 - L));
+            if (WIDE) { kl = key; for (uint32_t t = L; t < L0; ++t) kl /= ix.nletters; }
             if (__ldg(s_off[L] + kl + 1) > __ldg(s_off[L] + kl)) { la = L; break; }
         }
         out.alive[q] = la;
@@ -207,11 +218,11 @@ fused_search_kernel(const __grid_constant__ IndexView ix, const __grid_constant_
 }
 
 namespace {
-template <bool STATS, int MINB>
+template <bool STATS, int MINB, bool WIDE = false>
 void launch_instance(unsigned grid, size_t smem, cudaStream_t s, const IndexView& ix, const SeedView& sv, uint32_t k, const uint8_t* d_bytes, const uint64_t* d_off,
                      const uint32_t* d_ids, uint32_t npat, const uint8_t* d_lut, uint32_t cap, const FusedOut& out, StatsDev* st, uint32_t kc) {
-    CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<STATS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
-    fused_search_kernel<STATS, MINB><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+    CUDA_OK(cudaFuncSetAttribute(fused_search_kernel<STATS, MINB, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));      // per device: set at every launch
+    fused_search_kernel<STATS, MINB, WIDE><<<grid, FUSED_THREADS, smem, s>>>(ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
 }
 }  // namespace
 
@@ -221,7 +232,11 @@ void launch_fused_search(const IndexView& ix, const SeedView& sv, uint32_t k, co
     const size_t smem = (size_t)cap * FUSED_THREADS * sizeof(uint2);
     const unsigned grid = (npat + FUSED_THREADS - 1) / FUSED_THREADS;
 #define INSTANCE(STATS, MINB) launch_instance<STATS, MINB>(grid, smem, s, ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc)
-    if (st) INSTANCE(true, 10);
+    if (ix.wide) {                  // 24 registers of Occ block per interval: 8 CTAs/SM (64 registers)
+        if (st) launch_instance<true, 8, true>(grid, smem, s, ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+        else launch_instance<false, 8, true>(grid, smem, s, ix, sv, k, d_bytes, d_off, d_ids, npat, d_lut, cap, out, st, kc);
+    }
+    else if (st) INSTANCE(true, 10);
     else if (cap <= 14) INSTANCE(false, 12);      // 12 CTAs/SM: 40 registers (40 B of spill in a cold path), at most 14 KB of frontier each; 3.27 -> 3.09 ms
     else INSTANCE(false, 10);
 #undef INSTANCE

@@ -84,8 +84,8 @@ struct IndexView {
                                  // strings of the segments reachable from string eof_flat[r] (x > y: none) -- the whole
                                  // preceding_dollars_finder + empty-string closure of link() in one 8-byte gather
     const uint2*    str_info;    // string -> (1-based segment, index inside the segment)
-    // wide alphabets (5..7 letters + end-marker, e.g. {#,A,C,G,N,T}): 3-bit letter codes, 128-byte Occ blocks (below), searched
-    // by the level-synchronous engine only.  wide == 0: everything above, Cl[] included, is the 2-bit layout.
+    // wide alphabets (5..7 letters + end-marker, e.g. {#,A,C,G,N,T}): 3-bit letter codes, 96-byte Occ blocks (below).
+    // wide == 0: everything above, Cl[] included, is the 2-bit layout.
     uint32_t wide;
     uint32_t Clw[9];             // wide: Clw[c] = first row of the pile of letter c, n for c >= nletters
 };
@@ -140,19 +140,20 @@ __device__ __forceinline__ uint32_t occ_rank_eof(const uint4* __restrict__ occ, 
     return r;
 }
 
-// ---- wide alphabets: one 128-byte block per 128 rows = 8 x uint4.  Entry j (0..3) covers rows 32j..32j+31:
-//   [j]      .x .y .z bit-planes 0..2 of the 3-bit letter code, .w end-marker mask ('#' rows have planes 0)
-//   [4 + j]  .x .y   occurrences of letters 2j and 2j+1 in rows [0, 128*blk)
-// so that the same 4-lane group ranks any of up to 8 letters and '#' with two 128-bit loads per lane.
-constexpr uint32_t OCCW_U4 = 8;
+// ---- wide alphabets (5..7 letters): one 96-byte block per 128 rows = 6 x uint4
+//   [j], j = 0..3   rows 32j..32j+31: .x .y .z bit-planes 0..2 of the 3-bit letter code, .w end-marker mask ('#' rows have planes 0)
+//   [4], [5]        occurrences of letters 0..3 / 4..7 in rows [0, 128*blk)
+// A 4-lane group ranks any letter and '#' with one 128-bit + one 64-bit load per lane (lane j: entry j + the counts of letters
+// 2j, 2j+1); the one-thread-per-pattern kernel fetches the whole block with three 256-bit loads.
+constexpr uint32_t OCCW_U4 = 6;
 __device__ __forceinline__ uint32_t occw_match(const uint4& v, int c) {
     return ((c & 1) ? v.x : ~v.x) & ((c & 2) ? v.y : ~v.y) & ((c & 4) ? v.z : ~v.z) & ~v.w;
 }
-__device__ __forceinline__ void rank4w_from(uint4 va, uint4 vb, uint32_t pos, int c, int lane4, uint32_t& rc, uint32_t& rd) {
+__device__ __forceinline__ void rank4w_from(uint4 va, uint2 cn, uint32_t pos, int c, int lane4, uint32_t& rc, uint32_t& rd) {
     int below = (int)(pos & (OCC_ROWS - 1)) - 32 * lane4;
     uint32_t lm = below <= 0 ? 0u : (below >= 32 ? 0xffffffffu : ((1u << below) - 1u));
-    uint32_t pc = __popc(occw_match(va, c) & lm) + (lane4 == (c >> 1) ? ((c & 1) ? vb.y : vb.x) : 0u);
-    uint32_t pd = __popc(va.w & lm) - (vb.x + vb.y);          // wraps; the 4-lane sum is exact mod 2^32
+    uint32_t pc = __popc(occw_match(va, c) & lm) + (lane4 == (c >> 1) ? ((c & 1) ? cn.y : cn.x) : 0u);
+    uint32_t pd = __popc(va.w & lm) - (cn.x + cn.y);          // wraps; the 4-lane sum is exact mod 2^32
     pc += __shfl_xor_sync(0xffffffffu, pc, 1); pc += __shfl_xor_sync(0xffffffffu, pc, 2);
     pd += __shfl_xor_sync(0xffffffffu, pd, 1); pd += __shfl_xor_sync(0xffffffffu, pd, 2);
     rc = pc;
@@ -167,8 +168,7 @@ __device__ __forceinline__ uint32_t occw_symbol(const uint4* __restrict__ occ, u
 __device__ __forceinline__ uint32_t occw_rank1(const uint4* __restrict__ occ, uint32_t pos, int c) {
     uint32_t blk = pos >> 7, off = pos & 127;
     const uint4* b = occ + (size_t)blk * OCCW_U4;
-    const uint4 cn = __ldg(&b[4 + (c >> 1)]);
-    uint32_t r = (c & 1) ? cn.y : cn.x;
+    uint32_t r = __ldg(reinterpret_cast<const uint32_t*>(b + 4) + c);
     for (int j = 0; j < 4; ++j) {
         int below = (int)off - 32 * j;
         if (below <= 0) break;
@@ -180,12 +180,12 @@ __device__ __forceinline__ uint32_t occw_rank1(const uint4* __restrict__ occ, ui
 __device__ __forceinline__ uint32_t occw_rank_eof(const uint4* __restrict__ occ, uint32_t pos) {
     uint32_t blk = pos >> 7, off = pos & 127;
     const uint4* b = occ + (size_t)blk * OCCW_U4;
-    uint32_t r = blk * OCC_ROWS;
+    const uint4 c0 = __ldg(&b[4]), c1 = __ldg(&b[5]);
+    uint32_t r = blk * OCC_ROWS - (c0.x + c0.y + c0.z + c0.w + c1.x + c1.y + c1.z + c1.w);
     for (int j = 0; j < 4; ++j) {
-        uint4 v = __ldg(&b[j]), cn = __ldg(&b[4 + j]);
-        r -= cn.x + cn.y;
         int below = (int)off - 32 * j;
-        if (below > 0) r += __popc(v.w & (below >= 32 ? 0xffffffffu : ((1u << below) - 1u)));
+        if (below <= 0) break;
+        r += __popc(__ldg(&b[j]).w & (below >= 32 ? 0xffffffffu : ((1u << below) - 1u)));
     }
     return r;
 }
@@ -323,6 +323,69 @@ __device__ __forceinline__ void lf_range(const uint4* __restrict__ occ, uint32_t
     lf_range_loaded(B, occ, a, b, c, x0, x1, rca, rcb, rda, rdb, nblk);
 }
 
+// ---- the one-thread-per-pattern kernel on the wide layout: a whole 96-byte block in registers
+struct BlkW { uint32_t w[24]; };     // w[4j..4j+3] = planes 0..2 + '#' mask of rows 32j..32j+31; w[16 + c] = count of letter c before the block
+__device__ __forceinline__ void load_blk_w(const uint4* __restrict__ occ, uint32_t blk, BlkW& b) {
+    const uint4* p = occ + (size_t)blk * OCCW_U4;
+    ld256(p, b.w); ld256(p + 2, b.w + 8); ld256(p + 4, b.w + 16);
+}
+__device__ __forceinline__ uint32_t count_of_w(const BlkW& b, int c) {      // selects, not an indexed register array
+    const uint32_t lo = (c & 2) ? ((c & 1) ? b.w[19] : b.w[18]) : ((c & 1) ? b.w[17] : b.w[16]);
+    const uint32_t hi = (c & 2) ? ((c & 1) ? b.w[23] : b.w[22]) : ((c & 1) ? b.w[21] : b.w[20]);
+    return (c & 4) ? hi : lo;
+}
+__device__ __forceinline__ uint32_t letters_before_w(const BlkW& b) {
+    return b.w[16] + b.w[17] + b.w[18] + b.w[19] + b.w[20] + b.w[21] + b.w[22] + b.w[23];
+}
+// rank of letter c and number of '#' in rows [0, off) of the block
+__device__ __forceinline__ void rank_in_blk_w(const BlkW& b, uint32_t off, int c, uint32_t& rc, uint32_t& nmk) {
+    const uint32_t x0 = (c & 1) ? 0u : 0xffffffffu, x1 = (c & 2) ? 0u : 0xffffffffu, x2 = (c & 4) ? 0u : 0xffffffffu;
+    uint32_t r = count_of_w(b, c), k = 0;
+    #pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint32_t lm = low_mask((int)off - 32 * j);
+        r += __popc((b.w[4 * j] ^ x0) & (b.w[4 * j + 1] ^ x1) & (b.w[4 * j + 2] ^ x2) & ~b.w[4 * j + 3] & lm);
+        k += __popc(b.w[4 * j + 3] & lm);
+    }
+    rc = r; nmk = k;
+}
+// LF of the row range [a, b) by letter c on the wide layout (same contract as lf_range)
+__device__ __forceinline__ void lf_range_w(const uint4* __restrict__ occ, uint32_t a, uint32_t b, int c,
+                                           uint32_t& rca, uint32_t& rcb, uint32_t& rda, uint32_t& rdb, uint32_t& nblk) {
+    BlkW B;
+    const uint32_t blkA = a >> 7, blkB = b >> 7;
+    load_blk_w(occ, blkA, B);
+    uint32_t ka, kb;
+    rank_in_blk_w(B, a & 127u, c, rca, ka);
+    rda = blkA * OCC_ROWS - letters_before_w(B) + ka;
+    nblk = 1;
+    if (blkB != blkA) { load_blk_w(occ, blkB, B); nblk = 2; }
+    rank_in_blk_w(B, b & 127u, c, rcb, kb);
+    rdb = blkB * OCC_ROWS - letters_before_w(B) + kb;
+}
+// n <= 16 bytes at p -> 4-bit codes (character i at bits 4i..4i+3); false when a byte is not a letter of the index alphabet
+__device__ __forceinline__ bool fetch_codes_w(const uint8_t* __restrict__ p, uint32_t n, const uint8_t* s_lut, uint64_t& codes) {
+    uint32_t w[4];
+    if (((uint32_t)(uintptr_t)p & 15u) == 0) { const uint4 a = __ldg((const uint4*)p); w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; }
+    else {
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint32_t v = 0;
+            #pragma unroll
+            for (int t = 0; t < 4; ++t) if (4u * j + t < n) v |= (uint32_t)__ldg(p + 4 * j + t) << (8 * t);
+            w[j] = v;
+        }
+    }
+    uint64_t cw = 0; uint32_t bad = 0;
+    #pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const uint32_t c = s_lut[(w[i >> 2] >> (8 * (i & 3))) & 255u];
+        cw |= (uint64_t)(c & 7u) << (4 * i);
+        bad |= (c > 7u ? 1u : 0u) << i;
+    }
+    codes = n >= 16 ? cw : cw & ((1ull << (4 * n)) - 1);
+    return (bad & (n >= 16 ? 0xffffu : ((1u << n) - 1u))) == 0;
+}
 #endif
 
 // ---------------------------------------------------------------------------------------------------
@@ -446,8 +509,8 @@ struct Index {
     IndexView view{};
     uint32_t seed_k = 0;
     int locate_mode = EDSBWT_LOCATE_SA;
-    bool wide = false;               // 5..7 letters: 3-bit codes, 128-byte Occ blocks, level-synchronous engine only
-    uint32_t key_bits = 2;           // bits per character of a seed key (3 when wide)
+    bool wide = false;               // 5..7 letters: 3-bit codes, 96-byte Occ blocks
+    uint32_t key_radix = 4;          // seed key = sum of letter codes * radix^i (the number of letters when wide: 5^12 keys for {A,C,G,N,T})
     std::vector<SeedLevel*> seed;       // seed[L] for L = 1..seed_k (index 0 unused)
     uint64_t seed_intervals = 0;
     Workspace* ws = nullptr;

@@ -60,7 +60,6 @@ extern "C" int edsbwt_count_static(edsbwt_index* idx, const uint8_t* d_pat_bytes
     if (npat == 0) return EDSBWT_OK;
     try {
         Index& ix = idx->ix;
-        if (ix.wide) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "edsbwt_count_static launches the 2-bit step-loop kernel: not available for an alphabet of %u letters", ix.host.sigma - 1);
         std::lock_guard<std::mutex> all(g_mu);                 // one call at a time: the scratch is shared
         std::lock_guard<std::mutex> lock(ix.mu);               // ... and the handle's stream
         CUDA_OK(cudaSetDevice(ix.device));

@@ -60,7 +60,7 @@ typedef struct {
     uint32_t move_a;            /* balancing parameter                                          */
     uint32_t move_rounds;       /* balancing rounds the builder needed                          */
     uint32_t from_file;         /* bit 0: the HBM image was read from <base>.edsbwt; bit 1: the move table from <base>_MLF.edsbwt */
-    uint32_t engine;            /* EDSBWT_ENGINE_* in force (an alphabet of 5..7 letters always runs EDSBWT_ENGINE_LEVELSYNC)      */
+    uint32_t engine;            /* EDSBWT_ENGINE_* in force (an alphabet of 5..7 letters never runs EDSBWT_ENGINE_ITEMS)           */
     uint32_t table_occ_wide[64];/* tableOcc[sigma][sigma], row-major, for every sigma <= 8                                          */
 } edsbwt_info;
 
