@@ -68,7 +68,8 @@ def parse_args():
                          "length --len sharded over the GPUs (strong scaling), count-only and locate, on the same 250 Mbp index")
     ap.add_argument("--total", type=int, default=100000000, help="cfg5: patterns of the whole job")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="multi-GPU result gather: peer copies into an IPC arena on rank 0 (default) or ncclSend/ncclRecv")
-    ap.add_argument("--gather-chunks", type=int, default=4, help="chunks per shard of the multi-GPU leg (gather of chunk c overlaps the search of chunk c+1)")
+    ap.add_argument("--gather-chunks", type=int, default=0, help="chunks per shard of the multi-GPU leg (gather of chunk c overlaps the search of chunk c+1); "
+                    "0 = 2 chunks at 2 GPUs, 4 beyond (measured: profiles/r02_bench_n2_peer_*.json, r02_bench_n4.json, r02_bench_n8.json)")
     ap.add_argument("--engine", default="auto", choices=["auto", "items", "step"],
                     help="first-pass kernel: auto = the library default (step-loop kernel for bytes, item kernel for 2-bit words), or force one (A/B)")
     return ap.parse_args()
@@ -453,7 +454,9 @@ def main():
     gpu_occ_head = np.array(p_occ[:min(int(got), 1 << 18)], copy=True)      # tuples of the first patterns: row parity against the reference sample
     # ---- multi-GPU result gather (north star: "only an NCCL/NVLink gather of per-pattern counts and occurrence buffers"):
     #      shard search + all-gather of the counts + gather-v of the tuples to rank 0, timed on the device
-    gather_ms, gather_bytes, gather_parity, nchunks = 0.0, 0, None, args.gather_chunks
+    # fewer chunks = fewer kernel tails, more chunks = less of the last transfer exposed: at 2 GPUs rank 0 receives 102 MB and
+    # 2 chunks win (3.81 vs 4.06 ms), with 3 or 7 senders the inbound link is the longer pole and 4 chunks hide it
+    gather_ms, gather_bytes, gather_parity, nchunks = 0.0, 0, None, (args.gather_chunks or (2 if world == 2 else 4))
     if world > 1:
         # every shard is searched in chunks; the counts and tuples of chunk c are put on the wire (ncclSend / ncclRecv, one group
         # per chunk) as soon as it is searched and travel while chunk c + 1 is searched.  Timed on the device: CUDA events on this
