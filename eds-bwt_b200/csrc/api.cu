@@ -143,7 +143,8 @@ static Pipe& pipe_of(Index& ix) {
         ix.pipe = new Pipe;
         CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->in, cudaStreamNonBlocking));
         CUDA_OK(cudaStreamCreateWithFlags(&ix.pipe->outs, cudaStreamNonBlocking));
-        for (int i = 0; i < 2; ++i) { CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_in[i], cudaEventDisableTiming)); CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_out[i], cudaEventDisableTiming)); }
+        for (int i = 0; i < 2; ++i) CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_in[i], cudaEventDisableTiming));
+        for (int i = 0; i < Pipe::NRES; ++i) CUDA_OK(cudaEventCreateWithFlags(&ix.pipe->ev_out[i], cudaEventDisableTiming));
     }
     return *ix.pipe;
 }
@@ -216,8 +217,10 @@ static int search_into_impl(edsbwt_index* idx, const HostBatch& hb, int locate, 
         CUDA_OK(cudaEventRecord(P.ev_in[sl], P.in));
     };
     // search of patterns [lo, hi) of chunk [b, ..) whose input sits in slot sl; on an occurrence overflow the range is halved
-    std::function<void(int, uint32_t, uint32_t, uint32_t)> search_range = [&](int sl, uint32_t b, uint32_t lo, uint32_t hi) {
+    // (results go to slot rs: Pipe::NRES of them, so that the search is not held up by a copy-out that lags two chunks behind)
+    std::function<void(int, int, uint32_t, uint32_t, uint32_t)> search_range = [&](int sl, int rs, uint32_t b, uint32_t lo, uint32_t hi) {
         PatHint hint{};
+        hint.after = P.outs;          // the copy-out below waits for the locate kernels on the device, not here
         const uint8_t* d_bytes = nullptr; const uint64_t* d_off = nullptr; uint64_t nbytes = 0;
         if (packed) { hint.fixed_len = hb.fixed_len; hint.d_words = P.words[sl].p + (size_t)(lo - b) * hb.stride(); hint.d_invalid = hb.invalid ? P.invalid[sl].p + (lo - b) / 32 : nullptr; }
         else {
@@ -228,14 +231,14 @@ static int search_into_impl(edsbwt_index* idx, const HostBatch& hb, int locate, 
             else { hint.fixed_len = hb.fixed_len; hint.fixed_base = hb.off_of(lo); }
         }
         try {
-            run_search(ix, d_bytes, d_off, hi - lo, nbytes, 0, locate != 0, lf_variant, P.res[sl], lo, &hint);
+            run_search(ix, d_bytes, d_off, hi - lo, nbytes, 0, locate != 0, lf_variant, P.res[rs], lo, &hint);
         } catch (const OccOverflow&) {
             uint32_t mid = lo + (hi - lo) / 2;
             if (packed) mid = b + (((mid - b) + 31) & ~31u);
             if (mid <= lo || mid >= hi) EDS_FAIL(EDSBWT_E_UNSUPPORTED, "patterns %u..%u alone have more than %llu occurrences", lo, hi - 1, (unsigned long long)ix.occ_limit);
-            search_range(sl, b, lo, mid);
+            search_range(sl, rs, b, lo, mid);
             CUDA_OK(cudaStreamSynchronize(P.outs));              // the slot's result buffers are reused by the second half
-            search_range(sl, b, mid, hi);
+            search_range(sl, rs, b, mid, hi);
             return;
         }
         const edsbwt_stats& st = ix.last;
@@ -243,9 +246,9 @@ static int search_into_impl(edsbwt_index* idx, const HostBatch& hb, int locate, 
         acc.lf_intervals += st.lf_intervals; acc.lf_kernel_ms += st.lf_kernel_ms; acc.locate_kernel_ms += st.locate_kernel_ms; acc.total_ms += st.total_ms;
         acc.frontier_peak = std::max(acc.frontier_peak, st.frontier_peak); acc.occ_blocks += st.occ_blocks; acc.overflow_patterns += st.overflow_patterns;
         acc.levelsync_patterns += st.levelsync_patterns; acc.search_kernel_ms += st.search_kernel_ms;
-        // run_search returned with the compute stream idle: copy out on the third stream
-        CUDA_OK(cudaMemcpyAsync(counts + lo, P.res[sl].counts.p, (size_t)(hi - lo) * 4, cudaMemcpyDeviceToHost, P.outs));
-        const uint64_t k = P.res[sl].nocc;
+        // run_search returned with the sizes known and P.outs waiting for the chunk's last kernels: copy out on that stream
+        CUDA_OK(cudaMemcpyAsync(counts + lo, P.res[rs].counts.p, (size_t)(hi - lo) * 4, cudaMemcpyDeviceToHost, P.outs));
+        const uint64_t k = P.res[rs].nocc;
         if (locate && k) {
             if (grow && total_occ + k > occ_cap) {               // edsbwt_search: enlarge the malloc'ed buffer (copies into the old one must land first)
                 CUDA_OK(cudaStreamSynchronize(P.outs));
@@ -254,8 +257,8 @@ static int search_into_impl(edsbwt_index* idx, const HostBatch& hb, int locate, 
                 if (!nb) EDS_FAIL(EDSBWT_E_IO, "host out of memory for %llu occurrences", (unsigned long long)ncap);
                 *grow = occ = nb; occ_cap = ncap;
             }
-            if (occ && total_occ + k <= occ_cap) CUDA_OK(cudaMemcpyAsync(occ + total_occ, P.res[sl].occ.p, (size_t)k * sizeof(edsbwt_occ), cudaMemcpyDeviceToHost, P.outs));
-            else if (occ && total_occ < occ_cap) { CUDA_OK(cudaMemcpyAsync(occ + total_occ, P.res[sl].occ.p, (size_t)(occ_cap - total_occ) * sizeof(edsbwt_occ), cudaMemcpyDeviceToHost, P.outs)); nospace = true; }
+            if (occ && total_occ + k <= occ_cap) CUDA_OK(cudaMemcpyAsync(occ + total_occ, P.res[rs].occ.p, (size_t)k * sizeof(edsbwt_occ), cudaMemcpyDeviceToHost, P.outs));
+            else if (occ && total_occ < occ_cap) { CUDA_OK(cudaMemcpyAsync(occ + total_occ, P.res[rs].occ.p, (size_t)(occ_cap - total_occ) * sizeof(edsbwt_occ), cudaMemcpyDeviceToHost, P.outs)); nospace = true; }
             else nospace = true;
             total_occ += k;
         }
@@ -263,12 +266,12 @@ static int search_into_impl(edsbwt_index* idx, const HostBatch& hb, int locate, 
     issue_in(0);
     for (uint32_t c = 0; c < nchunks; ++c) {
         const uint32_t b = cb[c], e = cb[c + 1];
-        const int sl = c & 1;
+        const int sl = c & 1, rs = (int)(c % Pipe::NRES);
         if (c + 1 < nchunks) issue_in(c + 1);                       // overlaps the search below
-        if (c >= 2) CUDA_OK(cudaEventSynchronize(P.ev_out[sl]));     // result buffers of chunk c-2 are free again
+        if (c >= (uint32_t)Pipe::NRES) CUDA_OK(cudaEventSynchronize(P.ev_out[rs]));     // result buffers of chunk c - NRES are free again
         CUDA_OK(cudaStreamWaitEvent(ix.stream, P.ev_in[sl], 0));
-        search_range(sl, b, b, e);
-        CUDA_OK(cudaEventRecord(P.ev_out[sl], P.outs));
+        search_range(sl, rs, b, b, e);
+        CUDA_OK(cudaEventRecord(P.ev_out[rs], P.outs));
     }
     CUDA_OK(cudaStreamSynchronize(P.outs));
     drain.armed = false;

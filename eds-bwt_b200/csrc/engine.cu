@@ -1064,6 +1064,23 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             coff = ws.uoff.p; ws.launches += 1;
         }
     };
+    // total in 64 bits (the 32-bit offsets wrap silently when a batch of short patterns has more than 2^32 occurrences), the
+    // exclusive scan of the counts, entry npat = the total (written on the device), and the total on its way to h_pin[16..17]
+    bool scanned = false;
+    auto enqueue_occ_offsets = [&]() {
+        ws.occ_ofs.ensure((size_t)npat + 2);
+        size_t tmp = 0, tmp2 = 0;
+        cub::TransformInputIterator<unsigned long long, WidenU32, const uint32_t*> wide(out.counts.p, WidenU32());
+        unsigned long long* d_total = reinterpret_cast<unsigned long long*>(ws.d_stats + 1);
+        CUDA_OK(cub::DeviceReduce::Sum(nullptr, tmp2, wide, d_total, (int)npat, s));
+        CUDA_OK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, out.counts.p, ws.occ_ofs.p, (int)npat, s));
+        ws.cubtmp.ensure(std::max(tmp, tmp2));
+        CUDA_OK(cub::DeviceReduce::Sum(ws.cubtmp.p, tmp2, wide, d_total, (int)npat, s));
+        CUDA_OK(cub::DeviceScan::ExclusiveSum(ws.cubtmp.p, tmp, out.counts.p, ws.occ_ofs.p, (int)npat, s));
+        ws.launches += 4;
+        CUDA_OK(cudaMemcpyAsync(ws.occ_ofs.p + npat, d_total, 4, cudaMemcpyDeviceToDevice, s));      // low word: the total when it fits (checked on the host)
+        CUDA_OK(cudaMemcpyAsync(ws.h_pin + 16, d_total, 8, cudaMemcpyDeviceToHost, s));
+    };
     if (npat) {
         ws.plist.ensure(npat); ws.fcursor.ensure(8);
         CUDA_OK(cudaMemsetAsync(ws.fcursor.p, 0, 32, s));
@@ -1109,8 +1126,12 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             }
             ws.launches += 1; fused_ran = true;
             CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 32, cudaMemcpyDeviceToHost, s));
+            // The counts are final unless a pattern overflowed (none at cfg4): the occurrence total and the offsets of the locate
+            // are queued right behind the kernel, and ONE host round trip brings back the cursors and the total together.
+            if (locate) { enqueue_occ_offsets(); scanned = true; }
             CUDA_OK(cudaStreamSynchronize(s));
             nstage = ws.h_pin[0]; novf = ws.h_pin[1];
+            if (novf) scanned = false;
             if (ws.h_pin[5]) EDS_FAIL(EDSBWT_E_ARG, "total_bytes (%llu) is smaller than the span of the pattern offsets", (unsigned long long)total_bytes);
             novf1 = novf;
             // variant-dense indexes (cfg3: a site every 6 bp) carry longer frontiers: a second pass costs a full pattern latency,
@@ -1158,24 +1179,9 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
             }
         }
         if (locate) {
-            ws.occ_ofs.ensure((size_t)npat + 2);
-            // total in 64 bits first (the 32-bit offsets below wrap silently when a batch of short patterns has more than 2^32
-            // occurrences), then the exclusive scan of the counts (npat + 1 entries: the last one is the total)
-            size_t tmp = 0, tmp2 = 0;
-            cub::TransformInputIterator<unsigned long long, WidenU32, const uint32_t*> wide(out.counts.p, WidenU32());
-            unsigned long long* d_total = reinterpret_cast<unsigned long long*>(ws.d_stats + 1);
-            CUDA_OK(cub::DeviceReduce::Sum(nullptr, tmp2, wide, d_total, (int)npat, s));
-            CUDA_OK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, out.counts.p, ws.occ_ofs.p, (int)npat, s));
-            ws.cubtmp.ensure(std::max(tmp, tmp2));
-            CUDA_OK(cub::DeviceReduce::Sum(ws.cubtmp.p, tmp2, wide, d_total, (int)npat, s));
-            CUDA_OK(cub::DeviceScan::ExclusiveSum(ws.cubtmp.p, tmp, out.counts.p, ws.occ_ofs.p, (int)npat, s));
-            ws.launches += 4;
-            CUDA_OK(cudaMemcpyAsync(ws.h_pin, d_total, 8, cudaMemcpyDeviceToHost, s));
-            CUDA_OK(cudaStreamSynchronize(s));
-            const uint64_t nocc = *reinterpret_cast<const unsigned long long*>(ws.h_pin);
+            if (!scanned) { enqueue_occ_offsets(); CUDA_OK(cudaStreamSynchronize(s)); }
+            const uint64_t nocc = *reinterpret_cast<const unsigned long long*>(ws.h_pin + 16);
             if (nocc > ix.occ_limit) throw OccOverflow{};
-            const uint32_t tot32 = (uint32_t)nocc;
-            CUDA_OK(cudaMemcpyAsync(ws.occ_ofs.p + npat, &tot32, 4, cudaMemcpyHostToDevice, s));
             out.nocc = nocc;
             if (nocc) {
                 out.occ.ensure(nocc);
@@ -1203,18 +1209,23 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
         }
     }
     CUDA_OK(cudaEventRecord(ws.ev1, s));
-    CUDA_OK(cudaStreamSynchronize(s));
+    // The chunk pipeline of the host-buffer calls (api.cu) does not wait for the locate kernels here: its copy-out stream takes
+    // the dependency, and the next chunk's kernels queue up behind this one's without a host round trip in between.  The
+    // per-kernel times of edsbwt_last_stats are then not available (0); counters and launch counts are.
+    const bool deferred = hint && hint->after && !stats;
+    if (deferred) CUDA_OK(cudaStreamWaitEvent(hint->after, ws.ev1, 0));
+    else CUDA_OK(cudaStreamSynchronize(s));
     CUDA_OK(cudaGetLastError());
     StatsDev hs{};
     if (stats) CUDA_OK(cudaMemcpy(&hs, ws.d_stats, sizeof hs, cudaMemcpyDeviceToHost));
-    float ms = 0; CUDA_OK(cudaEventElapsedTime(&ms, ws.ev0, ws.ev1));
+    float ms = 0; if (!deferred) CUDA_OK(cudaEventElapsedTime(&ms, ws.ev0, ws.ev1));
     edsbwt_stats& ls = ix.last;
     ls = edsbwt_stats{};
     ls.I = hs.I; ls.S = hs.S; ls.E = hs.E; ls.L = hs.L; ls.O = hs.O; ls.lf_intervals = hs.lf_intervals; ls.occ_blocks = hs.occ_blocks;
     ls.steps = steps; ls.kernel_launches = ws.launches; ls.lf_kernel_ms = ws.lf_ms; ls.total_ms = ms; ls.frontier_peak = peak;
     ls.overflow_patterns = (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move) ? novf1 : 0; ls.levelsync_patterns = novf;
-    if (fused_ran) { float fm = 0; CUDA_OK(cudaEventElapsedTime(&fm, ws.evf0, ws.evf1)); ls.search_kernel_ms = fm; }
-    if (locate_ran) { float lm = 0; CUDA_OK(cudaEventElapsedTime(&lm, ws.evl0, ws.evl1)); ls.locate_kernel_ms = lm; }
+    if (fused_ran) { float fm = 0; CUDA_OK(cudaEventElapsedTime(&fm, ws.evf0, ws.evf1)); ls.search_kernel_ms = fm; }      // (completed before the cursors were read)
+    if (locate_ran && !deferred) { float lm = 0; CUDA_OK(cudaEventElapsedTime(&lm, ws.evl0, ws.evl1)); ls.locate_kernel_ms = lm; }
 }
 
 }  // namespace edsbwt

@@ -451,11 +451,13 @@ struct SearchOut {
 // previous chunk is searched on the compute stream and the chunk before that is copied out on a third
 struct Pipe {
     cudaStream_t in = nullptr, outs = nullptr;
-    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+    static constexpr int NRES = 2;      // result slots (4 were measured: no gain, profiles/r02_e2e_chunks.txt -- the copy-out is slow because it shares the memory system with the search kernel, not because the search waits for a slot)
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_out[NRES] = {nullptr, nullptr};
     DevBuf<uint8_t> bytes[2]; DevBuf<uint64_t> off[2];
     DevBuf<uint64_t> words[2]; DevBuf<uint32_t> invalid[2];      // packed batches (edsbwt_search_into_packed)
-    SearchOut res[2];
-    ~Pipe() { for (int i = 0; i < 2; ++i) { if (ev_in[i]) cudaEventDestroy(ev_in[i]); if (ev_out[i]) cudaEventDestroy(ev_out[i]); }
+    SearchOut res[NRES];
+    ~Pipe() { for (int i = 0; i < 2; ++i) if (ev_in[i]) cudaEventDestroy(ev_in[i]);
+              for (int i = 0; i < NRES; ++i) if (ev_out[i]) cudaEventDestroy(ev_out[i]);
               if (in) cudaStreamDestroy(in); if (outs) cudaStreamDestroy(outs); }
 };
 
@@ -554,6 +556,7 @@ struct PatHint {
     uint64_t fixed_base = 0;
     const uint64_t* d_words = nullptr;   // the caller's own 2-bit words (PackedPats layout, stride ceil(fixed_len / 32)); d_bytes may then be null
     const uint32_t* d_invalid = nullptr; // with d_words: bitmap of patterns that hold a byte outside the alphabet (null: none)
+    cudaStream_t after = nullptr;        // not null: run_search returns without waiting for its last kernels; `after` is made to wait for them instead
 };
 void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32_t npat, uint64_t total_bytes,
                 uint32_t max_len, bool locate, int lf_variant, SearchOut& out, uint32_t pat_base = 0, const PatHint* hint = nullptr);
