@@ -126,3 +126,37 @@ def test_empty_pattern_file(eb, tmp_path):
     open(pf, "wb").close()
     data, off = eb.read_patterns(pf)
     assert off.tolist() == [0] and len(data) == 0
+
+
+def test_struct_layouts_match_the_header(eb, tmp_path):
+    """the ctypes mirrors of include/edsbwt.h's structs (tests / bench binding) have the C compiler's sizes and field offsets"""
+    import ctypes as C
+    import subprocess
+    structs = {"edsbwt_info": eb.Info, "edsbwt_open_opts": eb.OpenOpts, "edsbwt_stats": eb.Stats, "edsbwt_gather_cfg": eb.GatherCfg}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "edsbwt.h"', 'int main(void) {']
+    for cname, cls in structs.items():
+        lines.append('printf("%s sizeof %%zu\\n", sizeof(%s));' % (cname, cname))
+        for fname, _ in cls._fields_:
+            cfield = {"granule_bytes": "granule_bytes"}.get(fname, fname)
+            lines.append('printf("%s %s %%zu\\n", offsetof(%s, %s));' % (cname, fname, cname, cfield))
+    lines.append('printf("edsbwt_occ sizeof %zu\\n", sizeof(edsbwt_occ)); return 0; }')
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = str(tmp_path / "layout")
+    inc = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include")
+    subprocess.run(["gcc", "-std=c99", "-I", inc, str(src), "-o", exe], check=True)
+    out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout.split("\n")
+    seen = 0
+    for ln in out:
+        t = ln.split()
+        if len(t) != 3:
+            continue
+        cname, what, val = t[0], t[1], int(t[2])
+        if cname == "edsbwt_occ":
+            assert val == eb.OCC_DTYPE.itemsize == 20
+        elif what == "sizeof":
+            assert C.sizeof(structs[cname]) == val, cname
+        else:
+            assert getattr(structs[cname], what).offset == val, (cname, what)
+        seen += 1
+    assert seen > 40
