@@ -1009,6 +1009,14 @@ static uint32_t levelsync_search(Index& ix, const uint8_t* d_bytes, const uint64
     return nF;
 }
 
+// Clears the few control words of a search on the SMs.  cudaMemsetAsync runs on a copy engine: while the chunk pipeline keeps the
+// copy engines busy with 17 MB / 43 MB transfers, each of these 32-byte memsets waited 40-70 us behind them and held up the
+// search kernel queued after it (profiles/r02_e2e_timeline.txt: 0.2 ms per chunk).
+__global__ void zero_words_kernel(uint32_t* __restrict__ a, uint32_t na, uint32_t* __restrict__ b, uint32_t nb) {
+    const uint32_t i = threadIdx.x;
+    if (i < na) a[i] = 0u;
+    if (i < nb) b[i] = 0u;
+}
 __global__ void fixed_offsets_kernel(uint64_t* __restrict__ off, uint32_t n, uint64_t first, uint64_t len) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i <= n) off[i] = first + (uint64_t)i * len;
@@ -1038,7 +1046,8 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     // min(k, canonical_k) so that every step beyond the canonical depth is really executed and counted
     const uint32_t k_eff = stats ? std::min(ix.seed_k, ix.canonical_k) : ix.seed_k;
     StatsDev* st = stats ? ws.d_stats : nullptr;
-    CUDA_OK(cudaMemsetAsync(ws.d_stats, 0, sizeof(StatsDev), s));
+    static_assert(sizeof(StatsDev) / 4 <= 32, "zero_words_kernel clears at most 32 words per array");
+    if (!npat) CUDA_OK(cudaMemsetAsync(ws.d_stats, 0, sizeof(StatsDev), s));
     CUDA_OK(cudaEventRecord(ws.ev0, s));
     out.npat = npat; out.nocc = 0;
     out.counts.ensure(npat ? npat : 1);
@@ -1083,7 +1092,8 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
     };
     if (npat) {
         ws.plist.ensure(npat); ws.fcursor.ensure(8);
-        CUDA_OK(cudaMemsetAsync(ws.fcursor.p, 0, 32, s));
+        // counters + cursors ([0] staging slots, [1] / [2] overflow of pass 1 / 2, [3] heavy patterns of the locate, [4] item-kernel work, [5] pack error)
+        zero_words_kernel<<<1, 32, 0, s>>>(reinterpret_cast<uint32_t*>(ws.d_stats), (uint32_t)(sizeof(StatsDev) / 4), ws.fcursor.p, 8u);
         uint32_t nstage = 0;
         const uint32_t* ids = nullptr;
         if (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move) {
@@ -1189,8 +1199,7 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
                 if (move) launch_move_locate(ix.view, ix.move->view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, npat, nocc, pat_base, out.occ.p, st, s);
                 else {
                     // light patterns: one thread each; heavy ones (> 32 occurrences) are queued on the device and taken by warps
-                    ws.heavy.ensure(npat); uint32_t* nheavy = ws.fcursor.p + 3;
-                    CUDA_OK(cudaMemsetAsync(nheavy, 0, 4, s));
+                    ws.heavy.ensure(npat); uint32_t* nheavy = ws.fcursor.p + 3;      // cleared with the cursors at the start of the search
                     const unsigned hgrid = 148 * 8;
                     if (ix.locate_mode == EDSBWT_LOCATE_WALK) {
                         locate_light_kernel<true><<<grid_for(npat, 256), 256, 0, s>>>(ix.view, ws.plist.p, ws.occ_ofs.p, ws.staging.p, ix.seed_ivp.p, npat, pat_base, out.occ.p, ws.heavy.p, nheavy, st);
