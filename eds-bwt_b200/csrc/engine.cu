@@ -1017,6 +1017,22 @@ __global__ void zero_words_kernel(uint32_t* __restrict__ a, uint32_t na, uint32_
     if (i < na) a[i] = 0u;
     if (i < nb) b[i] = 0u;
 }
+// Read-back of the control words through the SMs: the cursors (and, after the scans, the occurrence total) are stored straight
+// into the pinned host words of the workspace (cudaMallocHost memory is device-accessible under UVA).  As 32-byte
+// cudaMemcpyAsync calls they ran on the device-to-host copy engine, IN ORDER behind the previous chunk's 35-60 MB tuple copy:
+// the host saw the cursors up to 0.3 ms after the search kernel had ended, and the locate kernels and the next chunk's search
+// started that much later (profiles/r02_e2e_timeline.txt).  total != nullptr: also occ_ofs[npat] = low word of the total.
+__global__ void publish_control_kernel(const uint32_t* __restrict__ cursors, const unsigned long long* __restrict__ total,
+                                       uint32_t* __restrict__ ofs_end, volatile uint32_t* __restrict__ host_words) {
+    const uint32_t i = threadIdx.x;
+    if (i < 8) host_words[i] = cursors[i];
+    if (total && i == 8) {
+        const unsigned long long t = *total;
+        *ofs_end = (uint32_t)t;
+        host_words[16] = (uint32_t)t; host_words[17] = (uint32_t)(t >> 32);
+    }
+    __threadfence_system();
+}
 __global__ void fixed_offsets_kernel(uint64_t* __restrict__ off, uint32_t n, uint64_t first, uint64_t len) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i <= n) off[i] = first + (uint64_t)i * len;
@@ -1087,13 +1103,15 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
         CUDA_OK(cub::DeviceReduce::Sum(ws.cubtmp.p, tmp2, wide, d_total, (int)npat, s));
         CUDA_OK(cub::DeviceScan::ExclusiveSum(ws.cubtmp.p, tmp, out.counts.p, ws.occ_ofs.p, (int)npat, s));
         ws.launches += 4;
-        CUDA_OK(cudaMemcpyAsync(ws.occ_ofs.p + npat, d_total, 4, cudaMemcpyDeviceToDevice, s));      // low word: the total when it fits (checked on the host)
-        CUDA_OK(cudaMemcpyAsync(ws.h_pin + 16, d_total, 8, cudaMemcpyDeviceToHost, s));
+        // occ_ofs[npat] = low word of the total (the total itself when it fits: checked on the host), cursors + total to the host
+        publish_control_kernel<<<1, 32, 0, s>>>(ws.fcursor.p, d_total, ws.occ_ofs.p + npat, ws.h_pin);
+        ws.launches += 1;
     };
     if (npat) {
         ws.plist.ensure(npat); ws.fcursor.ensure(8);
         // counters + cursors ([0] staging slots, [1] / [2] overflow of pass 1 / 2, [3] heavy patterns of the locate, [4] item-kernel work, [5] pack error)
         zero_words_kernel<<<1, 32, 0, s>>>(reinterpret_cast<uint32_t*>(ws.d_stats), (uint32_t)(sizeof(StatsDev) / 4), ws.fcursor.p, 8u);
+        ws.launches += 1;
         uint32_t nstage = 0;
         const uint32_t* ids = nullptr;
         if (ix.engine != EDSBWT_ENGINE_LEVELSYNC || move) {
@@ -1135,10 +1153,10 @@ void run_search(Index& ix, const uint8_t* d_bytes, const uint64_t* d_off, uint32
                 CUDA_OK(cudaEventRecord(ws.evf1, s));
             }
             ws.launches += 1; fused_ran = true;
-            CUDA_OK(cudaMemcpyAsync(ws.h_pin, ws.fcursor.p, 32, cudaMemcpyDeviceToHost, s));
             // The counts are final unless a pattern overflowed (none at cfg4): the occurrence total and the offsets of the locate
             // are queued right behind the kernel, and ONE host round trip brings back the cursors and the total together.
             if (locate) { enqueue_occ_offsets(); scanned = true; }
+            else { publish_control_kernel<<<1, 32, 0, s>>>(ws.fcursor.p, nullptr, nullptr, ws.h_pin); ws.launches += 1; }
             CUDA_OK(cudaStreamSynchronize(s));
             nstage = ws.h_pin[0]; novf = ws.h_pin[1];
             if (novf) scanned = false;
